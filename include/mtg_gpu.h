@@ -1,0 +1,127 @@
+/*
+ * mtg_gpu.h -- C ABI of the B200-native `metagraph build` hot path.
+ *
+ * This is the boundary a MetaGraph maintainer binds instead of the CPU
+ * implementation behind IBOSSChunkConstructor
+ *   (metagraph/src/graph/representation/succinct/boss_chunk_construct.hpp:18-34,
+ *    factory boss_chunk_construct.cpp:1134-1178).
+ * Plain pointers and sizes only; no C++/torch types cross it. All functions
+ * return 0 on success or an MTG_ERR_* code; mtg_last_error() gives the text.
+ * There is NO CPU fallback: every entry point fails with MTG_ERR_CUDA when no
+ * sm_100 device / kernel image is available.
+ *
+ * Reads -> packed k-mers (tight alphabet, KMerBOSS layout kmer_boss.hpp:17-28)
+ *   -> radix sort -> unique / saturating count -> [canonical] reverse-complement
+ *   completion -> dummy sink / source k-mer recovery -> BOSS arrays W, last, F
+ *   [, weights] in the sdsl int_vector bit layout BOSS::Chunk stores
+ *   (boss_chunk.cpp:31-133, :372-386).
+ */
+#ifndef MTG_GPU_H
+#define MTG_GPU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MTG_OK 0
+#define MTG_ERR_BAD_ARG 1
+#define MTG_ERR_CUDA 2
+#define MTG_ERR_OOM 3
+#define MTG_ERR_STATE 4
+#define MTG_ERR_UNSUPPORTED 5
+
+#define MTG_ALPHABET_DNA 0      /* -D_DNA_GRAPH: "ACGT" / "$ACGT" (kmer/alphabets.hpp:65-77,128-141) */
+#define MTG_ALPHABET_PROTEIN 1  /* -D_PROTEIN_GRAPH (kmer/alphabets.hpp:27-39,90-102) */
+
+#define MTG_MAX_SIGMA 32
+#define MTG_MAX_K 128
+
+typedef struct mtg_ctx mtg_ctx;
+
+/* Mirrors the arguments of IBOSSChunkConstructor::initialize
+ * (boss_chunk_construct.hpp:22-31). */
+typedef struct mtg_params {
+    uint32_t k;               /* BOSS node length (CLI -k minus 1); collected k-mers have k+1 chars */
+    uint32_t alphabet;        /* MTG_ALPHABET_* (a compile-time macro in the reference) */
+    uint32_t both_strands;    /* canonical mode: CANONICAL_ONLY collection + rc completion */
+    uint32_t bits_per_count;  /* 0 = no weights, else 1..32 (--count-width) */
+    const char *filter_suffix;/* NULL or "" ; non-empty suffix (--suffix) => MTG_ERR_UNSUPPORTED for now */
+    int32_t device;           /* CUDA device ordinal */
+    uint32_t reserved;
+    double memory_preallocated; /* bytes; hint for the initial read-staging capacity */
+} mtg_params;
+
+/* Result of mtg_build_chunk: the contents of a BOSS::Chunk (boss_chunk.hpp:19-104).
+ * Pointers are library-owned pinned host memory, valid until mtg_free_chunk().
+ * W / last / weights hold n_rows entries (row 0 is the placeholder) packed LSB-first
+ * into little-endian 64-bit words exactly as sdsl::int_vector<> stores them. */
+typedef struct mtg_chunk {
+    uint64_t n_rows;
+    uint32_t sigma;           /* BOSS alphabet size incl. '$' */
+    uint32_t k;               /* node length */
+    uint32_t W_width;         /* bits per W entry: hi(2*sigma-1)+1 (boss_chunk.cpp:388-390) */
+    uint32_t weights_width;   /* bits_per_count, 0 if no weights */
+    uint64_t F[MTG_MAX_SIGMA];
+    const uint64_t *W;        /* ceil(n_rows*W_width/64) words */
+    const uint64_t *last;     /* ceil(n_rows/64) words */
+    const uint64_t *weights;  /* ceil(n_rows*weights_width/64) words or NULL */
+    /* counters the reference logs (boss_chunk_construct.cpp:267-302) */
+    uint64_t n_input_kmers;   /* valid (k+1)-windows extracted from the reads */
+    uint64_t n_real;          /* real k-mers after sort/unique (and rc completion) */
+    uint64_t n_dummy_sink;
+    uint64_t n_dummy_source[MTG_MAX_K]; /* [i] = #dummy k-mers with dummy prefix length i+1 */
+    /* device time (CUDA events) of the last build, ms; [0]=total, then per phase */
+    float ms_total, ms_extract, ms_sort, ms_unique, ms_rc, ms_dummy, ms_emit;
+    uint32_t n_kernel_launches;
+    uint32_t reserved;
+    void *impl;
+} mtg_chunk;
+
+/* Creates a constructor for one chunk (= IBOSSChunkConstructor::initialize). */
+int mtg_create(const mtg_params *params, mtg_ctx **out);
+void mtg_destroy(mtg_ctx *ctx);
+const char *mtg_last_error(const mtg_ctx *ctx); /* ctx may be NULL: last creation error */
+
+/* add_sequences (boss_chunk_construct.cpp:988-994): `n_reads` reads stored back to back
+ * in `bases`; read i is bases[offsets[i] .. offsets[i+1]). `counts` (nullable) gives the
+ * per-read multiplicity (vector<pair<string,uint64_t>> overload); NULL means 1.
+ * Thread-safe; the caller's buffers may be reused as soon as the call returns. */
+int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets,
+                   const uint64_t *counts, size_t n_reads);
+
+/* Same for reads that are already resident in device memory in the library's packed
+ * layout: the reads separated (and terminated) by one 0x00 byte each, `n_bytes` total,
+ * 16-byte aligned. `n_windows_max` >= number of (k+1)-windows they contain. The buffer
+ * must stay valid until mtg_build_chunk returns. All counts are 1. */
+int mtg_push_packed_device(mtg_ctx *ctx, const void *d_packed, size_t n_bytes,
+                           uint64_t n_windows_max);
+
+/* Host helper producing that packed layout (for callers that keep reads resident). */
+size_t mtg_packed_size(const uint64_t *offsets, size_t n_reads);
+void mtg_pack_reads(const char *bases, const uint64_t *offsets, size_t n_reads, char *dst);
+
+/* build_chunk (boss_chunk_construct.cpp:996-1040): drains the pipeline, runs
+ * sort/unique/rc/dummy/emit on the device, copies the chunk to pinned host memory.
+ * The context is cleared afterwards (like kmer_collector.clear(), :353). */
+int mtg_build_chunk(mtg_ctx *ctx, mtg_chunk *out);
+void mtg_free_chunk(mtg_chunk *chunk);
+
+/* Test hooks (parity of intermediate stages): run extraction + sort +
+ * unique (+ rc completion) only and return the sorted real k-mers of the collector
+ * alphabet: words[2*i] = low 64 bits, words[2*i+1] = high 64 bits; counts nullable. */
+int mtg_debug_sorted_kmers(mtg_ctx *ctx, uint64_t **words, uint32_t **counts, uint64_t *n);
+void mtg_debug_free(void *p);
+
+/* Stand-alone primitive hooks (device-side parity tests of the radix sort). */
+int mtg_debug_sort_u64(int device, uint64_t *keys, uint32_t *vals /*nullable*/, uint64_t n,
+                       uint32_t key_bits);
+int mtg_debug_sort_u128(int device, uint64_t *keys_lohi, uint32_t *vals /*nullable*/, uint64_t n,
+                        uint32_t key_bits);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MTG_GPU_H */

@@ -1,0 +1,751 @@
+// C ABI (include/mtg_gpu.h) and the pipeline driver of the B200 BOSS chunk build.
+// Host-side counterpart of BOSSChunkConstructor / KmerCollector
+// (boss_chunk_construct.cpp:948-1048, kmer/kmer_collector.cpp:129-234) and of
+// construct_boss_chunk (boss_chunk_construct.cpp:248-356).
+#include <algorithm>
+#include <cstring>
+#include <deque>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../include/mtg_gpu.h"
+#include "mtg_stages.cuh"
+
+using namespace mtg;
+
+namespace {
+
+thread_local std::string g_create_error;
+
+struct DevBuf {   // stream-ordered device allocation
+    void *p = nullptr;
+    size_t bytes = 0;
+    cudaStream_t s = nullptr;
+    DevBuf() {}
+    DevBuf(size_t n, cudaStream_t st) { alloc(n, st); }
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    DevBuf(DevBuf &&o) noexcept { p = o.p; bytes = o.bytes; s = o.s; o.p = nullptr; }
+    DevBuf &operator=(DevBuf &&o) noexcept {
+        if (this != &o) { release(); p = o.p; bytes = o.bytes; s = o.s; o.p = nullptr; }
+        return *this;
+    }
+    void alloc(size_t n, cudaStream_t st) {
+        release();
+        s = st;
+        bytes = n ? n : 16;
+        MTG_CUDA(cudaMallocAsync(&p, bytes, s));
+    }
+    void release() {
+        if (p) cudaFreeAsync(p, s);
+        p = nullptr;
+    }
+    ~DevBuf() { release(); }
+    template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct PinnedBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    cudaEvent_t ev = nullptr;
+    bool busy = false;
+};
+
+struct ReadSegment {
+    const uint8_t *d_packed = nullptr;
+    size_t nbytes = 0;
+    uint64_t n_windows_max = 0;
+    DevBuf own_packed, starts, counts;
+    uint64_t n_reads = 0;
+    bool has_starts = false, has_counts = false;
+};
+
+struct ChunkImpl {
+    void *pinned = nullptr;
+};
+
+}  // namespace
+
+struct mtg_ctx {
+    mtg_params prm;
+    Alpha al;
+    uint32_t L2;
+    ExtractLut lut;
+    int device = 0;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    std::mutex mu;
+    std::vector<ReadSegment> segs;
+    std::deque<PinnedBuf> pinned;
+    bool any_explicit_counts = false;
+    uint32_t cmax = 0;   // container count type max (boss_chunk_construct.cpp:1147-1160)
+    std::string error;
+    unsigned launches = 0;
+};
+
+namespace {
+
+int fail(mtg_ctx *ctx, int code, const std::string &msg) {
+    if (ctx) ctx->error = msg; else g_create_error = msg;
+    return code;
+}
+int fail_cuda(mtg_ctx *ctx, const CudaError &e) {
+    std::string msg = std::string("CUDA error: ") + cudaGetErrorString(e.err) + " at " + e.file + ":"
+                      + std::to_string(e.line);
+    cudaGetLastError();
+    return fail(ctx, e.err == cudaErrorMemoryAllocation ? MTG_ERR_OOM : MTG_ERR_CUDA, msg);
+}
+
+// alphabets (kmer/alphabets.hpp:27-149), rebuilt from their definitions
+void build_lut(uint32_t alphabet, ExtractLut *lut) {
+    if (alphabet == MTG_ALPHABET_DNA) {
+        for (int i = 0; i < 256; ++i) lut->code[i] = 0xff;
+        const char *up = "ACGT", *lo = "acgt";
+        for (int c = 0; c < 4; ++c) { lut->code[(int)up[c]] = c; lut->code[(int)lo[c]] = c; }
+        lut->code[(int)'U'] = lut->code[(int)'u'] = 3;
+    } else {
+        // every character is a letter of the protein alphabet ('X' = 25 for unknowns);
+        // chars >= 0x80 map like table[0] (kmer_extractor.cpp:30-34)
+        for (int i = 0; i < 256; ++i) lut->code[i] = 25;
+        const char *alph = "ABCDEFGHIJKLMNOPQRSTUVWYZX";
+        for (int c = 0; c < 26; ++c) {
+            lut->code[(int)alph[c]] = c;
+            lut->code[(int)alph[c] - 'A' + 'a'] = c;
+        }
+    }
+    lut->code[0] = 0xff;   // read separator of the packed layout
+}
+
+PinnedBuf *get_pinned(mtg_ctx *ctx, size_t bytes) {
+    for (auto &b : ctx->pinned) {
+        if (b.busy && cudaEventQuery(b.ev) == cudaSuccess) b.busy = false;
+    }
+    for (auto &b : ctx->pinned)
+        if (!b.busy && b.bytes >= bytes) { b.busy = true; return &b; }
+    for (auto &b : ctx->pinned)
+        if (!b.busy) {   // grow an idle one
+            cudaFreeHost(b.p);
+            b.p = nullptr;
+            MTG_CUDA(cudaMallocHost(&b.p, bytes));
+            b.bytes = bytes;
+            b.busy = true;
+            return &b;
+        }
+    PinnedBuf nb;
+    MTG_CUDA(cudaMallocHost(&nb.p, bytes));
+    nb.bytes = bytes;
+    MTG_CUDA(cudaEventCreateWithFlags(&nb.ev, cudaEventDisableTiming));
+    nb.busy = true;
+    ctx->pinned.push_back(nb);
+    return &ctx->pinned.back();
+}
+
+void pack_range(const char *bases, const uint64_t *offsets, size_t r0, size_t r1, char *dst) {
+    for (size_t r = r0; r < r1; ++r) {
+        size_t len = offsets[r + 1] - offsets[r];
+        memcpy(dst, bases + offsets[r], len);
+        dst[len] = 0;
+        dst += len + 1;
+    }
+}
+
+void pack_parallel(const char *bases, const uint64_t *offsets, size_t r0, size_t r1, char *dst) {
+    size_t bytes = offsets[r1] - offsets[r0] + (r1 - r0);
+    unsigned nt = (unsigned)std::min<size_t>(std::max<size_t>(bytes >> 22, 1),
+                                             std::min(16u, std::max(1u, std::thread::hardware_concurrency())));
+    if (nt <= 1) { pack_range(bases, offsets, r0, r1, dst); return; }
+    std::vector<std::thread> th;
+    size_t per = (r1 - r0 + nt - 1) / nt;
+    for (unsigned t = 0; t < nt; ++t) {
+        size_t a = r0 + t * per, b = std::min(r1, a + per);
+        if (a >= b) break;
+        char *d = dst + (offsets[a] - offsets[r0]) + (a - r0);
+        th.emplace_back(pack_range, bases, offsets, a, b, d);
+    }
+    for (auto &t : th) t.join();
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *mtg_last_error(const mtg_ctx *ctx) {
+    return ctx ? ctx->error.c_str() : g_create_error.c_str();
+}
+
+int mtg_create(const mtg_params *p, mtg_ctx **out) {
+    if (!p || !out) return fail(nullptr, MTG_ERR_BAD_ARG, "null argument");
+    *out = nullptr;
+    if (p->alphabet != MTG_ALPHABET_DNA && p->alphabet != MTG_ALPHABET_PROTEIN)
+        return fail(nullptr, MTG_ERR_BAD_ARG, "unknown alphabet");
+    const uint32_t L1 = p->alphabet == MTG_ALPHABET_DNA ? 2 : 5;
+    const uint32_t L2 = p->alphabet == MTG_ALPHABET_DNA ? 3 : 5;
+    const uint32_t sigma = p->alphabet == MTG_ALPHABET_DNA ? 5 : 27;
+    // boss_chunk_construct.cpp:1057-1062
+    if (p->k < 1 || p->k > 256 / L2 - 1)
+        return fail(nullptr, MTG_ERR_BAD_ARG, "For succinct graph, k must be between 2 and "
+                                               + std::to_string(256 / L2));
+    if (p->bits_per_count > 32)   // :1157-1159
+        return fail(nullptr, MTG_ERR_BAD_ARG, "Error: trying to allocate too many bits per k-mer count");
+    if (p->filter_suffix && p->filter_suffix[0])
+        return fail(nullptr, MTG_ERR_UNSUPPORTED, "suffix-filtered chunks (--suffix) are not on the GPU path yet");
+    if (p->both_strands && p->alphabet != MTG_ALPHABET_DNA)
+        return fail(nullptr, MTG_ERR_BAD_ARG, "canonical mode requires a DNA alphabet");
+    const uint32_t K = p->k + 1;
+    if (K * L1 > 128)
+        return fail(nullptr, MTG_ERR_UNSUPPORTED, "k-mers wider than 128 bits are not supported yet");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(nullptr, MTG_ERR_CUDA, "no CUDA device available (there is no CPU fallback)");
+    }
+    if (p->device < 0 || p->device >= ndev) return fail(nullptr, MTG_ERR_BAD_ARG, "bad device ordinal");
+    mtg_ctx *ctx = new mtg_ctx();
+    try {
+        ctx->prm = *p;
+        ctx->prm.filter_suffix = nullptr;
+        ctx->device = p->device;
+        ctx->al = Alpha{K, L1, sigma, 0};
+        uint32_t hi = 0;
+        for (uint32_t v = 2 * sigma - 1; v > 1; v >>= 1) ++hi;   // sdsl::bits::hi
+        ctx->al.W_width = hi + 1;                                // boss_chunk.cpp:388-390
+        ctx->L2 = L2;
+        ctx->cmax = p->bits_per_count == 0 ? 0xffffffffu
+                    : p->bits_per_count <= 8 ? 0xffu : p->bits_per_count <= 16 ? 0xffffu : 0xffffffffu;
+        build_lut(p->alphabet, &ctx->lut);
+        MTG_CUDA(cudaSetDevice(ctx->device));
+        cudaDeviceProp prop;
+        MTG_CUDA(cudaGetDeviceProperties(&prop, ctx->device));
+        if (prop.major < 10) {
+            delete ctx;
+            return fail(nullptr, MTG_ERR_CUDA, "device is not sm_100 (kernels are built for sm_100a only)");
+        }
+        MTG_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        cudaMemPool_t pool;
+        MTG_CUDA(cudaDeviceGetDefaultMemPool(&pool, ctx->device));
+        uint64_t thr = UINT64_MAX;
+        MTG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
+    } catch (const CudaError &e) {
+        int rc = fail_cuda(nullptr, e);
+        delete ctx;
+        return rc;
+    }
+    *out = ctx;
+    return MTG_OK;
+}
+
+void mtg_destroy(mtg_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    ctx->segs.clear();
+    for (auto &b : ctx->pinned) {
+        if (b.p) cudaFreeHost(b.p);
+        if (b.ev) cudaEventDestroy(b.ev);
+    }
+    if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+    delete ctx;
+}
+
+size_t mtg_packed_size(const uint64_t *offsets, size_t n_reads) {
+    size_t b = (size_t)(offsets[n_reads] - offsets[0]) + n_reads;
+    return (b + 15) & ~(size_t)15;
+}
+
+void mtg_pack_reads(const char *bases, const uint64_t *offsets, size_t n_reads, char *dst) {
+    size_t raw = (size_t)(offsets[n_reads] - offsets[0]) + n_reads;
+    pack_parallel(bases, offsets, 0, n_reads, dst);
+    memset(dst + raw, 0, mtg_packed_size(offsets, n_reads) - raw);
+}
+
+int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, const uint64_t *counts,
+                   size_t n_reads) {
+    if (!ctx || (!bases && n_reads) || !offsets) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+    if (n_reads == 0) return MTG_OK;
+    const uint32_t K = ctx->al.K;
+    try {
+        MTG_CUDA(cudaSetDevice(ctx->device));
+        // split very large pushes so that packing and H2D overlap
+        const size_t CHUNK = (size_t)64 << 20;
+        size_t r0 = 0;
+        while (r0 < n_reads) {
+            size_t r1 = r0;
+            size_t bytes = 0;
+            uint64_t nwin = 0;
+            while (r1 < n_reads && (bytes < CHUNK)) {
+                size_t len = offsets[r1 + 1] - offsets[r1];
+                bytes += len + 1;
+                if (len >= K) nwin += len - K + 1;
+                ++r1;
+            }
+            size_t padded = (bytes + 15) & ~(size_t)15;
+            const bool want_starts = ctx->prm.bits_per_count > 0;
+            size_t nr = r1 - r0;
+            size_t stage_bytes = padded + (want_starts ? nr * 8 + 16 : 0) + (counts ? nr * 4 + 16 : 0);
+            PinnedBuf *pb;
+            ReadSegment seg;
+            {
+                std::lock_guard<std::mutex> lk(ctx->mu);
+                pb = get_pinned(ctx, stage_bytes);
+            }
+            char *h = (char *)pb->p;
+            pack_parallel(bases, offsets, r0, r1, h);
+            memset(h + bytes, 0, padded - bytes);
+            uint64_t *h_starts = (uint64_t *)(h + padded);
+            uint32_t *h_counts = (uint32_t *)(h + padded + (want_starts ? nr * 8 + 16 : 0));
+            if (want_starts) {
+                uint64_t pos = 0;
+                for (size_t r = r0; r < r1; ++r) {
+                    h_starts[r - r0] = pos;
+                    pos += offsets[r + 1] - offsets[r] + 1;
+                }
+            }
+            if (counts)
+                for (size_t r = r0; r < r1; ++r)   // kmer_collector.cpp:92
+                    h_counts[r - r0] = (uint32_t)std::min<uint64_t>(counts[r], ctx->cmax);
+            {
+                std::lock_guard<std::mutex> lk(ctx->mu);
+                seg.own_packed.alloc(padded, ctx->stream);
+                MTG_CUDA(cudaMemcpyAsync(seg.own_packed.p, h, padded, cudaMemcpyHostToDevice, ctx->stream));
+                if (want_starts) {
+                    seg.starts.alloc(nr * 8, ctx->stream);
+                    MTG_CUDA(cudaMemcpyAsync(seg.starts.p, h_starts, nr * 8, cudaMemcpyHostToDevice, ctx->stream));
+                    seg.has_starts = true;
+                }
+                if (counts) {
+                    seg.counts.alloc(nr * 4, ctx->stream);
+                    MTG_CUDA(cudaMemcpyAsync(seg.counts.p, h_counts, nr * 4, cudaMemcpyHostToDevice, ctx->stream));
+                    seg.has_counts = true;
+                    ctx->any_explicit_counts = true;
+                }
+                MTG_CUDA(cudaEventRecord(pb->ev, ctx->stream));
+                seg.d_packed = seg.own_packed.as<uint8_t>();
+                seg.nbytes = padded;
+                seg.n_windows_max = nwin;
+                seg.n_reads = nr;
+                ctx->segs.push_back(std::move(seg));
+            }
+            r0 = r1;
+        }
+    } catch (const CudaError &e) {
+        return fail_cuda(ctx, e);
+    }
+    return MTG_OK;
+}
+
+int mtg_push_packed_device(mtg_ctx *ctx, const void *d_packed, size_t n_bytes, uint64_t n_windows_max) {
+    if (!ctx || !d_packed) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+    if (((uintptr_t)d_packed & 15) != 0) return fail(ctx, MTG_ERR_BAD_ARG, "packed reads must be 16-byte aligned");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    ReadSegment seg;
+    seg.d_packed = (const uint8_t *)d_packed;
+    seg.nbytes = n_bytes;
+    seg.n_windows_max = n_windows_max;
+    ctx->segs.push_back(std::move(seg));
+    return MTG_OK;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Pipeline driver
+// ---------------------------------------------------------------------------
+namespace {
+
+struct Timer {
+    cudaEvent_t ev[8];
+    int n = 0;
+    cudaStream_t s;
+    explicit Timer(cudaStream_t st) : s(st) {
+        for (auto &e : ev) cudaEventCreate(&e);
+    }
+    ~Timer() { for (auto &e : ev) cudaEventDestroy(e); }
+    void mark() { cudaEventRecord(ev[n++], s); }
+    float ms(int a, int b) { float t = 0; cudaEventElapsedTime(&t, ev[a], ev[b]); return t; }
+};
+
+unsigned long long read_counter(const unsigned long long *d, cudaStream_t s) {
+    unsigned long long h = 0;
+    MTG_CUDA(cudaMemcpyAsync(&h, d, sizeof(h), cudaMemcpyDeviceToHost, s));
+    MTG_CUDA(cudaStreamSynchronize(s));
+    return h;
+}
+
+struct RealSet {   // sorted distinct real k-mers (both strands in canonical mode)
+    DevBuf keys, counts;
+    uint64_t m = 0, n_input = 0;
+};
+
+template <typename KeyT>
+void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const SortPlan &plan,
+               cudaStream_t s, unsigned *launches) {
+    // sorts; on return `a` (and *va) hold the sorted data
+    SortWorkspace ws;
+    DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
+    DevBuf hist(sizeof(unsigned long long) * MAX_SORT_PASSES * RADIX, s);
+    DevBuf ctr(sizeof(unsigned int) * MAX_SORT_PASSES, s);
+    ws.status = status.as<unsigned long long>();
+    ws.hist = hist.as<unsigned long long>();
+    ws.tile_counters = ctr.as<unsigned int>();
+    KeyT *keys[2] = {a.as<KeyT>(), b.as<KeyT>()};
+    uint32_t *vals[2] = {va ? va->as<uint32_t>() : nullptr, vb ? vb->as<uint32_t>() : nullptr};
+    int cur = radix_sort<KeyT>(keys, va ? vals : nullptr, n, plan, ws, s, launches);
+    if (cur == 1) {
+        std::swap(a, b);
+        if (va) std::swap(*va, *vb);
+    }
+}
+
+// extraction + sort + unique/count (+ rc completion): KmerCollector::data()
+// (kmer_collector.hpp:94) followed by add_reverse_complements.
+template <typename KeyT>
+void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    const bool payload = counting && ctx->any_explicit_counts;
+    uint64_t n_ub = 0;
+    for (auto &seg : ctx->segs) n_ub += seg.n_windows_max;
+
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();   // [0] extract, [1] unique, [2] rc
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
+    DevBuf keysA(sizeof(KeyT) * n_ub, s), keysB(sizeof(KeyT) * n_ub, s);
+    DevBuf valsA, valsB;
+    if (payload) { valsA.alloc(4 * n_ub, s); valsB.alloc(4 * n_ub, s); }
+
+    if (tm) tm->mark();
+    std::vector<DevBuf> ones;
+    for (auto &seg : ctx->segs) {
+        ExtractArgs a;
+        a.packed = seg.d_packed;
+        a.nbytes = seg.nbytes;
+        a.lut = &ctx->lut;
+        a.K = al.K;
+        a.L = al.L;
+        a.canonical = ctx->prm.both_strands != 0;
+        a.out_counts = payload ? valsA.as<uint32_t>() : nullptr;
+        a.out_counter = d_ctr;
+        a.read_starts = nullptr;
+        a.read_counts = nullptr;
+        a.n_reads = 0;
+        if (payload) {
+            if (!seg.has_starts) throw CudaError{cudaErrorInvalidValue, "device-packed reads cannot be mixed with explicit counts", 0};
+            a.read_starts = seg.starts.as<uint64_t>();
+            a.n_reads = seg.n_reads;
+            if (seg.has_counts) {
+                a.read_counts = seg.counts.as<uint32_t>();
+            } else {
+                ones.emplace_back(4 * seg.n_reads, s);
+                fill_u32(ones.back().as<uint32_t>(), 1, seg.n_reads, s, &ctx->launches);
+                a.read_counts = ones.back().as<uint32_t>();
+            }
+        }
+        extract_kmers<KeyT>(a, keysA.as<KeyT>(), s);
+        ctx->launches += 1;
+    }
+    const uint64_t n = read_counter(d_ctr, s);
+    rs->n_input = n;
+    ones.clear();
+    if (tm) tm->mark();
+
+    SortPlan plan;
+    plan.n = 0;
+    plan_add_key_bits(plan, 0, al.K * al.L);
+    sort_keys<KeyT>(keysA, keysB, payload ? &valsA : nullptr, payload ? &valsB : nullptr, n, plan, s,
+                    &ctx->launches);
+    if (tm) tm->mark();
+
+    // unique: keysA (sorted) -> keysB
+    DevBuf starts;
+    if (counting) starts.alloc(8 * (n + 1), s);
+    {
+        DevBuf status(sizeof(unsigned long long) * unique_status_words(n), s);
+        DevBuf tctr(sizeof(unsigned int), s);
+        unique_keys<KeyT>(keysA.as<KeyT>(), n, keysB.as<KeyT>(), counting ? starts.as<uint64_t>() : nullptr,
+                          d_ctr + 1, status.as<unsigned long long>(), tctr.as<unsigned int>(), s,
+                          &ctx->launches);
+    }
+    const uint64_t m = read_counter(d_ctr + 1, s);
+    keysA.release();
+    const bool canon = ctx->prm.both_strands != 0;
+    const uint64_t cap = canon ? 2 * m : m;
+    DevBuf counts;
+    if (counting) {
+        counts.alloc(4 * cap, s);
+        run_counts(starts.as<uint64_t>(), payload ? valsA.as<uint32_t>() : nullptr, m, ctx->cmax,
+                   counts.as<uint32_t>(), s, &ctx->launches);
+    }
+    starts.release();
+    valsA.release();
+    valsB.release();
+    if (tm) tm->mark();
+
+    if (!canon) {
+        rs->keys = std::move(keysB);
+        rs->counts = std::move(counts);
+        rs->m = m;
+        if (tm) tm->mark();
+        return;
+    }
+    // canonical: append reverse complements, sort the union
+    DevBuf r0(sizeof(KeyT) * cap, s), r1(sizeof(KeyT) * cap, s);
+    MTG_CUDA(cudaMemcpyAsync(r0.p, keysB.p, sizeof(KeyT) * m, cudaMemcpyDeviceToDevice, s));
+    keysB.release();
+    append_reverse_complements<KeyT>(r0.as<KeyT>(), counting ? counts.as<uint32_t>() : nullptr, m, al,
+                                     ctx->cmax, d_ctr + 2, s, &ctx->launches);
+    const uint64_t m2 = m + read_counter(d_ctr + 2, s);
+    DevBuf counts1;
+    if (counting) counts1.alloc(4 * cap, s);
+    sort_keys<KeyT>(r0, r1, counting ? &counts : nullptr, counting ? &counts1 : nullptr, m2, plan, s,
+                    &ctx->launches);
+    rs->keys = std::move(r0);
+    rs->counts = std::move(counts);
+    rs->m = m2;
+    if (tm) tm->mark();
+}
+
+template <typename KeyT>
+void build_impl(mtg_ctx *ctx, mtg_chunk *out) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint32_t K = al.K, L = al.L;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    ctx->launches = 0;
+    Timer tm(s);
+    RealSet rs;
+    collect_reals<KeyT>(ctx, &rs, &tm);   // marks 0..4: start, extract, sort, unique, rc
+    const uint64_t m = rs.m;
+    const KeyT *reals = rs.keys.as<KeyT>();
+
+    // ---- dummy k-mers ----
+    DevBuf ctr(64 + 8 * MTG_MAX_K, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();   // [0] sinks [1] sources-1 [8..] levels
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64 + 8 * MTG_MAX_K, s));
+    uint64_t cap = std::max<uint64_t>(1024, m / 8);
+    DevBuf sink, src, srcB;
+    uint64_t n_sink = 0, d1 = 0;
+    while (true) {
+        sink.alloc(sizeof(KeyT) * cap, s);
+        src.alloc(sizeof(KeyT) * cap, s);
+        find_dummy_candidates<KeyT>(reals, m, al, sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap,
+                                    d_ctr + 1, s, &ctx->launches);
+        n_sink = read_counter(d_ctr, s);
+        d1 = read_counter(d_ctr + 1, s);
+        if (n_sink <= cap && d1 <= cap) break;
+        cap = std::max(n_sink, d1);
+    }
+    // sources-1 in forward-lex order, then all their distinct prefixes
+    srcB.alloc(sizeof(KeyT) * std::max<uint64_t>(d1, 1), s);
+    {
+        SortPlan plan;
+        plan.n = 0;
+        plan_add_key_bits(plan, 0, (K - 1) * L);
+        sort_keys<KeyT>(src, srcB, nullptr, nullptr, d1, plan, s, &ctx->launches);
+    }
+    srcB.release();
+    DevBuf per_entry(4 * std::max<uint64_t>(d1, 1), s), offsets(8 * (d1 + 1), s);
+    source_prefix_counts<KeyT>(src.as<KeyT>(), d1, al, per_entry.as<uint32_t>(), s, &ctx->launches);
+    {
+        DevBuf status(8 * (d1 / 2048 + 2), s), tctr(4, s);
+        exclusive_scan_u32(per_entry.as<uint32_t>(), d1, offsets.as<uint64_t>(),
+                           status.as<unsigned long long>(), tctr.as<unsigned int>(), s, &ctx->launches);
+    }
+    const uint64_t d_src = read_counter(offsets.as<unsigned long long>() + d1, s);
+    const uint64_t d = n_sink + d_src;
+    DevBuf dk0(sizeof(KeyT) * std::max<uint64_t>(d, 1), s), dk1(sizeof(KeyT) * std::max<uint64_t>(d, 1), s);
+    DevBuf di0(4 * std::max<uint64_t>(d, 1), s), di1(4 * std::max<uint64_t>(d, 1), s);
+    MTG_CUDA(cudaMemcpyAsync(dk0.p, sink.p, sizeof(KeyT) * n_sink, cudaMemcpyDeviceToDevice, s));
+    fill_u32(di0.as<uint32_t>(), INFO_W_DOLLAR, n_sink, s, &ctx->launches);
+    generate_source_dummies<KeyT>(src.as<KeyT>(), per_entry.as<uint32_t>(), offsets.as<uint64_t>(), d1, al,
+                                  dk0.as<KeyT>() + n_sink, di0.as<uint32_t>() + n_sink, d_ctr + 8, s,
+                                  &ctx->launches);
+    sink.release(); src.release(); per_entry.release(); offsets.release();
+    // final order: node bits, then more '$' first, then W  (LSD: W, nd, node)
+    flip_info(di0.as<uint32_t>(), d, s, &ctx->launches);
+    {
+        SortPlan plan;
+        plan.n = 0;
+        plan.p[plan.n++] = DigitPass{0, 0, (int)L};
+        plan.p[plan.n++] = DigitPass{1, 0, 7};
+        plan_add_key_bits(plan, L, K * L);
+        sort_keys<KeyT>(dk0, dk1, &di0, &di1, d, plan, s, &ctx->launches);
+    }
+    flip_info(di0.as<uint32_t>(), d, s, &ctx->launches);
+    dk1.release(); di1.release();
+    DevBuf rank(8 * std::max<uint64_t>(d, 1), s);
+    dummy_ranks<KeyT>(reals, m, dk0.as<KeyT>(), d, al, rank.as<uint64_t>(), s, &ctx->launches);
+    tm.mark();   // 5: dummies done
+
+    // ---- merge + emit ----
+    const uint64_t E = m + d + 2;
+    DevBuf row_keys(sizeof(KeyT) * E, s), row_info(E, s), row_counts;
+    if (counting) row_counts.alloc(4 * E, s);
+    merge_rows<KeyT>(reals, counting ? rs.counts.as<uint32_t>() : nullptr, m, dk0.as<KeyT>(),
+                     di0.as<uint32_t>(), rank.as<uint64_t>(), d, al, row_keys.as<KeyT>(),
+                     row_info.as<uint8_t>(), counting ? row_counts.as<uint32_t>() : nullptr, s,
+                     &ctx->launches);
+    rs.keys.release(); rs.counts.release(); dk0.release(); di0.release(); rank.release();
+    const uint32_t ww = ctx->prm.bits_per_count;
+    const size_t tiles = div_up(E, (size_t)2048);
+    const size_t W_words = tiles * 32 * al.W_width, last_words = tiles * 32, wt_words = tiles * 32 * ww;
+    DevBuf outbuf(8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA), s);
+    uint64_t *dW = outbuf.as<uint64_t>(), *dLast = dW + W_words, *dWt = dLast + last_words;
+    unsigned long long *dF = (unsigned long long *)(dWt + wt_words);
+    emit_chunk<KeyT>(row_keys.as<KeyT>(), row_info.as<uint8_t>(),
+                     counting ? row_counts.as<uint32_t>() : nullptr, E, al, ww, dW, dLast,
+                     counting ? dWt : nullptr, dF, s, &ctx->launches);
+    tm.mark();   // 6: emit done
+
+    // ---- results to pinned host memory ----
+    ChunkImpl *impl = new ChunkImpl();
+    size_t hbytes = 8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA + MTG_MAX_K + 16);
+    if (cudaMallocHost(&impl->pinned, hbytes) != cudaSuccess) {
+        delete impl;
+        throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
+    }
+    uint64_t *h = (uint64_t *)impl->pinned;
+    MTG_CUDA(cudaMemcpyAsync(h, dW, 8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA),
+                             cudaMemcpyDeviceToHost, s));
+    uint64_t *h_levels = h + W_words + last_words + wt_words + MTG_MAX_SIGMA;
+    MTG_CUDA(cudaMemcpyAsync(h_levels, d_ctr + 8, 8 * MTG_MAX_K, cudaMemcpyDeviceToHost, s));
+    MTG_CUDA(cudaStreamSynchronize(s));
+
+    memset(out, 0, sizeof(*out));
+    out->n_rows = E;
+    out->sigma = al.sigma;
+    out->k = K - 1;
+    out->W_width = al.W_width;
+    out->weights_width = ww;
+    out->W = h;
+    out->last = h + W_words;
+    out->weights = counting ? h + W_words + last_words : nullptr;
+    const uint64_t *hF = h + W_words + last_words + wt_words;
+    for (uint32_t c = 0; c < al.sigma; ++c) out->F[c] = hF[c];
+    out->n_input_kmers = rs.n_input;
+    out->n_real = m;
+    out->n_dummy_sink = n_sink;
+    for (uint32_t c = 0; c + 1 < K && c < MTG_MAX_K; ++c) out->n_dummy_source[c] = h_levels[c];
+    out->ms_extract = tm.ms(0, 1);
+    out->ms_sort = tm.ms(1, 2);
+    out->ms_unique = tm.ms(2, 3);
+    out->ms_rc = tm.ms(3, 4);
+    out->ms_dummy = tm.ms(4, 5);
+    out->ms_emit = tm.ms(5, 6);
+    out->ms_total = tm.ms(0, 6);
+    out->n_kernel_launches = ctx->launches;
+    out->impl = impl;
+}
+
+void clear_ctx(mtg_ctx *ctx) {
+    ctx->segs.clear();
+    ctx->any_explicit_counts = false;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mtg_build_chunk(mtg_ctx *ctx, mtg_chunk *out) {
+    if (!ctx || !out) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = MTG_OK;
+    try {
+        MTG_CUDA(cudaSetDevice(ctx->device));
+        if (ctx->al.K * ctx->al.L <= 64) build_impl<uint64_t>(ctx, out);
+        else build_impl<u128>(ctx, out);
+    } catch (const CudaError &e) {
+        rc = fail_cuda(ctx, e);
+        cudaStreamSynchronize(ctx->stream);
+    }
+    clear_ctx(ctx);
+    return rc;
+}
+
+void mtg_free_chunk(mtg_chunk *chunk) {
+    if (!chunk || !chunk->impl) return;
+    ChunkImpl *impl = (ChunkImpl *)chunk->impl;
+    if (impl->pinned) cudaFreeHost(impl->pinned);
+    delete impl;
+    chunk->impl = nullptr;
+    chunk->W = chunk->last = chunk->weights = nullptr;
+}
+
+int mtg_debug_sorted_kmers(mtg_ctx *ctx, uint64_t **words, uint32_t **counts, uint64_t *n) {
+    if (!ctx || !words || !n) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    int rc = MTG_OK;
+    try {
+        MTG_CUDA(cudaSetDevice(ctx->device));
+        RealSet rs;
+        const bool wide = ctx->al.K * ctx->al.L > 64;
+        if (wide) collect_reals<u128>(ctx, &rs, nullptr);
+        else collect_reals<uint64_t>(ctx, &rs, nullptr);
+        *n = rs.m;
+        *words = (uint64_t *)malloc(16 * std::max<uint64_t>(rs.m, 1));
+        if (wide) {
+            MTG_CUDA(cudaMemcpyAsync(*words, rs.keys.p, 16 * rs.m, cudaMemcpyDeviceToHost, ctx->stream));
+            MTG_CUDA(cudaStreamSynchronize(ctx->stream));
+        } else {
+            std::vector<uint64_t> tmp(rs.m);
+            MTG_CUDA(cudaMemcpyAsync(tmp.data(), rs.keys.p, 8 * rs.m, cudaMemcpyDeviceToHost, ctx->stream));
+            MTG_CUDA(cudaStreamSynchronize(ctx->stream));
+            for (uint64_t i = 0; i < rs.m; ++i) { (*words)[2 * i] = tmp[i]; (*words)[2 * i + 1] = 0; }
+        }
+        if (counts) {
+            *counts = nullptr;
+            if (ctx->prm.bits_per_count) {
+                *counts = (uint32_t *)malloc(4 * std::max<uint64_t>(rs.m, 1));
+                MTG_CUDA(cudaMemcpyAsync(*counts, rs.counts.p, 4 * rs.m, cudaMemcpyDeviceToHost, ctx->stream));
+                MTG_CUDA(cudaStreamSynchronize(ctx->stream));
+            }
+        }
+    } catch (const CudaError &e) {
+        rc = fail_cuda(ctx, e);
+    }
+    clear_ctx(ctx);
+    return rc;
+}
+
+void mtg_debug_free(void *p) { free(p); }
+
+static int debug_sort(int device, void *keys, uint32_t *vals, uint64_t n, uint32_t key_bits, bool wide) {
+    try {
+        MTG_CUDA(cudaSetDevice(device));
+        cudaStream_t s;
+        MTG_CUDA(cudaStreamCreate(&s));
+        {
+            size_t kb = wide ? 16 : 8;
+            DevBuf a(kb * n, s), b(kb * n, s), va, vb;
+            MTG_CUDA(cudaMemcpyAsync(a.p, keys, kb * n, cudaMemcpyHostToDevice, s));
+            if (vals) {
+                va.alloc(4 * n, s); vb.alloc(4 * n, s);
+                MTG_CUDA(cudaMemcpyAsync(va.p, vals, 4 * n, cudaMemcpyHostToDevice, s));
+            }
+            SortPlan plan;
+            plan.n = 0;
+            plan_add_key_bits(plan, 0, key_bits);
+            unsigned launches = 0;
+            if (wide) sort_keys<u128>(a, b, vals ? &va : nullptr, vals ? &vb : nullptr, n, plan, s, &launches);
+            else sort_keys<uint64_t>(a, b, vals ? &va : nullptr, vals ? &vb : nullptr, n, plan, s, &launches);
+            MTG_CUDA(cudaMemcpyAsync(keys, a.p, kb * n, cudaMemcpyDeviceToHost, s));
+            if (vals) MTG_CUDA(cudaMemcpyAsync(vals, va.p, 4 * n, cudaMemcpyDeviceToHost, s));
+            MTG_CUDA(cudaStreamSynchronize(s));
+        }
+        cudaStreamSynchronize(s);
+        cudaStreamDestroy(s);
+    } catch (const CudaError &e) {
+        return fail_cuda(nullptr, e);
+    }
+    return MTG_OK;
+}
+
+int mtg_debug_sort_u64(int device, uint64_t *keys, uint32_t *vals, uint64_t n, uint32_t key_bits) {
+    return debug_sort(device, keys, vals, n, key_bits, false);
+}
+int mtg_debug_sort_u128(int device, uint64_t *keys, uint32_t *vals, uint64_t n, uint32_t key_bits) {
+    return debug_sort(device, keys, vals, n, key_bits, true);
+}
+
+}  // extern "C"

@@ -1,0 +1,294 @@
+// K4: dummy sink / source k-mer recovery, K5: merge of real and dummy rows.
+// Set-level restatement of the reference's serial merge-join loops:
+//   add_dummy_sink_kmers   (boss_chunk_construct.cpp:54-98)
+//   add_dummy_source_kmers (boss_chunk_construct.cpp:123-168)
+//   dummy-prefix loop      (boss_chunk_construct.cpp:280-306)
+//   merge real + dummy     (boss_chunk_construct.cpp:308-348)
+// With T = {target nodes x[2..K]} and S = {source nodes x[1..K-1]} of the real k-mers:
+//   sinks      = T \ S  (as k-mers  t$)
+//   sources-1  = S \ T  (as k-mers  $ n[1..K-2] -> n[K-1])
+//   sources-c  = distinct prefixes of the sources-1 nodes, '$'-padded (c = 2..K-1).
+// Membership tests are binary searches in the sorted real array (probes are
+// sorted per leading character, so neighbouring threads walk the same cache lines).
+#include "mtg_scan.cuh"
+#include "mtg_stages.cuh"
+
+namespace mtg {
+
+namespace {
+
+template <typename KeyT>
+__device__ __forceinline__ uint64_t lower_bound_dev(const KeyT *a, uint64_t n, KeyT x) {
+    uint64_t lo = 0, hi = n;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) >> 1;
+        if (w_lt(a[mid], x)) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// append one element per emitting lane through a warp-aggregated atomic
+template <typename KeyT>
+__device__ __forceinline__ void warp_append(bool emit, KeyT v, KeyT *out, uint64_t cap,
+                                            unsigned long long *counter) {
+    unsigned bal = __ballot_sync(0xffffffffu, emit);
+    if (bal == 0) return;
+    unsigned long long base = 0;
+    if ((threadIdx.x & 31) == 0) base = atomicAdd(counter, (unsigned long long)__popc(bal));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (emit) {
+        uint64_t dst = base + __popc(bal & lanemask_lt());
+        if (dst < cap) out[dst] = v;
+    }
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+dummy_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al,
+                        KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink,
+                        KeyT *src_fwd, uint64_t src_cap, unsigned long long *d_num_src) {
+    using WT = WordTraits<KeyT>;
+    const uint32_t L = al.L, K = al.K;
+    const KeyT maskL = WT::low_mask(L);
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool emit_sink = false, emit_src = false;
+    KeyT sink = WT::zero(), fwd = WT::zero();
+    if (i < m) {
+        KeyT x = reals[i];
+        KeyT W = w_and(x, maskL);
+        // ---- sink: first element of its (x >> 2L, W) class? ----
+        KeyT grp = w_shr(x, 2 * L);
+        bool first = true;
+        for (uint64_t j = i; j-- > 0;) {
+            KeyT y = reals[j];
+            if (!w_eq(w_shr(y, 2 * L), grp)) break;
+            if (w_eq(w_and(y, maskL), W)) { first = false; break; }
+        }
+        if (first) {
+            // to_next(K, 0): [s_K, s_{K-1}..s_2 | 0]
+            sink = w_and(w_or(w_shr(x, L), w_shl(W, L * (K - 1))), w_not(maskL));
+            uint64_t p = lower_bound_dev(reals, m, sink);
+            emit_sink = !(p < m && w_eq(w_shr(reals[p], L), w_shr(sink, L)));
+        }
+        // ---- source-1: first k-mer of its node? ----
+        KeyT node = w_shr(x, L);
+        bool node_head = i == 0 || !w_eq(w_shr(reals[i - 1], L), node);
+        if (node_head) {
+            // to_prev(K, 0): [s_{K-2}..s_1, 0 | s_{K-1}]; group prefix = s_{K-2}..s_1
+            KeyT top = w_shr(x, L * (K - 1));   // s_{K-1}
+            KeyT prev = w_and(w_shl(w_and(x, w_not(maskL)), L), WT::low_mask(L * K));
+            KeyT g = w_shr(prev, 2 * L);
+            uint64_t p = lower_bound_dev(reals, m, prev);   // prev has W = 0, x_1 = 0
+            bool redundant = false;
+            for (; p < m; ++p) {
+                KeyT y = reals[p];
+                if (!w_eq(w_shr(y, 2 * L), g)) break;
+                if (w_eq(w_and(y, maskL), top)) { redundant = true; break; }
+            }
+            if (!redundant) {
+                emit_src = true;
+                // forward-lex packing of the node: s_1 most significant
+                for (uint32_t c = 1; c < K; ++c) {
+                    KeyT ch = w_and(w_shr(x, L * c), maskL);
+                    fwd = w_or(fwd, w_shl(ch, L * (K - 1 - c)));
+                }
+            }
+        }
+    }
+    warp_append(emit_sink, sink, sink_keys, sink_cap, d_num_sink);
+    warp_append(emit_src, fwd, src_fwd, src_cap, d_num_src);
+}
+
+template <typename KeyT>
+__device__ __forceinline__ int w_clz(KeyT x);
+template <> __device__ __forceinline__ int w_clz<uint64_t>(uint64_t x) { return __clzll(x); }
+template <> __device__ __forceinline__ int w_clz<u128>(u128 x) {
+    return x.hi ? __clzll(x.hi) : 64 + __clzll(x.lo);
+}
+
+template <typename KeyT>
+__global__ void source_prefix_counts_kernel(const KeyT *__restrict__ fwd, uint64_t d1, Alpha al,
+                                            uint32_t *__restrict__ per_entry) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= d1) return;
+    const uint32_t nchars = al.K - 1, bits = nchars * al.L;
+    uint32_t lcp = 0;
+    if (i > 0) {
+        KeyT d = w_xor(fwd[i], fwd[i - 1]);
+        bool same = w_eq(d, WordTraits<KeyT>::zero());
+        if (same) lcp = nchars;   // cannot happen for distinct nodes
+        else {
+            int lead = w_clz<KeyT>(d) - (WordTraits<KeyT>::BITS - (int)bits);   // equal leading bits
+            lcp = (uint32_t)lead / al.L;
+        }
+    }
+    per_entry[i] = nchars - lcp;
+}
+
+// Node i contributes prefixes of length j = lcp+1 .. K-1, i.e. dummy sources with
+// c = K - j leading '$': tight word has x_{c+t} = s_t (t = 1..j-1) and W = s_j.
+template <typename KeyT>
+__global__ void generate_source_dummies_kernel(const KeyT *__restrict__ fwd,
+                                               const uint32_t *__restrict__ per_entry,
+                                               const uint64_t *__restrict__ offsets, uint64_t d1,
+                                               Alpha al, KeyT *__restrict__ out_keys,
+                                               uint32_t *__restrict__ out_info,
+                                               unsigned long long *level_hist) {
+    using WT = WordTraits<KeyT>;
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= d1) return;
+    const uint32_t L = al.L, K = al.K, nchars = K - 1;
+    const KeyT maskL = WT::low_mask(L);
+    KeyT f = fwd[i];
+    uint32_t cnt = per_entry[i];
+    uint64_t dst = offsets[i];
+    // char s_t (t = 1..K-1) sits at bit L*(nchars - t) of f
+    for (uint32_t j = nchars - cnt + 1; j <= nchars; ++j) {
+        uint32_t c = K - j;
+        KeyT key = w_and(w_shr(f, L * (nchars - j)), maskL);   // W = s_j
+        for (uint32_t t = 1; t < j; ++t) {
+            KeyT ch = w_and(w_shr(f, L * (nchars - t)), maskL);
+            key = w_or(key, w_shl(ch, L * (c + t)));
+        }
+        out_keys[dst] = key;
+        out_info[dst] = c;
+        ++dst;
+        atomicAdd(&level_hist[c - 1], 1ull);
+    }
+}
+
+template <typename KeyT>
+__global__ void dummy_ranks_kernel(const KeyT *__restrict__ reals, uint64_t m,
+                                   const KeyT *__restrict__ dummy_keys, uint64_t d, Alpha al,
+                                   uint64_t *__restrict__ rank) {
+    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= d) return;
+    // '$' sorts before every real character: the dummy precedes all reals that agree
+    // with it on the non-'$' leading characters -> lower bound of the zero-filled word
+    KeyT probe = w_and(dummy_keys[j], w_not(WordTraits<KeyT>::low_mask(al.L)));
+    rank[j] = lower_bound_dev(reals, m, probe);
+}
+
+template <typename KeyT>
+__global__ void merge_dummies_kernel(const KeyT *__restrict__ dummy_keys,
+                                     const uint32_t *__restrict__ dummy_info,
+                                     const uint64_t *__restrict__ rank, uint64_t d, uint32_t K,
+                                     KeyT *__restrict__ row_keys, uint8_t *__restrict__ row_info,
+                                     uint32_t *__restrict__ row_counts) {
+    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j == 0) {
+        // row 0: placeholder; row 1: the all-'$' k-mer (boss_chunk_construct.cpp:310-315)
+        row_keys[0] = WordTraits<KeyT>::zero();
+        row_keys[1] = WordTraits<KeyT>::zero();
+        row_info[0] = (uint8_t)((K - 1) | INFO_W_DOLLAR);
+        row_info[1] = (uint8_t)((K - 1) | INFO_W_DOLLAR);
+        if (row_counts) { row_counts[0] = 0; row_counts[1] = 0; }
+    }
+    if (j >= d) return;
+    uint64_t pos = rank[j] + j + 2;
+    row_keys[pos] = dummy_keys[j];
+    row_info[pos] = (uint8_t)dummy_info[j];
+    if (row_counts) row_counts[pos] = 0;
+}
+
+template <typename KeyT>
+__global__ void merge_reals_kernel(const KeyT *__restrict__ reals,
+                                   const uint32_t *__restrict__ real_counts, uint64_t m,
+                                   const uint64_t *__restrict__ rank, uint64_t d,
+                                   KeyT *__restrict__ row_keys, uint8_t *__restrict__ row_info,
+                                   uint32_t *__restrict__ row_counts) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    // number of dummies ordered before real i = #{j : rank[j] <= i}
+    uint64_t lo = 0, hi = d;
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) >> 1;
+        if (rank[mid] <= i) lo = mid + 1; else hi = mid;
+    }
+    uint64_t pos = i + lo + 2;
+    row_keys[pos] = reals[i];
+    row_info[pos] = 0;
+    if (row_counts) row_counts[pos] = real_counts[i];
+}
+
+}  // namespace
+
+template <typename KeyT>
+void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, KeyT *sink_keys, uint64_t sink_cap,
+                           unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
+                           unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches) {
+    MTG_CUDA(cudaMemsetAsync(d_num_sink, 0, sizeof(unsigned long long), stream));
+    MTG_CUDA(cudaMemsetAsync(d_num_src, 0, sizeof(unsigned long long), stream));
+    if (m == 0) return;
+    dummy_candidates_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(
+        reals, m, al, sink_keys, sink_cap, d_num_sink, src_fwd, src_cap, d_num_src);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+template <typename KeyT>
+void source_prefix_counts(const KeyT *src_fwd, uint64_t d1, Alpha al, uint32_t *per_entry,
+                          cudaStream_t stream, unsigned *launches) {
+    if (d1 == 0) return;
+    source_prefix_counts_kernel<KeyT><<<(unsigned)div_up(d1, (size_t)256), 256, 0, stream>>>(
+        src_fwd, d1, al, per_entry);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+template <typename KeyT>
+void generate_source_dummies(const KeyT *src_fwd, const uint32_t *per_entry, const uint64_t *offsets,
+                             uint64_t d1, Alpha al, KeyT *out_keys, uint32_t *out_info,
+                             unsigned long long *level_hist, cudaStream_t stream,
+                             unsigned *launches) {
+    if (d1 == 0) return;
+    generate_source_dummies_kernel<KeyT><<<(unsigned)div_up(d1, (size_t)128), 128, 0, stream>>>(
+        src_fwd, per_entry, offsets, d1, al, out_keys, out_info, level_hist);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+template <typename KeyT>
+void dummy_ranks(const KeyT *reals, uint64_t m, const KeyT *dummy_keys, uint64_t d, Alpha al,
+                 uint64_t *rank, cudaStream_t stream, unsigned *launches) {
+    if (d == 0) return;
+    dummy_ranks_kernel<KeyT><<<(unsigned)div_up(d, (size_t)256), 256, 0, stream>>>(reals, m, dummy_keys,
+                                                                                 d, al, rank);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+template <typename KeyT>
+void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, const KeyT *dummy_keys,
+                const uint32_t *dummy_info, const uint64_t *rank, uint64_t d, Alpha al,
+                KeyT *row_keys, uint8_t *row_info, uint32_t *row_counts, cudaStream_t stream,
+                unsigned *launches) {
+    merge_dummies_kernel<KeyT><<<(unsigned)div_up(d ? d : 1, (size_t)256), 256, 0, stream>>>(
+        dummy_keys, dummy_info, rank, d, al.K, row_keys, row_info, row_counts);
+    *launches += 1;
+    if (m) {
+        merge_reals_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(
+            reals, real_counts, m, rank, d, row_keys, row_info, row_counts);
+        *launches += 1;
+    }
+    MTG_CUDA(cudaGetLastError());
+}
+
+#define INSTANTIATE(KeyT)                                                                          \
+    template void find_dummy_candidates<KeyT>(const KeyT *, uint64_t, Alpha, KeyT *, uint64_t,     \
+                                              unsigned long long *, KeyT *, uint64_t,              \
+                                              unsigned long long *, cudaStream_t, unsigned *);     \
+    template void source_prefix_counts<KeyT>(const KeyT *, uint64_t, Alpha, uint32_t *,            \
+                                             cudaStream_t, unsigned *);                            \
+    template void generate_source_dummies<KeyT>(const KeyT *, const uint32_t *, const uint64_t *,  \
+                                                uint64_t, Alpha, KeyT *, uint32_t *,               \
+                                                unsigned long long *, cudaStream_t, unsigned *);   \
+    template void dummy_ranks<KeyT>(const KeyT *, uint64_t, const KeyT *, uint64_t, Alpha,         \
+                                    uint64_t *, cudaStream_t, unsigned *);                         \
+    template void merge_rows<KeyT>(const KeyT *, const uint32_t *, uint64_t, const KeyT *,         \
+                                   const uint32_t *, const uint64_t *, uint64_t, Alpha, KeyT *,    \
+                                   uint8_t *, uint32_t *, cudaStream_t, unsigned *);
+INSTANTIATE(uint64_t)
+INSTANTIATE(u128)
+
+}  // namespace mtg

@@ -1,0 +1,218 @@
+// K1: reads -> packed (k+1)-mers in KMerBOSS layout, tight alphabet.
+// Replaces KmerExtractorT<L>::sequence_to_kmers (kmer/kmer_extractor.cpp:472-507),
+// ::sequence_to_kmers slide variants (:87-108, :166-196), KMerBOSS ctor/to_next/
+// to_prev (kmer/kmer_boss.hpp:123-186) and utils::drag_and_mark_segments
+// (common/algorithms.hpp:50-67) for the default (no --suffix) build.
+//
+// Layout: reads are packed back to back with one 0x00 separator after each read.
+// A block stages TILE_CHARS (+halo) characters: every thread encodes 64 chars
+// (4 x 128-bit loads) through the alphabet LUT into an L-bit little-endian bit
+// stream in shared memory plus an "invalid character" bitmap. A window starting
+// at char p is then just bits [L*p, L*(p+K)) of the stream: v = sum s_i << L(i-1).
+// The KMerBOSS word is the rotation  ((v << L) & mask) | (v >> L(K-1))
+// (kmer_boss.hpp:17-28) -- no rolling state, no redundant work per window.
+// Canonical mode (DNA, complement = code ^ 3): rc(v) = reverse 2-bit groups of ~v.
+#include "mtg_stages.cuh"
+
+namespace mtg {
+
+namespace {
+
+constexpr int EX_THREADS = 256;
+constexpr int EX_GROUP = 64;                       // chars encoded per thread
+constexpr int EX_TILE = EX_THREADS * EX_GROUP;     // windows per block
+constexpr int EX_WARPS = EX_THREADS / 32;
+constexpr int EX_WPW = EX_TILE / EX_WARPS;         // windows per warp
+
+// extract nb (<=64) bits at bit offset `off` of a little-endian u32 stream
+__device__ __forceinline__ uint64_t stream_bits64(const uint32_t *w, uint32_t off) {
+    uint32_t q = off >> 5, s = off & 31;
+    uint32_t w0 = w[q], w1 = w[q + 1], w2 = w[q + 2];
+    uint32_t lo = __funnelshift_r(w0, w1, s);
+    uint32_t hi = __funnelshift_r(w1, w2, s);
+    return ((uint64_t)hi << 32) | lo;
+}
+
+template <typename KeyT> struct Win;
+template <> struct Win<uint64_t> {
+    __device__ static __forceinline__ uint64_t load(const uint32_t *w, uint32_t off, unsigned nbits) {
+        return stream_bits64(w, off) & WordTraits<uint64_t>::low_mask(nbits);
+    }
+};
+template <> struct Win<u128> {
+    __device__ static __forceinline__ u128 load(const uint32_t *w, uint32_t off, unsigned nbits) {
+        u128 r = make_u128(stream_bits64(w, off), stream_bits64(w, off + 64));
+        return w_and(r, WordTraits<u128>::low_mask(nbits));
+    }
+};
+
+// reverse the order of the 2-bit groups of a word
+__device__ __forceinline__ uint64_t rev2(uint64_t x) {
+    x = __brevll(x);
+    return ((x >> 1) & 0x5555555555555555ull) | ((x & 0x5555555555555555ull) << 1);
+}
+__device__ __forceinline__ u128 rev2(u128 x) { return make_u128(rev2(x.hi), rev2(x.lo)); }
+
+template <typename KeyT>
+__device__ __forceinline__ KeyT boss_rotate(KeyT v, unsigned L, unsigned K) {
+    // v = sum_{i=1..K} s_i << L(i-1)  ->  sum_{i<K} s_i << L*i | s_K
+    KeyT hi = w_and(w_shl(v, L), WordTraits<KeyT>::low_mask(L * K));
+    return w_or(hi, w_shr(v, L * (K - 1)));
+}
+
+template <typename KeyT, int L, bool CANON, bool HAS_COUNT>
+__global__ void __launch_bounds__(EX_THREADS)
+extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut lut, uint32_t K,
+               KeyT *__restrict__ out_keys, uint32_t *__restrict__ out_counts,
+               unsigned long long *__restrict__ out_counter,
+               const uint64_t *__restrict__ read_starts, const uint32_t *__restrict__ read_counts,
+               uint64_t n_reads) {
+    constexpr int GW = 2 * L;                      // u32 words per 64-char group
+    extern __shared__ __align__(16) uint32_t ex_smem[];
+    const uint32_t halo_groups = (K - 1 + EX_GROUP - 1) / EX_GROUP;
+    const uint32_t ngroups = EX_THREADS + halo_groups;
+    uint32_t *codes = ex_smem;                         // [(ngroups) * GW + 4]
+    uint32_t *inval = codes + ngroups * GW + 4;        // [(ngroups) * 2 + 4]
+    __shared__ uint8_t sh_lut[256];
+    sh_lut[threadIdx.x] = lut.code[threadIdx.x];
+    __syncthreads();
+
+    const uint64_t tile_start = (uint64_t)blockIdx.x * EX_TILE;
+    // ---- stage + encode ----
+    for (uint32_t g = threadIdx.x; g < ngroups + 1; g += EX_THREADS) {
+        if (g == ngroups) {   // zero the slack words read by the funnel shifts
+            for (int i = 0; i < 4; ++i) { codes[ngroups * GW + i] = 0; inval[ngroups * 2 + i] = ~0u; }
+            break;
+        }
+        uint64_t gpos = tile_start + (uint64_t)g * EX_GROUP;
+        uint64_t acc = 0;
+        int nb = 0, wi = 0;
+        uint32_t bad[2] = {0, 0};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            uint4 raw = make_uint4(0, 0, 0, 0);
+            uint64_t pos = gpos + q * 16;
+            if (pos + 16 <= nbytes) {
+                raw = *reinterpret_cast<const uint4 *>(packed + pos);
+            } else if (pos < nbytes) {
+                uint8_t tmp[16];
+                for (int i = 0; i < 16; ++i) tmp[i] = pos + i < nbytes ? packed[pos + i] : 0;
+                raw = *reinterpret_cast<uint4 *>(tmp);
+            }
+            uint32_t rw[4] = {raw.x, raw.y, raw.z, raw.w};
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                uint32_t c = (rw[i >> 2] >> ((i & 3) * 8)) & 0xff;
+                uint32_t code = sh_lut[c];
+                if (code == 0xff) { bad[q >> 1] |= 1u << ((q & 1) * 16 + i); code = 0; }
+                acc |= (uint64_t)code << nb;
+                nb += L;
+                if (nb >= 32) {
+                    codes[g * GW + wi++] = (uint32_t)acc;
+                    acc >>= 32;
+                    nb -= 32;
+                }
+            }
+        }
+        inval[g * 2] = bad[0];
+        inval[g * 2 + 1] = bad[1];
+    }
+    __syncthreads();
+
+    // ---- windows: each warp owns EX_WPW consecutive window starts ----
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t wbase = warp * EX_WPW;
+    uint64_t myvalid = 0;
+    uint32_t total = 0;
+#pragma unroll 4
+    for (int it = 0; it < EX_WPW / 32; ++it) {
+        uint32_t p = wbase + it * 32 + lane;
+        uint32_t q = p >> 5, s = p & 31;
+        int remaining = (int)K;
+        int take = 32 - (int)s < remaining ? 32 - (int)s : remaining;
+        uint32_t m = take >= 32 ? ~0u : ((1u << take) - 1);
+        bool bad = ((inval[q] >> s) & m) != 0;
+        remaining -= take;
+        while (remaining > 0) {
+            ++q;
+            take = remaining < 32 ? remaining : 32;
+            m = take >= 32 ? ~0u : ((1u << take) - 1);
+            bad |= (inval[q] & m) != 0;
+            remaining -= take;
+        }
+        if (!bad) myvalid |= 1ull << it;
+        total += __popc(__ballot_sync(0xffffffffu, !bad));
+    }
+    if (total == 0) return;
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd(out_counter, (unsigned long long)total);
+    base = __shfl_sync(0xffffffffu, base, 0);
+
+    const unsigned KL = K * L;
+    for (int it = 0; it < EX_WPW / 32; ++it) {
+        bool ok = (myvalid >> it) & 1;
+        unsigned bal = __ballot_sync(0xffffffffu, ok);
+        if (ok) {
+            uint32_t p = wbase + it * 32 + lane;
+            KeyT v = Win<KeyT>::load(codes, p * L, KL);
+            KeyT key = boss_rotate(v, L, K);
+            if (CANON) {
+                // complement = ^3 on every 2-bit group, then reverse the groups
+                KeyT r = w_shr(rev2(w_not(v)), WordTraits<KeyT>::BITS - KL);
+                KeyT rkey = boss_rotate(r, L, K);
+                if (w_lt(rkey, key)) key = rkey;   // forward <= reverse keeps forward
+            }
+            uint64_t dst = base + __popc(bal & lanemask_lt());
+            out_keys[dst] = key;
+            if (HAS_COUNT) {
+                // read containing this window: last start <= global position
+                uint64_t gp = tile_start + p;
+                uint64_t lo = 0, hi = n_reads;   // invariant: starts[lo] <= gp < starts[hi]
+                while (hi - lo > 1) {
+                    uint64_t mid = (lo + hi) >> 1;
+                    if (read_starts[mid] <= gp) lo = mid; else hi = mid;
+                }
+                out_counts[dst] = read_counts[lo];
+            }
+        }
+        base += __popc(bal);
+    }
+}
+
+template <typename KeyT, int L, bool CANON>
+void launch_extract(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream) {
+    const uint32_t halo_groups = (a.K - 1 + EX_GROUP - 1) / EX_GROUP;
+    const uint32_t ngroups = EX_THREADS + halo_groups;
+    size_t smem = sizeof(uint32_t) * ((size_t)ngroups * 2 * L + 4 + (size_t)ngroups * 2 + 4);
+    unsigned grid = (unsigned)div_up(a.nbytes, (size_t)EX_TILE);
+    if (a.read_counts) {
+        auto k = extract_kernel<KeyT, L, CANON, true>;
+        k<<<grid, EX_THREADS, smem, stream>>>(a.packed, a.nbytes, *a.lut, a.K, out_keys, a.out_counts,
+                                             a.out_counter, a.read_starts, a.read_counts, a.n_reads);
+    } else {
+        auto k = extract_kernel<KeyT, L, CANON, false>;
+        k<<<grid, EX_THREADS, smem, stream>>>(a.packed, a.nbytes, *a.lut, a.K, out_keys, nullptr,
+                                             a.out_counter, nullptr, nullptr, 0);
+    }
+    MTG_CUDA(cudaGetLastError());
+}
+
+}  // namespace
+
+template <typename KeyT>
+void extract_kmers(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream) {
+    if (a.nbytes == 0) return;
+    if (a.L == 2) {
+        if (a.canonical) launch_extract<KeyT, 2, true>(a, out_keys, stream);
+        else launch_extract<KeyT, 2, false>(a, out_keys, stream);
+    } else if (a.L == 5) {
+        launch_extract<KeyT, 5, false>(a, out_keys, stream);
+    } else {
+        launch_extract<KeyT, 3, false>(a, out_keys, stream);
+    }
+}
+
+template void extract_kmers<uint64_t>(const ExtractArgs &, uint64_t *, cudaStream_t);
+template void extract_kmers<u128>(const ExtractArgs &, u128 *, cudaStream_t);
+
+}  // namespace mtg

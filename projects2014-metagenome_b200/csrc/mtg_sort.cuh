@@ -1,0 +1,59 @@
+// Onesweep LSD radix sort (hand-written, sm_100a): one global histogram kernel,
+// then one scatter kernel per digit with decoupled look-back across tiles.
+// Replaces ips4o::parallel::sort in SortedSet / SortedMultiset
+// (common/sorted_sets/sorted_set.cpp:41-48, sorted_multiset.cpp:54-84) and the
+// dummy k-mer sorts (boss_chunk_construct.cpp:280-306).
+#pragma once
+#include "mtg_common.cuh"
+
+namespace mtg {
+
+constexpr int RADIX_BITS = 8;
+constexpr int RADIX = 1 << RADIX_BITS;
+constexpr int MAX_SORT_PASSES = 40;
+
+// One LSD digit: `bits` bits starting at `shift` of the key (src 0) or of the
+// 32-bit value payload (src 1).
+struct DigitPass {
+    int src, shift, bits;
+};
+
+struct SortPlan {
+    int n;
+    DigitPass p[MAX_SORT_PASSES];
+};
+
+// plan covering key bits [lo, hi) in 8-bit digits
+inline void plan_add_key_bits(SortPlan &plan, int lo, int hi) {
+    for (int b = lo; b < hi; b += RADIX_BITS) {
+        int nb = hi - b < RADIX_BITS ? hi - b : RADIX_BITS;
+        plan.p[plan.n++] = DigitPass{0, b, nb};
+    }
+}
+
+struct SortWorkspace {
+    unsigned long long *status = nullptr;   // [tiles * RADIX]
+    size_t status_words = 0;
+    unsigned long long *hist = nullptr;     // [MAX_SORT_PASSES * RADIX] digit offsets
+    unsigned int *tile_counters = nullptr;  // [MAX_SORT_PASSES]
+};
+
+template <typename KeyT> struct SortTile;
+template <> struct SortTile<uint64_t> { static constexpr int THREADS = 256, IPT = 16; };
+template <> struct SortTile<u128> { static constexpr int THREADS = 256, IPT = 8; };
+
+template <typename KeyT>
+size_t sort_status_words(uint64_t n) {
+    size_t tile = SortTile<KeyT>::THREADS * SortTile<KeyT>::IPT;
+    return (div_up(n, tile) + 1) * RADIX;
+}
+
+// Sorts n keys (with optional 32-bit values). keys[0]/vals[0] hold the input; the
+// function ping-pongs between buffer 0 and 1 and returns the index of the buffer
+// holding the sorted output. Workspace must have status_words >= sort_status_words(n).
+// Returns the number of kernels launched through *launches.
+template <typename KeyT>
+int radix_sort(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan &plan,
+               SortWorkspace &ws, cudaStream_t stream, unsigned *launches);
+
+}  // namespace mtg

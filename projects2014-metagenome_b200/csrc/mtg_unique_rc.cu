@@ -1,0 +1,241 @@
+// K3 (segmented unique / count-reduce) and K1b (reverse-complement completion).
+// Replaces std::unique / the saturating count merge of SortedSet / SortedMultiset
+// (common/sorted_sets/sorted_set.cpp:41-48, sorted_multiset.cpp:54-84) and
+// add_reverse_complements (boss_chunk_construct.cpp:179-222).
+#include "mtg_scan.cuh"
+#include "mtg_stages.cuh"
+
+namespace mtg {
+
+namespace {
+
+constexpr int UQ_THREADS = 256;
+constexpr int UQ_IPT = 8;
+constexpr int UQ_TILE = UQ_THREADS * UQ_IPT;
+
+// Single-pass compaction of run heads with decoupled look-back.
+template <typename KeyT>
+__global__ void __launch_bounds__(UQ_THREADS)
+unique_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_keys,
+              uint64_t *__restrict__ out_starts, unsigned long long *d_num_out,
+              unsigned long long *status, unsigned int *tile_counter) {
+    __shared__ unsigned int sh_tile;
+    __shared__ uint32_t warp_tot[UQ_THREADS / 32 + 1];
+    __shared__ uint64_t slot;
+    if (threadIdx.x == 0) sh_tile = atomicAdd(tile_counter, 1u);
+    __syncthreads();
+    const uint32_t tile = sh_tile;
+    const uint64_t base = (uint64_t)tile * UQ_TILE + (uint64_t)threadIdx.x * UQ_IPT;
+    // blocked arrangement: thread owns UQ_IPT consecutive keys
+    KeyT k[UQ_IPT];
+    KeyT prev = WordTraits<KeyT>::zero();
+    if (base > 0 && base <= n) prev = keys[base - 1];
+    uint32_t heads = 0, cnt = 0;
+#pragma unroll
+    for (int i = 0; i < UQ_IPT; ++i) {
+        uint64_t idx = base + i;
+        if (idx < n) {
+            k[i] = keys[idx];
+            bool head = idx == 0 || !w_eq(k[i], prev);
+            prev = k[i];
+            if (head) { heads |= 1u << i; ++cnt; }
+        }
+    }
+    uint32_t excl = block_exclusive_scan<UQ_THREADS>(cnt, warp_tot);
+    uint32_t tile_total = warp_tot[UQ_THREADS / 32];
+    uint64_t tile_excl = lookback_exclusive(status, tile, tile_total, &slot);
+    uint64_t pos = tile_excl + excl;
+#pragma unroll
+    for (int i = 0; i < UQ_IPT; ++i) {
+        if (heads & (1u << i)) {
+            out_keys[pos] = k[i];
+            out_starts[pos] = base + i;
+            ++pos;
+        }
+    }
+    // the tile holding the last element publishes the total and the end marker
+    if (threadIdx.x == 0 && (uint64_t)(tile + 1) * UQ_TILE >= n) {
+        uint64_t m = tile_excl + tile_total;
+        *d_num_out = m;
+        out_starts[m] = n;
+    }
+}
+
+__global__ void run_counts_kernel(const uint64_t *__restrict__ starts, const uint32_t *__restrict__ vals,
+                                  uint64_t m, uint32_t cmax, uint32_t *__restrict__ counts) {
+    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    uint64_t a = starts[j], b = starts[j + 1];
+    uint64_t c;
+    if (vals) {
+        c = 0;
+        for (uint64_t i = a; i < b && c < cmax; ++i) c += vals[i];
+    } else {
+        c = b - a;
+    }
+    counts[j] = c > cmax ? cmax : (uint32_t)c;
+}
+
+constexpr int SC_THREADS = 256;
+constexpr int SC_IPT = 8;
+constexpr int SC_TILE = SC_THREADS * SC_IPT;
+
+__global__ void __launch_bounds__(SC_THREADS)
+scan_u32_kernel(const uint32_t *__restrict__ in, uint64_t n, uint64_t *__restrict__ out,
+                unsigned long long *status, unsigned int *tile_counter) {
+    __shared__ unsigned int sh_tile;
+    __shared__ uint32_t warp_tot[SC_THREADS / 32 + 1];
+    __shared__ uint64_t slot;
+    if (threadIdx.x == 0) sh_tile = atomicAdd(tile_counter, 1u);
+    __syncthreads();
+    const uint32_t tile = sh_tile;
+    const uint64_t base = (uint64_t)tile * SC_TILE + (uint64_t)threadIdx.x * SC_IPT;
+    uint32_t v[SC_IPT];
+    uint32_t sum = 0;
+#pragma unroll
+    for (int i = 0; i < SC_IPT; ++i) {
+        v[i] = base + i < n ? in[base + i] : 0;
+        sum += v[i];
+    }
+    uint32_t excl = block_exclusive_scan<SC_THREADS>(sum, warp_tot);
+    uint32_t tile_total = warp_tot[SC_THREADS / 32];
+    uint64_t run = lookback_exclusive(status, tile, tile_total, &slot) + excl;
+#pragma unroll
+    for (int i = 0; i < SC_IPT; ++i) {
+        if (base + i < n) out[base + i] = run;
+        run += v[i];
+    }
+    if (threadIdx.x == 0 && (uint64_t)(tile + 1) * SC_TILE >= n)
+        out[n] = slot + tile_total;
+}
+
+__global__ void fill_u32_kernel(uint32_t *p, uint32_t v, uint64_t n) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+__global__ void flip_info_kernel(uint32_t *p, uint64_t n) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = (127u - (p[i] & 127u)) | (p[i] & INFO_W_DOLLAR);
+}
+
+__device__ __forceinline__ uint64_t rev2_64(uint64_t x) {
+    x = __brevll(x);
+    return ((x >> 1) & 0x5555555555555555ull) | ((x & 0x5555555555555555ull) << 1);
+}
+__device__ __forceinline__ uint64_t rev2w(uint64_t x) { return rev2_64(x); }
+__device__ __forceinline__ u128 rev2w(u128 x) { return make_u128(rev2_64(x.hi), rev2_64(x.lo)); }
+
+// kmer::reverse_complement (kmer/kmer_transform.hpp:14-35) for the tight DNA
+// alphabet (complement = code ^ 3) on the KMerBOSS layout.
+template <typename KeyT>
+__device__ __forceinline__ KeyT rc_boss_dna(KeyT x, unsigned K) {
+    const unsigned L = 2, KL = 2 * K;
+    // undo the rotation: v = sum s_i << L(i-1)
+    KeyT v = w_or(w_shr(x, L), w_shl(w_and(x, WordTraits<KeyT>::low_mask(L)), L * (K - 1)));
+    KeyT r = w_shr(rev2w(w_not(v)), WordTraits<KeyT>::BITS - KL);
+    KeyT hi = w_and(w_shl(r, L), WordTraits<KeyT>::low_mask(KL));
+    return w_or(hi, w_shr(r, L * (K - 1)));
+}
+
+template <typename KeyT>
+__global__ void append_rc_kernel(KeyT *keys, uint32_t *counts, uint64_t m, uint32_t K, uint32_t cmax,
+                                 unsigned long long *d_appended) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool emit = false;
+    KeyT rc = WordTraits<KeyT>::zero();
+    uint32_t c = 0;
+    if (i < m) {
+        KeyT x = keys[i];
+        rc = rc_boss_dna(x, K);
+        emit = !w_eq(rc, x);
+        if (counts) {
+            c = counts[i];
+            if (!emit) counts[i] = c > cmax / 2 ? cmax : 2 * c;   // palindrome (:205-211)
+        }
+    }
+    unsigned bal = __ballot_sync(0xffffffffu, emit);
+    if (bal == 0) return;
+    unsigned long long base = 0;
+    if ((threadIdx.x & 31) == 0) base = atomicAdd(d_appended, (unsigned long long)__popc(bal));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (emit) {
+        uint64_t dst = m + base + __popc(bal & lanemask_lt());
+        keys[dst] = rc;
+        if (counts) counts[dst] = c;
+    }
+}
+
+}  // namespace
+
+size_t unique_status_words(uint64_t n) { return div_up(n, (size_t)UQ_TILE) + 1; }
+
+template <typename KeyT>
+void unique_keys(const KeyT *keys, uint64_t n, KeyT *out_keys, uint64_t *out_starts,
+                 unsigned long long *d_num_out, unsigned long long *scan_status,
+                 unsigned int *tile_counter, cudaStream_t stream, unsigned *launches) {
+    size_t tiles = div_up(n, (size_t)UQ_TILE);
+    MTG_CUDA(cudaMemsetAsync(scan_status, 0, sizeof(unsigned long long) * (tiles + 1), stream));
+    MTG_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream));
+    MTG_CUDA(cudaMemsetAsync(d_num_out, 0, sizeof(unsigned long long), stream));
+    if (n == 0) return;
+    unique_kernel<KeyT><<<(unsigned)tiles, UQ_THREADS, 0, stream>>>(keys, n, out_keys, out_starts,
+                                                                   d_num_out, scan_status, tile_counter);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+template void unique_keys<uint64_t>(const uint64_t *, uint64_t, uint64_t *, uint64_t *,
+                                    unsigned long long *, unsigned long long *, unsigned int *,
+                                    cudaStream_t, unsigned *);
+template void unique_keys<u128>(const u128 *, uint64_t, u128 *, uint64_t *, unsigned long long *,
+                                unsigned long long *, unsigned int *, cudaStream_t, unsigned *);
+
+void run_counts(const uint64_t *starts, const uint32_t *vals, uint64_t m, uint32_t cmax,
+                uint32_t *counts, cudaStream_t stream, unsigned *launches) {
+    if (m == 0) return;
+    run_counts_kernel<<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(starts, vals, m, cmax, counts);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+void exclusive_scan_u32(const uint32_t *in, uint64_t n, uint64_t *out, unsigned long long *scan_status,
+                        unsigned int *tile_counter, cudaStream_t stream, unsigned *launches) {
+    size_t tiles = div_up(n, (size_t)SC_TILE);
+    MTG_CUDA(cudaMemsetAsync(scan_status, 0, sizeof(unsigned long long) * (tiles + 1), stream));
+    MTG_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream));
+    if (n == 0) {
+        MTG_CUDA(cudaMemsetAsync(out, 0, sizeof(uint64_t), stream));
+        return;
+    }
+    scan_u32_kernel<<<(unsigned)tiles, SC_THREADS, 0, stream>>>(in, n, out, scan_status, tile_counter);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+void fill_u32(uint32_t *p, uint32_t v, uint64_t n, cudaStream_t stream, unsigned *launches) {
+    if (n == 0) return;
+    fill_u32_kernel<<<(unsigned)div_up(n, (size_t)256), 256, 0, stream>>>(p, v, n);
+    *launches += 1;
+}
+void flip_info(uint32_t *info, uint64_t n, cudaStream_t stream, unsigned *launches) {
+    if (n == 0) return;
+    flip_info_kernel<<<(unsigned)div_up(n, (size_t)256), 256, 0, stream>>>(info, n);
+    *launches += 1;
+}
+
+template <typename KeyT>
+void append_reverse_complements(KeyT *keys, uint32_t *counts, uint64_t m, Alpha al, uint32_t cmax,
+                                unsigned long long *d_appended, cudaStream_t stream,
+                                unsigned *launches) {
+    MTG_CUDA(cudaMemsetAsync(d_appended, 0, sizeof(unsigned long long), stream));
+    if (m == 0) return;
+    append_rc_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(keys, counts, m, al.K,
+                                                                               cmax, d_appended);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+template void append_reverse_complements<uint64_t>(uint64_t *, uint32_t *, uint64_t, Alpha, uint32_t,
+                                                   unsigned long long *, cudaStream_t, unsigned *);
+template void append_reverse_complements<u128>(u128 *, uint32_t *, uint64_t, Alpha, uint32_t,
+                                               unsigned long long *, cudaStream_t, unsigned *);
+
+}  // namespace mtg
