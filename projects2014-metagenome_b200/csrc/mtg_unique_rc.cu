@@ -49,7 +49,7 @@ unique_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_
     for (int i = 0; i < UQ_IPT; ++i) {
         if (heads & (1u << i)) {
             out_keys[pos] = k[i];
-            out_starts[pos] = base + i;
+            if (out_starts) out_starts[pos] = base + i;
             ++pos;
         }
     }
@@ -57,7 +57,7 @@ unique_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_
     if (threadIdx.x == 0 && (uint64_t)(tile + 1) * UQ_TILE >= n) {
         uint64_t m = tile_excl + tile_total;
         *d_num_out = m;
-        out_starts[m] = n;
+        if (out_starts) out_starts[m] = n;
     }
 }
 

@@ -1,0 +1,197 @@
+"""GPU parity tests: the CUDA path (through the C ABI) against the CPU oracle on the same
+seeded inputs. Bit-exact (integer / byte work): W, last, F, weights, counters."""
+import ctypes
+
+import numpy as np
+import pytest
+
+import mtg_b200
+import oracle_lib
+from mtg_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def dna_reads(seed, n, length, G, e=0.01, n_frac=0.0):
+    packed = synth.dna_reads_packed_np(seed, n, length, G, e)
+    reads = synth.packed_to_strings(packed)
+    if n_frac:
+        rng = np.random.default_rng(seed)
+        out = []
+        for r in reads:
+            b = bytearray(r.encode())
+            for p in np.nonzero(rng.random(len(b)) < n_frac)[0]:
+                b[p] = ord("N")
+            out.append(b.decode())
+        reads = out
+    return reads
+
+
+def gpu_build(reads, K, alphabet="DNA", canonical=False, bits_per_count=0, counts=None):
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, canonical, bits_per_count,
+                                                    alphabet=alphabet)
+    if counts is not None:
+        ctor.add_sequences(list(zip(reads, [int(c) for c in counts])))
+    else:
+        # several pushes, like the reference's 1 MB batches
+        step = max(1, len(reads) // 3)
+        for i in range(0, len(reads), step):
+            ctor.add_sequences(reads[i:i + step])
+    chunk = ctor.build_chunk()
+    ctor.close()
+    return chunk
+
+
+def check(reads, K, alphabet="DNA", canonical=False, bits_per_count=0, counts=None):
+    chunk = gpu_build(reads, K, alphabet, canonical, bits_per_count, counts)
+    ref = oracle_lib.oracle_build(reads, K, alphabet=alphabet, canonical=canonical,
+                                  bits_per_count=bits_per_count, counts=counts)
+    assert chunk.n_rows == ref["n_rows"]
+    assert chunk.stats["n_real"] == ref["n_real"]
+    assert chunk.stats["n_dummy_sink"] == ref["n_sink"]
+    assert chunk.stats["n_dummy_source"][: len(ref["n_src"])] == [int(x) for x in ref["n_src"]]
+    assert np.array_equal(chunk.F, ref["F"])
+    assert np.array_equal(chunk.last, ref["last"])
+    assert np.array_equal(chunk.W, ref["W"])
+    if bits_per_count:
+        assert np.array_equal(chunk.weights, ref["weights"])
+    else:
+        assert chunk.weights is None
+    # sdsl file bytes == what the reference's BOSS::Chunk::serialize would write
+    assert (chunk._int_vector_bytes(chunk.W_words, chunk.n_rows, chunk.W_width, False)
+            == oracle_lib.sdsl_int_vector_bytes(ref["W"], chunk.W_width))
+    assert (chunk._int_vector_bytes(chunk.last_words, chunk.n_rows, 1, True)
+            == oracle_lib.sdsl_int_vector_bytes(ref["last"], 1, True))
+    return chunk
+
+
+# ---- radix sort primitive ---------------------------------------------------
+
+@pytest.mark.parametrize("n", [0, 1, 100, 4096, 4097, 50_000, 1_000_003])
+@pytest.mark.parametrize("bits", [7, 24, 62, 64])
+def test_radix_sort_u64(n, bits):
+    rng = np.random.default_rng(n + bits)
+    keys = rng.integers(0, 2 ** 63, n, dtype=np.uint64) * 2 + rng.integers(0, 2, n, dtype=np.uint64)
+    if bits < 64:
+        keys &= np.uint64((1 << bits) - 1)
+    vals = np.arange(n, dtype=np.uint32)
+    lib = mtg_b200._lib.load()
+    k2 = keys.copy()
+    assert lib.mtg_debug_sort_u64(0, k2.ctypes.data_as(ctypes.c_void_p), None, n, bits) == 0
+    assert np.array_equal(k2, np.sort(keys))
+    k3, v3 = keys.copy(), vals.copy()
+    assert lib.mtg_debug_sort_u64(0, k3.ctypes.data_as(ctypes.c_void_p),
+                                  v3.ctypes.data_as(ctypes.c_void_p), n, bits) == 0
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(k3, keys[order])
+    assert np.array_equal(v3, vals[order])   # stability
+
+
+@pytest.mark.parametrize("n", [0, 5, 2048, 2049, 300_001])
+@pytest.mark.parametrize("bits", [70, 126, 128])
+def test_radix_sort_u128(n, bits):
+    rng = np.random.default_rng(n + bits)
+    lo = rng.integers(0, 2 ** 63, n, dtype=np.uint64) * 2 + rng.integers(0, 2, n, dtype=np.uint64)
+    hi = rng.integers(0, 2 ** 63, n, dtype=np.uint64) * 2 + rng.integers(0, 2, n, dtype=np.uint64)
+    if bits < 128:
+        hi &= np.uint64((1 << (bits - 64)) - 1)
+    if n > 10:
+        hi[: n // 2] = hi[0]   # ties on the high word
+        lo[: n // 4] = lo[0]
+    keys = np.stack([lo, hi], axis=1).copy()
+    vals = np.arange(n, dtype=np.uint32)
+    lib = mtg_b200._lib.load()
+    assert lib.mtg_debug_sort_u128(0, keys.ctypes.data_as(ctypes.c_void_p),
+                                   vals.ctypes.data_as(ctypes.c_void_p), n, bits) == 0
+    order = np.lexsort((lo, hi))   # stable, hi is the primary key
+    assert np.array_equal(keys[:, 0], lo[order])
+    assert np.array_equal(keys[:, 1], hi[order])
+    assert np.array_equal(vals, np.arange(n, dtype=np.uint32)[order])
+
+
+# ---- sorted k-mer set (extraction + sort + unique/count + rc) ------------------
+
+@pytest.mark.parametrize("K,canonical,bpc", [(12, False, 0), (31, True, 0), (31, True, 8),
+                                             (32, False, 16), (33, True, 8), (63, True, 0),
+                                             (64, False, 8)])
+def test_sorted_kmers(K, canonical, bpc):
+    reads = dna_reads(3, 1500, 120, 15000, n_frac=0.003)
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, canonical, bpc)
+    ctor.add_sequences(reads)
+    words, counts = ctor.debug_sorted_kmers()
+    ctor.close()
+    ref = oracle_lib.oracle_build(reads, K, canonical=canonical, bits_per_count=bpc)
+    assert np.array_equal(words, ref["kmers"][:, :2])
+    assert not ref["kmers"][:, 2:].any()
+    if bpc:
+        assert np.array_equal(counts.astype(np.uint64), ref["kmer_counts"])
+
+
+# ---- whole chunk ---------------------------------------------------------------
+
+@pytest.mark.parametrize("K", [2, 3, 4, 5, 8, 12, 20, 31, 32])
+@pytest.mark.parametrize("canonical", [False, True])
+def test_chunk_dna_u64(K, canonical):
+    check(dna_reads(K, 800, 90, 6000, n_frac=0.002), K, canonical=canonical)
+
+
+@pytest.mark.parametrize("K,canonical,bpc", [(33, False, 0), (40, True, 8), (63, True, 0),
+                                             (64, False, 12), (64, True, 0)])
+def test_chunk_dna_u128(K, canonical, bpc):
+    check(dna_reads(K, 600, 150, 8000), K, canonical=canonical, bits_per_count=bpc)
+
+
+@pytest.mark.parametrize("bpc", [1, 2, 8, 12, 16, 32])
+@pytest.mark.parametrize("canonical", [False, True])
+def test_chunk_weighted(bpc, canonical):
+    # deep coverage of a tiny genome: counts saturate for small widths
+    check(dna_reads(bpc, 3000, 80, 1200, e=0.002), 21, canonical=canonical, bits_per_count=bpc)
+
+
+def test_chunk_explicit_counts():
+    reads = dna_reads(9, 1000, 100, 5000)
+    rng = np.random.default_rng(1)
+    counts = rng.integers(1, 400, len(reads)).astype(np.uint64)
+    counts[:5] = [2 ** 40, 255, 256, 65535, 65536]   # clipped to the container type first
+    for bpc in (8, 12, 32):
+        check(reads, 25, canonical=True, bits_per_count=bpc, counts=counts)
+
+
+def test_chunk_palindromes_and_lowercase():
+    reads = ["ACGT" * 20, "acgtacgtnnACGTACGTACGTTTTTTTTTTTTAAAAAAAAAAAA", "TTTTTTTTTTTTTTTTTTTT",
+             "AAAAAAAAAAAAAAAAAAAAAAAA", "ACGUACGUACGUACGUUUU", "GATTACA", "", "AC", "NNNNNNNNNNNNNNNN"]
+    for K in (2, 4, 6, 8):
+        for canonical in (False, True):
+            check(reads, K, canonical=canonical, bits_per_count=8)
+
+
+def test_chunk_empty_and_short_inputs():
+    for reads in ([], ["ACG"], ["ACGTN" * 3], ["", "", ""]):
+        check(reads, 10)
+        check(reads, 10, canonical=True, bits_per_count=8)
+
+
+@pytest.mark.parametrize("K", [2, 3, 7, 12, 13, 25])
+def test_chunk_protein(K):
+    packed = synth.protein_reads_packed_np(4, 300, 120)
+    reads = synth.packed_to_strings(packed)
+    reads[0] = reads[0][:50] + "*?xbZ" + reads[0][55:]   # unknown characters are 'X'
+    check(reads, K, alphabet="Protein", bits_per_count=8 if K % 2 else 0)
+
+
+def test_chunk_multi_tile():
+    # > 1 extraction tile, many sort tiles, several emit tiles
+    reads = dna_reads(77, 20000, 150, 400_000, e=0.005)
+    c = check(reads, 31, canonical=True, bits_per_count=8)
+    assert c.stats["n_input_kmers"] == 20000 * 120
+
+
+def test_errors():
+    with pytest.raises(mtg_b200.MtgError):
+        mtg_b200.BOSSChunkConstructor.initialize(0)
+    with pytest.raises(mtg_b200.MtgError):
+        mtg_b200.BOSSChunkConstructor.initialize(85)
+    with pytest.raises(mtg_b200.MtgError):
+        mtg_b200.BOSSChunkConstructor.initialize(20, bits_per_count=33)
+    with pytest.raises(mtg_b200.MtgError):
+        mtg_b200.BOSSChunkConstructor.initialize(20, both_strands=True, alphabet="Protein")
