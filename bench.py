@@ -1,0 +1,367 @@
+#!/usr/bin/env python
+"""Benchmark of the B200-native `metagraph build` hot path (BOSS chunk construction).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Metric (BASELINE.json): input k-mers/s for the BOSS build, k=31. A step is one whole pass of
+the hot path (extract -> sort -> unique -> rc completion -> dummy k-mers -> W/last/F) over
+one batch of synthetic reads. N=1 workload = BASELINE.json configs[1]: 10M x 150bp DNA reads,
+k=31, canonical. `value` = reads resident in HBM, chunk left in HBM; `e2e` = the same through
+the host C ABI (pinned host reads in, chunk in pinned host memory out).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+METRIC = "input k-mers/sec for BOSS build k=31"
+UNIT = "kmers/s"
+
+WORKLOADS = {
+    # name: (n_reads, read_len, genome, seed, e, K, canonical, bits_per_count)
+    "cfg2": dict(name="synthetic 10Mx150bp DNA reads, k=31, canonical", n_reads=10_000_000,
+                 read_len=150, G=100_000_000, seed=1, e=0.005, K=31, canonical=True, bpc=0),
+    "cfg3": dict(name="synthetic 100Mx150bp DNA reads, k=31, --count-kmers", n_reads=100_000_000,
+                 read_len=150, G=1_000_000_000, seed=2, e=0.005, K=31, canonical=False, bpc=8),
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default=None, help="cfg2 (default at N=1) or cfg3")
+    ap.add_argument("--reads", type=int, default=0, help="override the number of reads (debug)")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-reads", type=int, default=1_000_000)
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for i, nm in enumerate(names):
+                if f[3 + i].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def algorithmic_bytes(st, R, w, c, P, canonical, W_width, bpc):
+    """SURVEY.md 8d byte model, evaluated on the counters of the actual build."""
+    N = st["n_input_kmers"]
+    Mp = st["n_real"]
+    D = st["n_dummy_sink"] + sum(st["n_dummy_source"])
+    E = st["n_rows"]
+    M = (Mp + 1) // 2 if canonical else Mp     # distinct canonical k-mers (palindromes ~ 0)
+    b = R + N * (w + c)                         # 1 extract
+    b += N * (w + c) * (1 + 2 * P)              # 2 sort
+    b += N * (w + c) + M * (w + c)              # 3 unique / count-reduce
+    if canonical:                               # 4 rc generate, sort rc, merge
+        b += 2 * M * (w + c) + M * (w + c) * (1 + 2 * P) + 2 * Mp * (w + c)
+    b += 4 * Mp * w + D * w * (1 + 2 * P)       # 5 dummy recovery
+    b += (Mp + D) * (w + c) + E * (W_width + 1 + bpc) / 8   # 6 merge + emit
+    return b
+
+
+def cpu_reference_run(wl, n_reads, threads, repeats=1):
+    """Times the reference's own CPU implementation (oracle/_ref/ref_driver_DNA, built from the
+    unmodified /root/reference sources) on a bounded sample of the workload. Returns
+    (kmers_per_s, info) or (None, why)."""
+    import numpy as np
+    import mtg_b200
+    from mtg_b200 import synth
+    import oracle_lib
+    drv = oracle_lib.ref_driver("DNA")
+    G = max(wl["read_len"] * 2, int(wl["G"] * n_reads / wl["n_reads"]))   # same coverage
+    n_kmers = n_reads * (wl["read_len"] - wl["K"] + 1)
+    with tempfile.TemporaryDirectory() as td:
+        if drv is None:
+            # oracle port (single thread) on a smaller sample
+            n_reads = min(n_reads, 100_000)
+            G = max(wl["read_len"] * 2, int(wl["G"] * n_reads / wl["n_reads"]))
+            n_kmers = n_reads * (wl["read_len"] - wl["K"] + 1)
+            packed = synth.dna_reads_packed_np(wl["seed"], n_reads, wl["read_len"], G, wl["e"])
+            reads = synth.packed_to_strings(packed)
+            t0 = time.perf_counter()
+            oracle_lib.oracle_build(reads, wl["K"], canonical=wl["canonical"],
+                                    bits_per_count=wl["bpc"])
+            dt = time.perf_counter() - t0
+            return n_kmers / dt, dict(kind="port", cores=1, seconds=dt, all_seconds=[dt] * repeats,
+                                      n_reads=n_reads, sample="%d reads x %d bp "
+                                      "(same coverage), oracle/mtg_oracle.cpp" % (n_reads, wl["read_len"]))
+        path = os.path.join(td, "reads.txt")
+        genome = synth.genome_np(wl["seed"], G)
+        with open(path, "wb") as f:
+            for r0 in range(0, n_reads, 200_000):
+                r1 = min(n_reads, r0 + 200_000)
+                p = synth.dna_reads_packed_np(wl["seed"], n_reads, wl["read_len"], G, wl["e"], r0, r1,
+                                              genome=genome)
+                p[:, -1] = ord("\n")
+                f.write(p.tobytes())
+        cmd = [drv, "-k", str(wl["K"]), "-p", str(threads), "--mem-gb", "8", "-o",
+               os.path.join(td, "out"), path]
+        if wl["canonical"]:
+            cmd.append("--canonical")
+        if wl["bpc"]:
+            cmd += ["--count-width", str(wl["bpc"])]
+        secs = []
+        for _ in range(repeats):
+            out = subprocess.run(cmd, capture_output=True, text=True, timeout=1500)
+            if out.returncode != 0:
+                return None, "ref_driver failed: " + out.stderr[-200:]
+            fields = out.stdout.split()
+            secs.append(float(fields[fields.index("build_sec") + 1]))
+        build_sec = secs[-1]
+        return n_kmers / build_sec, dict(
+            kind="reference", cores=threads, seconds=build_sec, all_seconds=secs, n_reads=n_reads,
+            sample="%d reads x %d bp, genome %d bp (same coverage as the workload), "
+                   "reference IBOSSChunkConstructor add_sequences+build_chunk, -p %d"
+                   % (n_reads, wl["read_len"], G, threads))
+
+
+def run_reference(args, wl):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    threads = os.cpu_count() or 1
+    n_reads = min(wl["n_reads"], args.cpu_sample_reads)
+    v, info = cpu_reference_run(wl, n_reads, threads, repeats=args.warmup + args.steps)
+    if v is None:
+        print(json.dumps({"impl": "reference", "unavailable": info}))
+        return
+    secs = info["all_seconds"][args.warmup:]
+    per_step = info["n_reads"] * (wl["read_len"] - wl["K"] + 1)
+    value = per_step * len(secs) / sum(secs)
+    vals = [(value, x) for x in secs]
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT,
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": 1e3 * sum(s for _, s in vals) / len(vals), "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": wl["name"], "sample": info["sample"]},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": info["cores"],
+                         "kind": info["kind"], "sample": info["sample"]},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }
+    print(json.dumps(line))
+
+
+def run_ours(args, wl):
+    import numpy as np
+    import torch
+    import mtg_b200
+    from mtg_b200 import synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the hot path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    K, L = wl["K"], wl["read_len"]
+    n_reads = wl["n_reads"]
+    if world > 1:
+        from mtg_b200 import multi_gpu
+        return multi_gpu.bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler,
+                               algorithmic_bytes)
+
+    # ---- synthetic reads, generated straight into HBM in the packed layout ----
+    packed = synth.dna_reads_packed_torch(wl["seed"], n_reads, L, wl["G"], wl["e"], device=dev)
+    n_bytes = packed.numel()
+    n_windows = n_reads * (L - K + 1)
+    stream = torch.cuda.current_stream()
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, wl["canonical"], wl["bpc"], device=local)
+    ctor.set_stream(stream.cuda_stream)
+
+    def step_device():
+        ctor.add_packed_device(packed.data_ptr(), n_bytes, n_windows)
+        return ctor.build_chunk_device()
+
+    for _ in range(args.warmup):
+        st = step_device()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    time.sleep(0.3)
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    stats = []
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for _ in range(args.steps):
+        stats.append(step_device())
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms_total = ev0.elapsed_time(ev1)
+    ms_per_step = ms_total / args.steps
+    st = stats[-1]
+    N = st["n_input_kmers"]
+    value = N * args.steps / (ms_total * 1e-3)
+
+    # ---- roofline of the dominant kernel (onesweep pass of the main sort) ----
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
+    n_launch = sum(s["n_onesweep"] for s in stats)
+    ms_kernel = sum(s["ms_onesweep_sum"] for s in stats) / max(n_launch, 1)
+    bytes_launch = st["onesweep_keys"] * st["onesweep_bytes_per_key"]
+    achieved = bytes_launch / (ms_kernel * 1e-3) / 1e9 if ms_kernel else 0.0
+    w = 8 if K * 2 <= 64 else 16
+    c = 0
+    P = (K * 2 + 7) // 8
+    alg = algorithmic_bytes(st, n_bytes, w, c, P, wl["canonical"], 4, wl["bpc"])
+    device_ms = sum(s["ms_total"] for s in stats) / len(stats)
+    roofline = {
+        "bound": "hbm", "kernel": "onesweep_pass_kernel<u64> (main k-mer sort, 8 launches/step)",
+        "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+        "traffic": None, "peak_source": peak_src,
+        "algorithmic_bytes_per_launch": bytes_launch, "ms_per_launch": ms_kernel,
+        "kernel_share_of_step": sum(s["ms_onesweep_sum"] for s in stats) / max(ms_total, 1e-9),
+        "whole_path": {"algorithmic_bytes_per_step": alg, "bytes_per_input_kmer": alg / max(N, 1),
+                       "device_ms_per_step": device_ms,
+                       "achieved": alg / (device_ms * 1e-3) / 1e9,
+                       "frac": alg / (device_ms * 1e-3) / 1e9 / peak},
+        "phases_ms": {k2: sum(s[k2] for s in stats) / len(stats) for k2 in
+                      ("ms_extract", "ms_sort", "ms_unique", "ms_rc", "ms_dummy", "ms_emit",
+                       "ms_sort_histogram")},
+    }
+
+    # ---- end to end through the host C ABI: pinned host reads in, pinned chunk out ----
+    e2e = None
+    if not args.no_e2e:
+        host = torch.empty((n_reads, L), dtype=torch.uint8, pin_memory=True)
+        host.copy_(packed[:, :L])
+        torch.cuda.synchronize()
+        bases = host.numpy().reshape(-1)
+        offsets = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(L)
+        ctor2 = mtg_b200.BOSSChunkConstructor.initialize(K - 1, wl["canonical"], wl["bpc"], device=local)
+
+        def step_host():
+            ctor2.add_packed(bases, offsets)
+            return ctor2.build_chunk()
+
+        chunk = step_host()   # warm-up (pinned staging, pools)
+        torch.cuda.synchronize()
+        e_steps = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            chunk = step_host()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        e2e = {"value": N * e_steps / dt, "unit": UNIT,
+               "h2d_bytes_per_step": int(n_reads * (L + 1)),
+               "d2h_bytes_per_step": int(chunk.stats["chunk_bytes"]),
+               "ms_per_step": 1e3 * dt / e_steps, "steps": e_steps,
+               "api": "mtg_push_reads(host bases+offsets) + mtg_build_chunk (host W/last/F)"}
+        ctor2.close()
+        del host
+
+    # ---- CPU baseline: the reference's own implementation on this box's host cores ----
+    cpu = None
+    if not args.no_cpu_baseline:
+        threads = os.cpu_count() or 1
+        v, info = cpu_reference_run(wl, min(n_reads, args.cpu_sample_reads), threads)
+        if v is not None:
+            cpu = {"value": v, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
+                   "sample": info["sample"], "seconds": info["seconds"]}
+        else:
+            cpu = {"value": None, "unit": UNIT, "cores": threads, "kind": "reference", "sample": info}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": wl["name"], "n_reads": n_reads, "read_len": L, "k": K,
+                   "mode": "canonical" if wl["canonical"] else "basic", "count_width": wl["bpc"],
+                   "genome_bp": wl["G"], "subst_rate": wl["e"], "seed": wl["seed"],
+                   "input_kmers": N, "real_kmers": st["n_real"], "rows": st["n_rows"],
+                   "l2_policy": "inputs larger than L2 (reads %.2f GB, keys %.2f GB per step)"
+                                % (n_bytes / 1e9, N * w / 1e9)},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(sum(s["n_kernel_launches"] for s in stats)),
+        "roofline": roofline, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line))
+    ctor.close()
+
+
+def main():
+    args = parse_args()
+    wl = dict(WORKLOADS[args.workload or ("cfg2" if args.gpus == 1 else "cfg3")])
+    if args.reads:
+        wl["G"] = max(2 * wl["read_len"], int(wl["G"] * args.reads / wl["n_reads"]))
+        wl["n_reads"] = args.reads
+        wl["name"] += " (scaled to %d reads)" % args.reads
+    if args.impl == "reference":
+        run_reference(args, wl)
+    else:
+        run_ours(args, wl)
+
+
+if __name__ == "__main__":
+    main()

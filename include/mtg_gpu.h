@@ -76,7 +76,13 @@ typedef struct mtg_chunk {
     /* device time (CUDA events) of the last build, ms; [0]=total, then per phase */
     float ms_total, ms_extract, ms_sort, ms_unique, ms_rc, ms_dummy, ms_emit;
     uint32_t n_kernel_launches;
-    uint32_t reserved;
+    uint32_t device_resident; /* 1: W/last/weights are DEVICE pointers (mtg_build_chunk_device) */
+    /* the dominant kernel (onesweep pass of the main k-mer sort), CUDA events around each launch */
+    float ms_onesweep_sum;    /* sum of the pass kernels' durations, ms */
+    float ms_sort_histogram;  /* the digit-histogram kernel */
+    uint32_t n_onesweep;      /* number of pass launches */
+    uint32_t onesweep_bytes_per_key; /* key (+payload) bytes one pass reads and writes per key */
+    uint64_t onesweep_keys;   /* keys per pass launch */
     void *impl;
 } mtg_chunk;
 
@@ -107,7 +113,14 @@ void mtg_pack_reads(const char *bases, const uint64_t *offsets, size_t n_reads, 
  * sort/unique/rc/dummy/emit on the device, copies the chunk to pinned host memory.
  * The context is cleared afterwards (like kmer_collector.clear(), :353). */
 int mtg_build_chunk(mtg_ctx *ctx, mtg_chunk *out);
+/* Same, but the chunk stays in HBM: out->W / last / weights are device pointers (used by the
+ * device-resident benchmark leg and by multi-GPU orchestration). */
+int mtg_build_chunk_device(mtg_ctx *ctx, mtg_chunk *out);
 void mtg_free_chunk(mtg_chunk *chunk);
+
+/* Run all work of this context on the caller's CUDA stream (cudaStream_t) instead of the
+ * library's own, so that the caller's events bracket it. Call before any push. */
+int mtg_set_stream(mtg_ctx *ctx, void *cuda_stream);
 
 /* Test hooks (parity of intermediate stages): run extraction + sort +
  * unique (+ rc completion) only and return the sorted real k-mers of the collector

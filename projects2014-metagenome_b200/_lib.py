@@ -32,13 +32,16 @@ class MtgChunk(ctypes.Structure):
                 ("ms_total", ctypes.c_float), ("ms_extract", ctypes.c_float),
                 ("ms_sort", ctypes.c_float), ("ms_unique", ctypes.c_float),
                 ("ms_rc", ctypes.c_float), ("ms_dummy", ctypes.c_float), ("ms_emit", ctypes.c_float),
-                ("n_kernel_launches", ctypes.c_uint32), ("reserved", ctypes.c_uint32),
+                ("n_kernel_launches", ctypes.c_uint32), ("device_resident", ctypes.c_uint32),
+                ("ms_onesweep_sum", ctypes.c_float), ("ms_sort_histogram", ctypes.c_float),
+                ("n_onesweep", ctypes.c_uint32), ("onesweep_bytes_per_key", ctypes.c_uint32),
+                ("onesweep_keys", ctypes.c_uint64),
                 ("impl", ctypes.c_void_p)]
 
 
 EXPORTS = ["mtg_create", "mtg_destroy", "mtg_last_error", "mtg_push_reads",
            "mtg_push_packed_device", "mtg_packed_size", "mtg_pack_reads", "mtg_build_chunk",
-           "mtg_free_chunk", "mtg_debug_sorted_kmers", "mtg_debug_free", "mtg_debug_sort_u64",
+           "mtg_build_chunk_device", "mtg_set_stream", "mtg_free_chunk", "mtg_debug_sorted_kmers", "mtg_debug_free", "mtg_debug_sort_u64",
            "mtg_debug_sort_u128"]
 
 _lib = None
@@ -77,6 +80,10 @@ def load():
     lib.mtg_pack_reads.restype = None
     lib.mtg_build_chunk.argtypes = [ctypes.c_void_p, ctypes.POINTER(MtgChunk)]
     lib.mtg_build_chunk.restype = ctypes.c_int
+    lib.mtg_build_chunk_device.argtypes = [ctypes.c_void_p, ctypes.POINTER(MtgChunk)]
+    lib.mtg_build_chunk_device.restype = ctypes.c_int
+    lib.mtg_set_stream.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    lib.mtg_set_stream.restype = ctypes.c_int
     lib.mtg_free_chunk.argtypes = [ctypes.POINTER(MtgChunk)]
     lib.mtg_free_chunk.restype = None
     lib.mtg_debug_sorted_kmers.argtypes = [ctypes.c_void_p, ctypes.POINTER(u64p),

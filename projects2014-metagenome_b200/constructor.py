@@ -210,6 +210,39 @@ class BOSSChunkConstructor:
         self._check(self._lib.mtg_push_packed_device(self._ctx, ctypes.c_void_p(dptr),
                                                      n_bytes, n_windows_max))
 
+    def set_stream(self, cuda_stream):
+        """Run the library's work on the caller's CUDA stream (an int cudaStream_t handle)."""
+        self._check(self._lib.mtg_set_stream(self._ctx, ctypes.c_void_p(cuda_stream)))
+
+    @staticmethod
+    def _stats(c):
+        return {
+            "n_rows": int(c.n_rows),
+            "n_input_kmers": int(c.n_input_kmers), "n_real": int(c.n_real),
+            "n_dummy_sink": int(c.n_dummy_sink),
+            "n_dummy_source": [int(c.n_dummy_source[i]) for i in range(c.k)],
+            "ms_total": c.ms_total, "ms_extract": c.ms_extract, "ms_sort": c.ms_sort,
+            "ms_unique": c.ms_unique, "ms_rc": c.ms_rc, "ms_dummy": c.ms_dummy,
+            "ms_emit": c.ms_emit, "n_kernel_launches": int(c.n_kernel_launches),
+            "ms_onesweep_sum": c.ms_onesweep_sum, "ms_sort_histogram": c.ms_sort_histogram,
+            "n_onesweep": int(c.n_onesweep),
+            "onesweep_bytes_per_key": int(c.onesweep_bytes_per_key),
+            "onesweep_keys": int(c.onesweep_keys),
+            "chunk_bytes": 8 * (((c.n_rows * c.W_width + 63) // 64) + ((c.n_rows + 63) // 64)
+                                + ((c.n_rows * c.weights_width + 63) // 64)),
+        }
+
+    def build_chunk_device(self):
+        """Build with the chunk left in HBM; returns the statistics only (F included)."""
+        c = MtgChunk()
+        self._check(self._lib.mtg_build_chunk_device(self._ctx, ctypes.byref(c)))
+        try:
+            st = self._stats(c)
+            st["F"] = [int(c.F[i]) for i in range(c.sigma)]
+            return st
+        finally:
+            self._lib.mtg_free_chunk(ctypes.byref(c))
+
     def build_chunk(self):
         c = MtgChunk()
         self._check(self._lib.mtg_build_chunk(self._ctx, ctypes.byref(c)))
@@ -224,14 +257,7 @@ class BOSSChunkConstructor:
                 nw = (n * c.weights_width + 63) // 64
                 wts = np.ctypeslib.as_array(c.weights, (nw,)).copy()
             F = np.array(c.F[: c.sigma], dtype=np.uint64)
-            stats = {
-                "n_input_kmers": int(c.n_input_kmers), "n_real": int(c.n_real),
-                "n_dummy_sink": int(c.n_dummy_sink),
-                "n_dummy_source": [int(c.n_dummy_source[i]) for i in range(c.k)],
-                "ms_total": c.ms_total, "ms_extract": c.ms_extract, "ms_sort": c.ms_sort,
-                "ms_unique": c.ms_unique, "ms_rc": c.ms_rc, "ms_dummy": c.ms_dummy,
-                "ms_emit": c.ms_emit, "n_kernel_launches": int(c.n_kernel_launches),
-            }
+            stats = self._stats(c)
             return Chunk(c.sigma, c.k, n, W, last, F, c.W_width, wts, c.weights_width, stats)
         finally:
             self._lib.mtg_free_chunk(ctypes.byref(c))

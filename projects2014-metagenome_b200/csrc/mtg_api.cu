@@ -64,6 +64,7 @@ struct ReadSegment {
 
 struct ChunkImpl {
     void *pinned = nullptr;
+    DevBuf dev;
 };
 
 }  // namespace
@@ -74,7 +75,7 @@ struct mtg_ctx {
     uint32_t L2;
     ExtractLut lut;
     int device = 0;
-    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaStream_t stream = nullptr, own_stream = nullptr;
     std::mutex mu;
     std::vector<ReadSegment> segs;
     std::deque<PinnedBuf> pinned;
@@ -221,7 +222,8 @@ int mtg_create(const mtg_params *p, mtg_ctx **out) {
             delete ctx;
             return fail(nullptr, MTG_ERR_CUDA, "device is not sm_100 (kernels are built for sm_100a only)");
         }
-        MTG_CUDA(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        MTG_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+        ctx->stream = ctx->own_stream;
         cudaMemPool_t pool;
         MTG_CUDA(cudaDeviceGetDefaultMemPool(&pool, ctx->device));
         uint64_t thr = UINT64_MAX;
@@ -244,7 +246,8 @@ void mtg_destroy(mtg_ctx *ctx) {
         if (b.p) cudaFreeHost(b.p);
         if (b.ev) cudaEventDestroy(b.ev);
     }
-    if (ctx->stream) { cudaStreamSynchronize(ctx->stream); cudaStreamDestroy(ctx->stream); }
+    if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
 
@@ -372,6 +375,15 @@ unsigned long long read_counter(const unsigned long long *d, cudaStream_t s) {
     return h;
 }
 
+struct SortProfile {   // CUDA events around every kernel of the main sort
+    cudaEvent_t ev[2 * MAX_SORT_PASSES + 2];
+    int npasses = 0;
+    uint64_t n = 0;
+    uint32_t bytes_per_key = 0;
+    SortProfile() { for (auto &e : ev) cudaEventCreate(&e); }
+    ~SortProfile() { for (auto &e : ev) cudaEventDestroy(e); }
+};
+
 struct RealSet {   // sorted distinct real k-mers (both strands in canonical mode)
     DevBuf keys, counts;
     uint64_t m = 0, n_input = 0;
@@ -379,7 +391,7 @@ struct RealSet {   // sorted distinct real k-mers (both strands in canonical mod
 
 template <typename KeyT>
 void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const SortPlan &plan,
-               cudaStream_t s, unsigned *launches) {
+               cudaStream_t s, unsigned *launches, cudaEvent_t *events = nullptr) {
     // sorts; on return `a` (and *va) hold the sorted data
     SortWorkspace ws;
     DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
@@ -388,6 +400,7 @@ void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const S
     ws.status = status.as<unsigned long long>();
     ws.hist = hist.as<unsigned long long>();
     ws.tile_counters = ctr.as<unsigned int>();
+    ws.events = events;
     KeyT *keys[2] = {a.as<KeyT>(), b.as<KeyT>()};
     uint32_t *vals[2] = {va ? va->as<uint32_t>() : nullptr, vb ? vb->as<uint32_t>() : nullptr};
     int cur = radix_sort<KeyT>(keys, va ? vals : nullptr, n, plan, ws, s, launches);
@@ -400,7 +413,7 @@ void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const S
 // extraction + sort + unique/count (+ rc completion): KmerCollector::data()
 // (kmer_collector.hpp:94) followed by add_reverse_complements.
 template <typename KeyT>
-void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm) {
+void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nullptr) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const bool counting = ctx->prm.bits_per_count > 0;
@@ -453,8 +466,13 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm) {
     SortPlan plan;
     plan.n = 0;
     plan_add_key_bits(plan, 0, al.K * al.L);
+    if (prof) {
+        prof->npasses = plan.n;
+        prof->n = n;
+        prof->bytes_per_key = 2 * (sizeof(KeyT) + (payload ? 4 : 0));
+    }
     sort_keys<KeyT>(keysA, keysB, payload ? &valsA : nullptr, payload ? &valsB : nullptr, n, plan, s,
-                    &ctx->launches);
+                    &ctx->launches, prof && n ? prof->ev : nullptr);
     if (tm) tm->mark();
 
     // unique: keysA (sorted) -> keysB
@@ -507,7 +525,7 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm) {
 }
 
 template <typename KeyT>
-void build_impl(mtg_ctx *ctx, mtg_chunk *out) {
+void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const uint32_t K = al.K, L = al.L;
@@ -515,7 +533,8 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out) {
     ctx->launches = 0;
     Timer tm(s);
     RealSet rs;
-    collect_reals<KeyT>(ctx, &rs, &tm);   // marks 0..4: start, extract, sort, unique, rc
+    SortProfile prof;
+    collect_reals<KeyT>(ctx, &rs, &tm, &prof);   // marks 0..4: start, extract, sort, unique, rc
     const uint64_t m = rs.m;
     const KeyT *reals = rs.keys.as<KeyT>();
 
@@ -600,15 +619,16 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out) {
 
     // ---- results to pinned host memory ----
     ChunkImpl *impl = new ChunkImpl();
-    size_t hbytes = 8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA + MTG_MAX_K + 16);
+    const size_t arr_words = device_output ? 0 : W_words + last_words + wt_words;
+    size_t hbytes = 8 * (arr_words + MTG_MAX_SIGMA + MTG_MAX_K + 16);
     if (cudaMallocHost(&impl->pinned, hbytes) != cudaSuccess) {
         delete impl;
         throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
     }
     uint64_t *h = (uint64_t *)impl->pinned;
-    MTG_CUDA(cudaMemcpyAsync(h, dW, 8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA),
-                             cudaMemcpyDeviceToHost, s));
-    uint64_t *h_levels = h + W_words + last_words + wt_words + MTG_MAX_SIGMA;
+    MTG_CUDA(cudaMemcpyAsync(h, dW + (device_output ? W_words + last_words + wt_words : 0),
+                             8 * (arr_words + MTG_MAX_SIGMA), cudaMemcpyDeviceToHost, s));
+    uint64_t *h_levels = h + arr_words + MTG_MAX_SIGMA;
     MTG_CUDA(cudaMemcpyAsync(h_levels, d_ctr + 8, 8 * MTG_MAX_K, cudaMemcpyDeviceToHost, s));
     MTG_CUDA(cudaStreamSynchronize(s));
 
@@ -618,10 +638,30 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out) {
     out->k = K - 1;
     out->W_width = al.W_width;
     out->weights_width = ww;
-    out->W = h;
-    out->last = h + W_words;
-    out->weights = counting ? h + W_words + last_words : nullptr;
-    const uint64_t *hF = h + W_words + last_words + wt_words;
+    if (device_output) {
+        out->W = dW;
+        out->last = dLast;
+        out->weights = counting ? dWt : nullptr;
+        out->device_resident = 1;
+        impl->dev = std::move(outbuf);
+    } else {
+        out->W = h;
+        out->last = h + W_words;
+        out->weights = counting ? h + W_words + last_words : nullptr;
+    }
+    const uint64_t *hF = h + arr_words;
+    if (prof.n) {
+        float t = 0;
+        for (int p = 0; p < prof.npasses; ++p) {
+            cudaEventElapsedTime(&t, prof.ev[2 * p], prof.ev[2 * p + 1]);
+            out->ms_onesweep_sum += t;
+        }
+        cudaEventElapsedTime(&t, prof.ev[2 * MAX_SORT_PASSES], prof.ev[2 * MAX_SORT_PASSES + 1]);
+        out->ms_sort_histogram = t;
+        out->n_onesweep = prof.npasses;
+        out->onesweep_bytes_per_key = prof.bytes_per_key;
+        out->onesweep_keys = prof.n;
+    }
     for (uint32_t c = 0; c < al.sigma; ++c) out->F[c] = hF[c];
     out->n_input_kmers = rs.n_input;
     out->n_real = m;
@@ -647,14 +687,14 @@ void clear_ctx(mtg_ctx *ctx) {
 
 extern "C" {
 
-int mtg_build_chunk(mtg_ctx *ctx, mtg_chunk *out) {
+static int build_chunk_common(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     if (!ctx || !out) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
     std::lock_guard<std::mutex> lk(ctx->mu);
     int rc = MTG_OK;
     try {
         MTG_CUDA(cudaSetDevice(ctx->device));
-        if (ctx->al.K * ctx->al.L <= 64) build_impl<uint64_t>(ctx, out);
-        else build_impl<u128>(ctx, out);
+        if (ctx->al.K * ctx->al.L <= 64) build_impl<uint64_t>(ctx, out, device_output);
+        else build_impl<u128>(ctx, out, device_output);
     } catch (const CudaError &e) {
         rc = fail_cuda(ctx, e);
         cudaStreamSynchronize(ctx->stream);
@@ -663,10 +703,23 @@ int mtg_build_chunk(mtg_ctx *ctx, mtg_chunk *out) {
     return rc;
 }
 
+int mtg_build_chunk(mtg_ctx *ctx, mtg_chunk *out) { return build_chunk_common(ctx, out, false); }
+int mtg_build_chunk_device(mtg_ctx *ctx, mtg_chunk *out) { return build_chunk_common(ctx, out, true); }
+
+int mtg_set_stream(mtg_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (!ctx->segs.empty()) return fail(ctx, MTG_ERR_STATE, "mtg_set_stream must precede the first push");
+    cudaStreamSynchronize(ctx->stream);
+    ctx->stream = cuda_stream ? (cudaStream_t)cuda_stream : ctx->own_stream;
+    return MTG_OK;
+}
+
 void mtg_free_chunk(mtg_chunk *chunk) {
     if (!chunk || !chunk->impl) return;
     ChunkImpl *impl = (ChunkImpl *)chunk->impl;
     if (impl->pinned) cudaFreeHost(impl->pinned);
+    impl->dev.release();
     delete impl;
     chunk->impl = nullptr;
     chunk->W = chunk->last = chunk->weights = nullptr;

@@ -220,7 +220,9 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         size_t sh = sizeof(unsigned int) * plan.n * RADIX;
         auto kern = sort_histogram_kernel<KeyT, HAS_VAL>;
         MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sh));
+        if (ws.events) cudaEventRecord(ws.events[2 * MAX_SORT_PASSES], stream);
         kern<<<grid, 512, sh, stream>>>(keys[0], vals ? vals[0] : nullptr, n, plan, ws.hist);
+        if (ws.events) cudaEventRecord(ws.events[2 * MAX_SORT_PASSES + 1], stream);
         sort_scan_hist_kernel<<<plan.n, RADIX, 0, stream>>>(ws.hist);
         *launches += 2;
     }
@@ -231,10 +233,12 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
     MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int cur = 0;
     for (int p = 0; p < plan.n; ++p) {
+        if (ws.events) cudaEventRecord(ws.events[2 * p], stream);
         kern<<<(unsigned)tiles, THREADS, smem, stream>>>(
             keys[cur], keys[cur ^ 1], HAS_VAL ? vals[cur] : nullptr, HAS_VAL ? vals[cur ^ 1] : nullptr,
             n, plan.p[p], ws.hist + (size_t)p * RADIX, ws.status, ws.tile_counters + p,
             (unsigned)(p + 1));
+        if (ws.events) cudaEventRecord(ws.events[2 * p + 1], stream);
         *launches += 1;
         cur ^= 1;
     }

@@ -36,6 +36,8 @@ struct SortWorkspace {
     size_t status_words = 0;
     unsigned long long *hist = nullptr;     // [MAX_SORT_PASSES * RADIX] digit offsets
     unsigned int *tile_counters = nullptr;  // [MAX_SORT_PASSES]
+    // optional profiling: [2p], [2p+1] bracket pass p; [2*MAX], [2*MAX+1] the histogram
+    cudaEvent_t *events = nullptr;
 };
 
 template <typename KeyT> struct SortTile;
