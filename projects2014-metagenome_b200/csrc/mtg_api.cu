@@ -5,6 +5,8 @@
 #include <algorithm>
 #include <cstring>
 #include <deque>
+#include <map>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -19,27 +21,103 @@ namespace {
 
 thread_local std::string g_create_error;
 
-struct DevBuf {   // stream-ordered device allocation
+// Device memory arena: a few large cudaMalloc slabs kept for the lifetime of the context,
+// carved first-fit with coalescing. All work of a context is ordered on one stream, so a
+// block can be reused as soon as it is released. (The CUDA stream-ordered pool showed
+// 100+ ms stalls whenever it had to grow or re-map multi-GB blocks.)
+struct Arena {
+    struct Slab { char *base; size_t size; };
+    std::vector<Slab> slabs;
+    std::map<char *, size_t> free_blocks;   // start -> size
+    std::map<char *, size_t> used;          // start -> size
+    std::mutex mu;
+    size_t total = 0;
+    static constexpr size_t ALIGN = 512;
+
+    void *alloc(size_t n) {
+        n = (std::max<size_t>(n, 1) + ALIGN - 1) & ~(ALIGN - 1);
+        std::lock_guard<std::mutex> lk(mu);
+        for (int attempt = 0; attempt < 2; ++attempt) {
+            // best fit
+            auto best = free_blocks.end();
+            for (auto it = free_blocks.begin(); it != free_blocks.end(); ++it)
+                if (it->second >= n && (best == free_blocks.end() || it->second < best->second)) best = it;
+            if (best != free_blocks.end()) {
+                char *p = best->first;
+                size_t sz = best->second;
+                free_blocks.erase(best);
+                if (sz > n) free_blocks[p + n] = sz - n;
+                used[p] = n;
+                return p;
+            }
+            // grow: one new slab (at least 256 MB, or the request)
+            size_t want = std::max<size_t>(n, (size_t)256 << 20);
+            void *p = nullptr;
+            cudaError_t e = cudaMalloc(&p, want);
+            if (e != cudaSuccess && want > n) { cudaGetLastError(); want = n; e = cudaMalloc(&p, want); }
+            if (e != cudaSuccess) { cudaGetLastError(); throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__}; }
+            slabs.push_back(Slab{(char *)p, want});
+            total += want;
+            free_blocks[(char *)p] = want;
+        }
+        throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
+    }
+    void free(void *ptr) {
+        if (!ptr) return;
+        std::lock_guard<std::mutex> lk(mu);
+        char *p = (char *)ptr;
+        auto u = used.find(p);
+        if (u == used.end()) return;
+        size_t n = u->second;
+        used.erase(u);
+        auto it = free_blocks.emplace(p, n).first;
+        // coalesce with the next / previous block when they are adjacent in the same slab
+        auto same_slab = [&](char *a, char *b) {
+            for (auto &sl : slabs)
+                if (a >= sl.base && a < sl.base + sl.size) return b >= sl.base && b < sl.base + sl.size;
+            return false;
+        };
+        auto nx = std::next(it);
+        if (nx != free_blocks.end() && it->first + it->second == nx->first && same_slab(it->first, nx->first)) {
+            it->second += nx->second;
+            free_blocks.erase(nx);
+        }
+        if (it != free_blocks.begin()) {
+            auto pv = std::prev(it);
+            if (pv->first + pv->second == it->first && same_slab(pv->first, it->first)) {
+                pv->second += it->second;
+                free_blocks.erase(it);
+            }
+        }
+    }
+    ~Arena() {
+        for (auto &sl : slabs) cudaFree(sl.base);
+    }
+};
+
+thread_local std::shared_ptr<Arena> t_arena;   // arena of the context the thread works for
+
+struct DevBuf {   // arena-backed device allocation (stream-ordered by construction)
     void *p = nullptr;
     size_t bytes = 0;
-    cudaStream_t s = nullptr;
+    std::shared_ptr<Arena> arena;
     DevBuf() {}
     DevBuf(size_t n, cudaStream_t st) { alloc(n, st); }
     DevBuf(const DevBuf &) = delete;
     DevBuf &operator=(const DevBuf &) = delete;
-    DevBuf(DevBuf &&o) noexcept { p = o.p; bytes = o.bytes; s = o.s; o.p = nullptr; }
+    DevBuf(DevBuf &&o) noexcept { p = o.p; bytes = o.bytes; arena = std::move(o.arena); o.p = nullptr; }
     DevBuf &operator=(DevBuf &&o) noexcept {
-        if (this != &o) { release(); p = o.p; bytes = o.bytes; s = o.s; o.p = nullptr; }
+        if (this != &o) { release(); p = o.p; bytes = o.bytes; arena = std::move(o.arena); o.p = nullptr; }
         return *this;
     }
-    void alloc(size_t n, cudaStream_t st) {
+    void alloc(size_t n, cudaStream_t) {
         release();
-        s = st;
+        arena = t_arena;
         bytes = n ? n : 16;
-        MTG_CUDA(cudaMallocAsync(&p, bytes, s));
+        p = arena->alloc(bytes);
     }
     void release() {
-        if (p) cudaFreeAsync(p, s);
+        if (p && arena) arena->free(p);
         p = nullptr;
     }
     ~DevBuf() { release(); }
@@ -64,8 +142,45 @@ struct ReadSegment {
 
 struct ChunkImpl {
     void *pinned = nullptr;
+    size_t pinned_bytes = 0;
     DevBuf dev;
 };
+
+// Small process-wide cache of pinned result buffers (pinning hundreds of MB per build
+// costs more than the build itself).
+struct PinnedCache {
+    std::mutex mu;
+    std::vector<std::pair<void *, size_t>> free_list;
+    void *acquire(size_t bytes, size_t *got) {
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            for (size_t i = 0; i < free_list.size(); ++i)
+                if (free_list[i].second >= bytes) {
+                    void *p = free_list[i].first;
+                    *got = free_list[i].second;
+                    free_list.erase(free_list.begin() + i);
+                    return p;
+                }
+        }
+        void *p = nullptr;
+        if (cudaMallocHost(&p, bytes) != cudaSuccess) { cudaGetLastError(); return nullptr; }
+        *got = bytes;
+        return p;
+    }
+    void release(void *p, size_t bytes) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (free_list.size() >= 2) {   // keep the two largest
+            size_t mi = 0;
+            for (size_t i = 1; i < free_list.size(); ++i)
+                if (free_list[i].second < free_list[mi].second) mi = i;
+            if (free_list[mi].second >= bytes) { cudaFreeHost(p); return; }
+            cudaFreeHost(free_list[mi].first);
+            free_list.erase(free_list.begin() + mi);
+        }
+        free_list.emplace_back(p, bytes);
+    }
+};
+PinnedCache g_pinned_cache;
 
 }  // namespace
 
@@ -79,6 +194,7 @@ struct mtg_ctx {
     std::mutex mu;
     std::vector<ReadSegment> segs;
     std::deque<PinnedBuf> pinned;
+    std::shared_ptr<Arena> arena = std::make_shared<Arena>();
     bool any_explicit_counts = false;
     uint32_t cmax = 0;   // container count type max (boss_chunk_construct.cpp:1147-1160)
     std::string error;
@@ -224,10 +340,6 @@ int mtg_create(const mtg_params *p, mtg_ctx **out) {
         }
         MTG_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
         ctx->stream = ctx->own_stream;
-        cudaMemPool_t pool;
-        MTG_CUDA(cudaDeviceGetDefaultMemPool(&pool, ctx->device));
-        uint64_t thr = UINT64_MAX;
-        MTG_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr));
     } catch (const CudaError &e) {
         int rc = fail_cuda(nullptr, e);
         delete ctx;
@@ -269,6 +381,7 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
     const uint32_t K = ctx->al.K;
     try {
         MTG_CUDA(cudaSetDevice(ctx->device));
+        t_arena = ctx->arena;
         // split very large pushes so that packing and H2D overlap
         const size_t CHUNK = (size_t)64 << 20;
         size_t r0 = 0;
@@ -621,7 +734,8 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     ChunkImpl *impl = new ChunkImpl();
     const size_t arr_words = device_output ? 0 : W_words + last_words + wt_words;
     size_t hbytes = 8 * (arr_words + MTG_MAX_SIGMA + MTG_MAX_K + 16);
-    if (cudaMallocHost(&impl->pinned, hbytes) != cudaSuccess) {
+    impl->pinned = g_pinned_cache.acquire(hbytes, &impl->pinned_bytes);
+    if (!impl->pinned) {
         delete impl;
         throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
     }
@@ -693,6 +807,7 @@ static int build_chunk_common(mtg_ctx *ctx, mtg_chunk *out, bool device_output) 
     int rc = MTG_OK;
     try {
         MTG_CUDA(cudaSetDevice(ctx->device));
+        t_arena = ctx->arena;
         if (ctx->al.K * ctx->al.L <= 64) build_impl<uint64_t>(ctx, out, device_output);
         else build_impl<u128>(ctx, out, device_output);
     } catch (const CudaError &e) {
@@ -718,7 +833,7 @@ int mtg_set_stream(mtg_ctx *ctx, void *cuda_stream) {
 void mtg_free_chunk(mtg_chunk *chunk) {
     if (!chunk || !chunk->impl) return;
     ChunkImpl *impl = (ChunkImpl *)chunk->impl;
-    if (impl->pinned) cudaFreeHost(impl->pinned);
+    if (impl->pinned) g_pinned_cache.release(impl->pinned, impl->pinned_bytes);
     impl->dev.release();
     delete impl;
     chunk->impl = nullptr;
@@ -731,6 +846,7 @@ int mtg_debug_sorted_kmers(mtg_ctx *ctx, uint64_t **words, uint32_t **counts, ui
     int rc = MTG_OK;
     try {
         MTG_CUDA(cudaSetDevice(ctx->device));
+        t_arena = ctx->arena;
         RealSet rs;
         const bool wide = ctx->al.K * ctx->al.L > 64;
         if (wide) collect_reals<u128>(ctx, &rs, nullptr);
@@ -766,6 +882,7 @@ void mtg_debug_free(void *p) { free(p); }
 static int debug_sort(int device, void *keys, uint32_t *vals, uint64_t n, uint32_t key_bits, bool wide) {
     try {
         MTG_CUDA(cudaSetDevice(device));
+        t_arena = std::make_shared<Arena>();
         cudaStream_t s;
         MTG_CUDA(cudaStreamCreate(&s));
         {
@@ -788,6 +905,7 @@ static int debug_sort(int device, void *keys, uint32_t *vals, uint64_t n, uint32
         }
         cudaStreamSynchronize(s);
         cudaStreamDestroy(s);
+        t_arena.reset();
     } catch (const CudaError &e) {
         return fail_cuda(nullptr, e);
     }
