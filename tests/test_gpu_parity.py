@@ -195,3 +195,19 @@ def test_errors():
         mtg_b200.BOSSChunkConstructor.initialize(20, bits_per_count=33)
     with pytest.raises(mtg_b200.MtgError):
         mtg_b200.BOSSChunkConstructor.initialize(20, both_strands=True, alphabet="Protein")
+
+
+# ---- golden vectors of the reference's own implementation (tests/golden/*.npz) ----
+
+from golden_cases import CASES, case_reads  # noqa: E402
+from test_oracle_golden import assert_chunk_equals_golden, load_golden  # noqa: E402
+
+
+@pytest.mark.parametrize("name", sorted(n for n in CASES if not CASES[n].get("suffix")))
+def test_gpu_matches_reference_golden(name):
+    case = CASES[name]
+    reads, counts = case_reads(case)
+    chunk = gpu_build(reads, case["K"], case.get("alphabet", "DNA"), case.get("canonical", False),
+                      case.get("bpc", 0), counts)
+    res = {"W": chunk.W, "last": chunk.last, "F": chunk.F, "weights": chunk.weights}
+    assert_chunk_equals_golden(res, load_golden(name), case.get("bpc", 0))
