@@ -134,6 +134,11 @@ int mtg_debug_sort_u64(int device, uint64_t *keys, uint32_t *vals /*nullable*/, 
 int mtg_debug_sort_u128(int device, uint64_t *keys_lohi, uint32_t *vals /*nullable*/, uint64_t n,
                         uint32_t key_bits);
 
+/* Device-resident timing of the radix sort alone on n pseudo-random keys of key_bits bits
+ * (tuning aid): ms_out[0] = digit-histogram kernel, [1] = mean onesweep pass, [2] = whole sort. */
+int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_vals, int iters,
+                         float *ms_out);
+
 #ifdef __cplusplus
 }
 #endif

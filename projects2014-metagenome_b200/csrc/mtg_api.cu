@@ -912,6 +912,59 @@ static int debug_sort(int device, void *keys, uint32_t *vals, uint64_t n, uint32
     return MTG_OK;
 }
 
+// Device-resident timing of the radix sort alone on pseudo-random keys (sort tuning):
+// ms_out[0] = histogram kernel, ms_out[1] = mean onesweep pass, ms_out[2] = whole sort; best of iters.
+int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_vals, int iters,
+                         float *ms_out) {
+    const bool wide = key_bits > 64;
+    try {
+        MTG_CUDA(cudaSetDevice(device));
+        t_arena = std::make_shared<Arena>();
+        cudaStream_t s;
+        MTG_CUDA(cudaStreamCreate(&s));
+        {
+            size_t kb = wide ? 16 : 8;
+            DevBuf a(kb * n, s), b(kb * n, s), va, vb;
+            if (with_vals) { va.alloc(4 * n, s); vb.alloc(4 * n, s); }
+            SortPlan plan;
+            plan.n = 0;
+            plan_add_key_bits(plan, 0, key_bits);
+            uint32_t top = wide ? key_bits - 64 : key_bits;
+            uint64_t hi_mask = top >= 64 ? ~0ull : ((1ull << top) - 1);
+            cudaEvent_t ev[2 * MAX_SORT_PASSES + 2], e0, e1;
+            for (auto &e : ev) cudaEventCreate(&e);
+            cudaEventCreate(&e0); cudaEventCreate(&e1);
+            ms_out[0] = ms_out[1] = ms_out[2] = 1e30f;
+            for (int it = 0; it < iters; ++it) {
+                DevBuf &cur = a;
+                fill_random_words(cur.as<uint64_t>(), n * (wide ? 2 : 1), it + 1, hi_mask, wide, s);
+                if (with_vals) fill_random_words(va.as<uint64_t>(), n / 2, it + 7, ~0ull, false, s);
+                unsigned launches = 0;
+                cudaEventRecord(e0, s);
+                if (wide) sort_keys<u128>(a, b, with_vals ? &va : nullptr, with_vals ? &vb : nullptr, n, plan, s, &launches, ev);
+                else sort_keys<uint64_t>(a, b, with_vals ? &va : nullptr, with_vals ? &vb : nullptr, n, plan, s, &launches, ev);
+                cudaEventRecord(e1, s);
+                MTG_CUDA(cudaStreamSynchronize(s));
+                float t = 0, sum = 0;
+                for (int p = 0; p < plan.n; ++p) { cudaEventElapsedTime(&t, ev[2 * p], ev[2 * p + 1]); sum += t; }
+                ms_out[1] = std::min(ms_out[1], sum / plan.n);
+                cudaEventElapsedTime(&t, ev[2 * MAX_SORT_PASSES], ev[2 * MAX_SORT_PASSES + 1]);
+                ms_out[0] = std::min(ms_out[0], t);
+                cudaEventElapsedTime(&t, e0, e1);
+                ms_out[2] = std::min(ms_out[2], t);
+            }
+            for (auto &e : ev) cudaEventDestroy(e);
+            cudaEventDestroy(e0); cudaEventDestroy(e1);
+        }
+        cudaStreamSynchronize(s);
+        cudaStreamDestroy(s);
+        t_arena.reset();
+    } catch (const CudaError &e) {
+        return fail_cuda(nullptr, e);
+    }
+    return MTG_OK;
+}
+
 int mtg_debug_sort_u64(int device, uint64_t *keys, uint32_t *vals, uint64_t n, uint32_t key_bits) {
     return debug_sort(device, keys, vals, n, key_bits, false);
 }

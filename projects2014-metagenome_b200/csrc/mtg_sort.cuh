@@ -44,10 +44,13 @@ template <typename KeyT> struct SortTile;
 template <> struct SortTile<uint64_t> { static constexpr int THREADS = 256, IPT = 16; };
 template <> struct SortTile<u128> { static constexpr int THREADS = 256, IPT = 8; };
 
+size_t sort_tile_keys(bool wide);
+// test/bench helper: pseudo-random words (top word of every key masked with hi_mask)
+void fill_random_words(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask, bool wide,
+                       cudaStream_t stream);   // keys per tile of the active kernel configuration
 template <typename KeyT>
 size_t sort_status_words(uint64_t n) {
-    size_t tile = SortTile<KeyT>::THREADS * SortTile<KeyT>::IPT;
-    return (div_up(n, tile) + 1) * RADIX;
+    return (div_up(n, sort_tile_keys(sizeof(KeyT) > 8)) + 1) * RADIX;
 }
 
 // Sorts n keys (with optional 32-bit values). keys[0]/vals[0] hold the input; the
