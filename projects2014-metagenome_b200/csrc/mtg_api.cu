@@ -3,6 +3,7 @@
 // (boss_chunk_construct.cpp:948-1048, kmer/kmer_collector.cpp:129-234) and of
 // construct_boss_chunk (boss_chunk_construct.cpp:248-356).
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <map>
@@ -579,38 +580,87 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
     SortPlan plan;
     plan.n = 0;
     plan_add_key_bits(plan, 0, al.K * al.L);
+    // Sequencing inputs repeat every k-mer ~coverage times. An LSD sort over the low `split`
+    // bits already brings the copies of a k-mer next to each other once 2^split >> n (equal keys
+    // share every digit and the passes are stable), so adjacent duplicates are folded (counts
+    // summed, saturating) after the low passes and the high passes run on the folded array.
+    // Folding adjacent equal keys is always safe; the final unique/count-reduce completes it.
+    int split_pass = 0;
+    {
+        int need_bits = 2;
+        while (need_bits < 64 && (n >> need_bits) != 0) ++need_bits;   // ~log2(n) + 1
+        int p = (need_bits + 1 + RADIX_BITS - 1) / RADIX_BITS;
+        const char *mn = getenv("MTG_MIDSORT_MIN");   // tests force the folded path on small inputs
+        const uint64_t min_n = mn ? strtoull(mn, nullptr, 10) : (1ull << 22);
+        if (n >= min_n && n > 0 && p < plan.n) split_pass = p;
+    }
+    SortPlan plan_lo = plan, plan_hi;
+    plan_hi.n = 0;
+    if (split_pass) {
+        plan_lo.n = split_pass;
+        for (int p = split_pass; p < plan.n; ++p) plan_hi.p[plan_hi.n++] = plan.p[p];
+    }
     if (prof) {
-        prof->npasses = plan.n;
+        prof->npasses = plan_lo.n;
         prof->n = n;
         prof->bytes_per_key = 2 * (sizeof(KeyT) + (payload ? 4 : 0));
     }
-    sort_keys<KeyT>(keysA, keysB, payload ? &valsA : nullptr, payload ? &valsB : nullptr, n, plan, s,
+    sort_keys<KeyT>(keysA, keysB, payload ? &valsA : nullptr, payload ? &valsB : nullptr, n, plan_lo, s,
                     &ctx->launches, prof && n ? prof->ev : nullptr);
-    if (tm) tm->mark();
 
-    // unique: keysA (sorted) -> keysB
-    DevBuf starts;
-    if (counting) starts.alloc(8 * (n + 1), s);
-    {
-        DevBuf status(sizeof(unsigned long long) * unique_status_words(n), s);
+    auto fold = [&](DevBuf &src, uint64_t cnt, DevBuf &dst, const uint32_t *src_vals, DevBuf *dst_counts,
+                    uint64_t counts_cap) -> uint64_t {
+        // dst = distinct adjacent keys of src; *dst_counts = saturating run sums (counting mode)
+        DevBuf starts;
+        if (counting) starts.alloc(8 * (cnt + 1), s);
+        DevBuf status(sizeof(unsigned long long) * unique_status_words(cnt), s);
         DevBuf tctr(sizeof(unsigned int), s);
-        unique_keys<KeyT>(keysA.as<KeyT>(), n, keysB.as<KeyT>(), counting ? starts.as<uint64_t>() : nullptr,
+        unique_keys<KeyT>(src.as<KeyT>(), cnt, dst.as<KeyT>(), counting ? starts.as<uint64_t>() : nullptr,
                           d_ctr + 1, status.as<unsigned long long>(), tctr.as<unsigned int>(), s,
                           &ctx->launches);
-    }
-    const uint64_t m = read_counter(d_ctr + 1, s);
-    keysA.release();
+        const uint64_t out = read_counter(d_ctr + 1, s);
+        if (counting) {
+            dst_counts->alloc(4 * std::max<uint64_t>(counts_cap ? counts_cap : out, 1), s);
+            run_counts(starts.as<uint64_t>(), src_vals, out, ctx->cmax, dst_counts->as<uint32_t>(), s,
+                       &ctx->launches);
+        }
+        return out;
+    };
+
     const bool canon = ctx->prm.both_strands != 0;
-    const uint64_t cap = canon ? 2 * m : m;
+    uint64_t m = 0;
     DevBuf counts;
-    if (counting) {
-        counts.alloc(4 * cap, s);
-        run_counts(starts.as<uint64_t>(), payload ? valsA.as<uint32_t>() : nullptr, m, ctx->cmax,
-                   counts.as<uint32_t>(), s, &ctx->launches);
+    if (split_pass) {
+        DevBuf c1, c1b;
+        const uint64_t m1 = fold(keysA, n, keysB, payload ? valsA.as<uint32_t>() : nullptr, &c1, 0);
+        valsA.release();
+        valsB.release();
+        if (counting) c1b.alloc(4 * std::max<uint64_t>(m1, 1), s);
+        if (tm) tm->mark();   // "sort" = low passes + fold; the high passes are booked under "unique"
+        sort_keys<KeyT>(keysB, keysA, counting ? &c1 : nullptr, counting ? &c1b : nullptr, m1, plan_hi, s,
+                        &ctx->launches);
+        c1b.release();
+        m = fold(keysB, m1, keysA, counting ? c1.as<uint32_t>() : nullptr, &counts, 0);
+        keysB.release();
+        if (canon && counting) {   // room for the reverse complements
+            DevBuf grown(4 * 2 * std::max<uint64_t>(m, 1), s);
+            MTG_CUDA(cudaMemcpyAsync(grown.p, counts.p, 4 * m, cudaMemcpyDeviceToDevice, s));
+            counts = std::move(grown);
+        }
+        std::swap(keysA, keysB);   // result in keysB, like the single-sort path
+    } else {
+        if (tm) tm->mark();
+        m = fold(keysA, n, keysB, payload ? valsA.as<uint32_t>() : nullptr, &counts, 0);
+        keysA.release();
+        valsA.release();
+        valsB.release();
+        if (canon && counting) {
+            DevBuf grown(4 * 2 * std::max<uint64_t>(m, 1), s);
+            MTG_CUDA(cudaMemcpyAsync(grown.p, counts.p, 4 * m, cudaMemcpyDeviceToDevice, s));
+            counts = std::move(grown);
+        }
     }
-    starts.release();
-    valsA.release();
-    valsB.release();
+    const uint64_t cap = canon ? 2 * m : m;
     if (tm) tm->mark();
 
     if (!canon) {

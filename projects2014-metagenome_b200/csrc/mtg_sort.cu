@@ -397,7 +397,7 @@ onesweep_pass_v2_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
 //   * rank = running per-warp digit offset (already holding the tile position) + popc(peers
 //     below my lane): stable, deterministic, no dependence on atomic ordering.
 // ---------------------------------------------------------------------------
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB>
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out_keys,
                         const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
@@ -508,16 +508,20 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     // ---- decoupled look-back per digit ----
     if (tid < RADIX) {
         unsigned long long excl = 0;
-        if (tile > 0) {
-            long long t = (long long)tile - 1;
-            while (true) {
-                unsigned long long s = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
-                unsigned flag = (unsigned)(s >> 62);
-                if (flag == 0 || ((s >> 56) & 63) != epoch) continue;   // not published yet
-                excl += s & OS_VALUE_MASK;
-                if (flag == 2) break;
-                --t;
+        if (LB == 0) {
+            if (tile > 0) {
+                long long t = (long long)tile - 1;
+                while (true) {
+                    unsigned long long s = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
+                    unsigned flag = (unsigned)(s >> 62);
+                    if (flag == 0 || ((s >> 56) & 63) != epoch) continue;   // not published yet
+                    excl += s & OS_VALUE_MASK;
+                    if (flag == 2) break;
+                    --t;
+                }
             }
+        } else {
+            excl = lookback_digit<(LB > 0 ? LB : 1)>(status, tile, tid, epoch);
         }
         st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(2, epoch, excl + count));
         goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
@@ -536,7 +540,7 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     }
 }
 
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB>
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
 void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
                uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
                unsigned int *ctr, unsigned epoch, cudaStream_t stream) {
@@ -544,7 +548,7 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
     size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
                   + 2 * sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
                   + sizeof(uint32_t) * (THREADS / 32 + 1);
-    auto kern = onesweep_pass_v3_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB>;
+    auto kern = onesweep_pass_v3_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB, LB>;
     static bool attr_set = false;
     if (!attr_set) {
         MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -559,7 +563,7 @@ static int sort_variant() {
     static int v = -1;
     if (v < 0) {
         const char *e = getenv("MTG_SORT_VARIANT");
-        v = e ? atoi(e) : 0;
+        v = e ? atoi(e) : 20;
     }
     return v;
 }
@@ -588,7 +592,6 @@ static int variant_tile(int v) {
     constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;   // u128 tiles hold half the keys
     switch (v) {
         case 5: case 22: return 8192 / S;
-        case 24: return 2048 / S;
         case 6: return 2048 / S;
         default: return 4096 / S;
     }
@@ -646,15 +649,17 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         k1<<<(unsigned)tiles, THREADS, smem, stream>>>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, \
                                                       ctr, ep);                                      \
     } while (0)
-#define V3(T, I, B) launch_v3<KeyT, HAS_VAL, T, I / S, B>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
+#define V3(T, I, B, LBW) launch_v3<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
 #define V2(T, I, B, LBW) launch_v2<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
         switch (variant) {
             case 1: V1(4, 1); break;
-            case 20: V3(256, 16, 3); break;
-            case 21: V3(256, 16, 4); break;
-            case 22: V3(512, 16, 2); break;
-            case 23: V3(512, 8, 3); break;
-            case 24: V3(256, 8, 6); break;
+            case 20: V3(256, 16, 3, 0); break;
+            case 21: V3(256, 16, 4, 0); break;
+            case 22: V3(512, 16, 2, 0); break;
+            case 25: V3(256, 16, 3, 4); break;
+            case 26: V3(256, 16, 3, 8); break;
+            case 27: V3(256, 16, 3, 16); break;
+            case 28: V3(256, 16, 3, 2); break;
             case 8: V1(1, 3); break;
             case 14: V1(0, 3); break;
             case 15: V1(0, 3, 1); break;

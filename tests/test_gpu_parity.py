@@ -211,3 +211,20 @@ def test_gpu_matches_reference_golden(name):
                       case.get("bpc", 0), counts)
     res = {"W": chunk.W, "last": chunk.last, "F": chunk.F, "weights": chunk.weights}
     assert_chunk_equals_golden(res, load_golden(name), case.get("bpc", 0))
+
+
+# ---- mid-sort folding of adjacent duplicates (large-input path, forced on small inputs) ----
+
+@pytest.mark.parametrize("K,canonical,bpc,explicit", [(31, True, 0, False), (31, False, 8, False),
+                                                       (25, True, 12, True), (63, True, 8, False),
+                                                       (40, False, 0, False), (12, False, 2, False)])
+def test_midsort_fold_path(K, canonical, bpc, explicit, monkeypatch):
+    monkeypatch.setenv("MTG_MIDSORT_MIN", "1")
+    reads = dna_reads(K + bpc, 2500, 110, 3000, e=0.004)   # ~80x coverage: many duplicates
+    counts = None
+    if explicit:
+        counts = np.random.default_rng(3).integers(1, 300, len(reads)).astype(np.uint64)
+    c = check(reads, K, canonical=canonical, bits_per_count=bpc, counts=counts)
+    monkeypatch.setenv("MTG_MIDSORT_MIN", str(1 << 60))
+    d = check(reads, K, canonical=canonical, bits_per_count=bpc, counts=counts)
+    assert np.array_equal(c.W_words, d.W_words)
