@@ -642,11 +642,6 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
         c1b.release();
         m = fold(keysB, m1, keysA, counting ? c1.as<uint32_t>() : nullptr, &counts, 0);
         keysB.release();
-        if (canon && counting) {   // room for the reverse complements
-            DevBuf grown(4 * 2 * std::max<uint64_t>(m, 1), s);
-            MTG_CUDA(cudaMemcpyAsync(grown.p, counts.p, 4 * m, cudaMemcpyDeviceToDevice, s));
-            counts = std::move(grown);
-        }
         std::swap(keysA, keysB);   // result in keysB, like the single-sort path
     } else {
         if (tm) tm->mark();
@@ -654,11 +649,6 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
         keysA.release();
         valsA.release();
         valsB.release();
-        if (canon && counting) {
-            DevBuf grown(4 * 2 * std::max<uint64_t>(m, 1), s);
-            MTG_CUDA(cudaMemcpyAsync(grown.p, counts.p, 4 * m, cudaMemcpyDeviceToDevice, s));
-            counts = std::move(grown);
-        }
     }
     const uint64_t cap = canon ? 2 * m : m;
     if (tm) tm->mark();
@@ -670,20 +660,33 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
         if (tm) tm->mark();
         return;
     }
-    // canonical: append reverse complements, sort the union
-    DevBuf r0(sizeof(KeyT) * cap, s), r1(sizeof(KeyT) * cap, s);
-    MTG_CUDA(cudaMemcpyAsync(r0.p, keysB.p, sizeof(KeyT) * m, cudaMemcpyDeviceToDevice, s));
-    keysB.release();
-    append_reverse_complements<KeyT>(r0.as<KeyT>(), counting ? counts.as<uint32_t>() : nullptr, m, al,
-                                     ctx->cmax, d_ctr + 2, s, &ctx->launches);
-    const uint64_t m2 = m + read_counter(d_ctr + 2, s);
-    DevBuf counts1;
-    if (counting) counts1.alloc(4 * cap, s);
-    sort_keys<KeyT>(r0, r1, counting ? &counts : nullptr, counting ? &counts1 : nullptr, m2, plan, s,
+    // canonical: reverse complements of the non-palindromes, sorted on their own and merged with
+    // the (already sorted) canonical half == add_reverse_complements' re-sort of the doubled array
+    DevBuf rb0(sizeof(KeyT) * std::max<uint64_t>(m, 1), s), rb1(sizeof(KeyT) * std::max<uint64_t>(m, 1), s);
+    DevBuf cb0, cb1;
+    if (counting) { cb0.alloc(4 * std::max<uint64_t>(m, 1), s); cb1.alloc(4 * std::max<uint64_t>(m, 1), s); }
+    append_reverse_complements<KeyT>(keysB.as<KeyT>(), rb0.as<KeyT>(), counting ? counts.as<uint32_t>() : nullptr,
+                                     counting ? cb0.as<uint32_t>() : nullptr, m, al, ctx->cmax, d_ctr + 2, s,
+                                     &ctx->launches);
+    const uint64_t mb = read_counter(d_ctr + 2, s);
+    sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s,
                     &ctx->launches);
-    rs->keys = std::move(r0);
-    rs->counts = std::move(counts);
+    rb1.release();
+    cb1.release();
+    const uint64_t m2 = m + mb;
+    DevBuf merged(sizeof(KeyT) * std::max<uint64_t>(m2, 1), s), merged_counts;
+    if (counting) merged_counts.alloc(4 * std::max<uint64_t>(m2, 1), s);
+    {
+        DevBuf part(8 * merge_partition_words(m2), s);
+        merge_sorted<KeyT>(keysB.as<KeyT>(), m, rb0.as<KeyT>(), mb, counting ? counts.as<uint32_t>() : nullptr,
+                           counting ? cb0.as<uint32_t>() : nullptr, merged.as<KeyT>(),
+                           counting ? merged_counts.as<uint32_t>() : nullptr, part.as<uint64_t>(), s,
+                           &ctx->launches);
+    }
+    rs->keys = std::move(merged);
+    rs->counts = std::move(merged_counts);
     rs->m = m2;
+    (void)cap;
     if (tm) tm->mark();
 }
 
@@ -706,12 +709,19 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     unsigned long long *d_ctr = ctr.as<unsigned long long>();   // [0] sinks [1] sources-1 [8..] levels
     MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64 + 8 * MTG_MAX_K, s));
     uint64_t cap = std::max<uint64_t>(1024, m / 8);
+    DevBuf bidx;
+    const bool use_index = m >= (1u << 16);
+    if (use_index) {
+        bidx.alloc(8 * bucket_index_words(al), s);
+        build_bucket_index<KeyT>(reals, m, al, bidx.as<uint64_t>(), s, &ctx->launches);
+    }
+    const uint64_t *d_bidx = use_index ? bidx.as<uint64_t>() : nullptr;
     DevBuf sink, src, srcB;
     uint64_t n_sink = 0, d1 = 0;
     while (true) {
         sink.alloc(sizeof(KeyT) * cap, s);
         src.alloc(sizeof(KeyT) * cap, s);
-        find_dummy_candidates<KeyT>(reals, m, al, sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap,
+        find_dummy_candidates<KeyT>(reals, m, al, d_bidx, sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap,
                                     d_ctr + 1, s, &ctx->launches);
         n_sink = read_counter(d_ctr, s);
         d1 = read_counter(d_ctr + 1, s);
@@ -757,7 +767,8 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     flip_info(di0.as<uint32_t>(), d, s, &ctx->launches);
     dk1.release(); di1.release();
     DevBuf rank(8 * std::max<uint64_t>(d, 1), s);
-    dummy_ranks<KeyT>(reals, m, dk0.as<KeyT>(), d, al, rank.as<uint64_t>(), s, &ctx->launches);
+    dummy_ranks<KeyT>(reals, m, dk0.as<KeyT>(), d, al, d_bidx, rank.as<uint64_t>(), s, &ctx->launches);
+    bidx.release();
     tm.mark();   // 5: dummies done
 
     // ---- merge + emit ----

@@ -17,6 +17,8 @@ namespace mtg {
 
 namespace {
 
+constexpr int MTG_MAX_LEVELS = 128;   // == MTG_MAX_K (include/mtg_gpu.h)
+
 template <typename KeyT>
 __device__ __forceinline__ uint64_t lower_bound_dev(const KeyT *a, uint64_t n, KeyT x) {
     uint64_t lo = 0, hi = n;
@@ -25,6 +27,33 @@ __device__ __forceinline__ uint64_t lower_bound_dev(const KeyT *a, uint64_t n, K
         if (w_lt(a[mid], x)) lo = mid + 1; else hi = mid;
     }
     return lo;
+}
+
+// Bucket index over the sorted reals: idx[b] = first position whose top B key bits are >= b.
+// A membership probe then searches ~m / 2^B keys instead of m (the probes of neighbouring
+// threads are sorted per leading character, so the index and the bucket stay cache resident).
+struct BucketIndex {
+    const uint64_t *idx;   // [2^B + 1]
+    uint32_t B, shift;     // bucket of x = x >> shift
+};
+template <typename KeyT>
+__device__ __forceinline__ uint64_t lower_bound_idx(const KeyT *a, uint64_t n, BucketIndex bi, KeyT x) {
+    if (!bi.idx) return lower_bound_dev(a, n, x);
+    uint64_t b = w_low64(w_shr(x, bi.shift));
+    uint64_t lo = bi.idx[b], hi = bi.idx[b + 1];
+    while (lo < hi) {
+        uint64_t mid = (lo + hi) >> 1;
+        if (w_lt(a[mid], x)) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+template <typename KeyT>
+__global__ void bucket_index_kernel(const KeyT *__restrict__ a, uint64_t n, uint32_t B, uint32_t shift,
+                                    uint64_t *__restrict__ idx) {
+    uint64_t b = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (b > (1ull << B)) return;
+    if (b == (1ull << B)) { idx[b] = n; return; }
+    idx[b] = lower_bound_dev(a, n, w_shl(WordTraits<KeyT>::from_u64(b), shift));
 }
 
 // append one element per emitting lane through a warp-aggregated atomic
@@ -44,7 +73,7 @@ __device__ __forceinline__ void warp_append(bool emit, KeyT v, KeyT *out, uint64
 
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
-dummy_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al,
+dummy_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, BucketIndex bi,
                         KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink,
                         KeyT *src_fwd, uint64_t src_cap, unsigned long long *d_num_src) {
     using WT = WordTraits<KeyT>;
@@ -67,7 +96,7 @@ dummy_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al,
         if (first) {
             // to_next(K, 0): [s_K, s_{K-1}..s_2 | 0]
             sink = w_and(w_or(w_shr(x, L), w_shl(W, L * (K - 1))), w_not(maskL));
-            uint64_t p = lower_bound_dev(reals, m, sink);
+            uint64_t p = lower_bound_idx(reals, m, bi, sink);
             emit_sink = !(p < m && w_eq(w_shr(reals[p], L), w_shr(sink, L)));
         }
         // ---- source-1: first k-mer of its node? ----
@@ -78,7 +107,7 @@ dummy_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al,
             KeyT top = w_shr(x, L * (K - 1));   // s_{K-1}
             KeyT prev = w_and(w_shl(w_and(x, w_not(maskL)), L), WT::low_mask(L * K));
             KeyT g = w_shr(prev, 2 * L);
-            uint64_t p = lower_bound_dev(reals, m, prev);   // prev has W = 0, x_1 = 0
+            uint64_t p = lower_bound_idx(reals, m, bi, prev);   // prev has W = 0, x_1 = 0
             bool redundant = false;
             for (; p < m; ++p) {
                 KeyT y = reals[p];
@@ -135,38 +164,53 @@ __global__ void generate_source_dummies_kernel(const KeyT *__restrict__ fwd,
                                                uint32_t *__restrict__ out_info,
                                                unsigned long long *level_hist) {
     using WT = WordTraits<KeyT>;
+    __shared__ unsigned int sh_levels[MTG_MAX_LEVELS];   // per-block level histogram
+    for (int c = threadIdx.x; c < MTG_MAX_LEVELS; c += blockDim.x) sh_levels[c] = 0;
+    __syncthreads();
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= d1) return;
     const uint32_t L = al.L, K = al.K, nchars = K - 1;
-    const KeyT maskL = WT::low_mask(L);
-    KeyT f = fwd[i];
-    uint32_t cnt = per_entry[i];
-    uint64_t dst = offsets[i];
-    // char s_t (t = 1..K-1) sits at bit L*(nchars - t) of f
-    for (uint32_t j = nchars - cnt + 1; j <= nchars; ++j) {
-        uint32_t c = K - j;
-        KeyT key = w_and(w_shr(f, L * (nchars - j)), maskL);   // W = s_j
-        for (uint32_t t = 1; t < j; ++t) {
+    if (i < d1) {
+        const KeyT maskL = WT::low_mask(L);
+        KeyT f = fwd[i];
+        uint32_t cnt = per_entry[i];
+        uint64_t dst = offsets[i];
+        // char s_t (t = 1..K-1) sits at bit L*(nchars - t) of f. The dummy with c = K - j leading
+        // '$' is  [s_{j-1} .. s_1 at slots c+j-1 .. c+1 | W = s_j]; going from j to j+1 the node
+        // part moves down one slot and s_j enters at the top: built incrementally.
+        const uint32_t j0 = nchars - cnt + 1;
+        // node part for j0: chars s_1..s_{j0-1}
+        KeyT node = WT::zero();
+        for (uint32_t t = 1; t < j0; ++t) {
             KeyT ch = w_and(w_shr(f, L * (nchars - t)), maskL);
-            key = w_or(key, w_shl(ch, L * (c + t)));
+            node = w_or(node, w_shl(ch, L * (K - j0 + t)));
         }
-        out_keys[dst] = key;
-        out_info[dst] = c;
-        ++dst;
-        atomicAdd(&level_hist[c - 1], 1ull);
+        for (uint32_t j = j0; j <= nchars; ++j) {
+            uint32_t c = K - j;
+            KeyT sj = w_and(w_shr(f, L * (nchars - j)), maskL);   // W = s_j
+            out_keys[dst] = w_or(node, sj);
+            out_info[dst] = c;
+            ++dst;
+            atomicAdd(&sh_levels[c - 1], 1u);
+            // next j: every node char moves one slot down (c shrinks by 1), s_j joins at slot K-1
+            node = w_or(w_shr(node, L), w_shl(sj, L * (K - 1)));
+            node = w_and(node, w_not(maskL));
+        }
     }
+    __syncthreads();
+    for (int c = threadIdx.x; c < MTG_MAX_LEVELS; c += blockDim.x)
+        if (sh_levels[c]) atomicAdd(&level_hist[c], (unsigned long long)sh_levels[c]);
 }
 
 template <typename KeyT>
 __global__ void dummy_ranks_kernel(const KeyT *__restrict__ reals, uint64_t m,
                                    const KeyT *__restrict__ dummy_keys, uint64_t d, Alpha al,
-                                   uint64_t *__restrict__ rank) {
+                                   BucketIndex bi, uint64_t *__restrict__ rank) {
     uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= d) return;
     // '$' sorts before every real character: the dummy precedes all reals that agree
     // with it on the non-'$' leading characters -> lower bound of the zero-filled word
     KeyT probe = w_and(dummy_keys[j], w_not(WordTraits<KeyT>::low_mask(al.L)));
-    rank[j] = lower_bound_dev(reals, m, probe);
+    rank[j] = lower_bound_idx(reals, m, bi, probe);
 }
 
 template <typename KeyT>
@@ -191,37 +235,97 @@ __global__ void merge_dummies_kernel(const KeyT *__restrict__ dummy_keys,
     if (row_counts) row_counts[pos] = 0;
 }
 
+constexpr int MR_THREADS = 256;
+constexpr int MR_TILE = 2048;
+constexpr int MR_CAP = 1024;
+
+// Each block places MR_TILE consecutive reals. The dummies that interleave with them are
+// rank[jlo..jhi): two block-wide searches find the range, the per-real count is a search in
+// shared memory (the range is short: dummies are a few percent of the rows).
 template <typename KeyT>
-__global__ void merge_reals_kernel(const KeyT *__restrict__ reals,
-                                   const uint32_t *__restrict__ real_counts, uint64_t m,
-                                   const uint64_t *__restrict__ rank, uint64_t d,
-                                   KeyT *__restrict__ row_keys, uint8_t *__restrict__ row_info,
-                                   uint32_t *__restrict__ row_counts) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
-    // number of dummies ordered before real i = #{j : rank[j] <= i}
-    uint64_t lo = 0, hi = d;
-    while (lo < hi) {
-        uint64_t mid = (lo + hi) >> 1;
-        if (rank[mid] <= i) lo = mid + 1; else hi = mid;
+__global__ void __launch_bounds__(MR_THREADS)
+merge_reals_kernel(const KeyT *__restrict__ reals, const uint32_t *__restrict__ real_counts, uint64_t m,
+                   const uint64_t *__restrict__ rank, uint64_t d, KeyT *__restrict__ row_keys,
+                   uint8_t *__restrict__ row_info, uint32_t *__restrict__ row_counts) {
+    __shared__ uint64_t s_rank[MR_CAP];
+    __shared__ uint64_t s_range[2];
+    const uint64_t i0 = (uint64_t)blockIdx.x * MR_TILE;
+    const uint64_t i1 = i0 + MR_TILE < m ? i0 + MR_TILE : m;
+    if (threadIdx.x < 2) {
+        // cnt(i) = #{j : rank[j] <= i}; [0] = cnt(i0 - 1), [1] = cnt(i1 - 1)
+        uint64_t lo = 0, hi = d;
+        if (threadIdx.x == 0 && i0 == 0) hi = 0;
+        const uint64_t bound = threadIdx.x == 0 ? i0 - 1 : i1 - 1;
+        while (lo < hi) {
+            uint64_t mid = (lo + hi) >> 1;
+            if (rank[mid] <= bound) lo = mid + 1; else hi = mid;
+        }
+        s_range[threadIdx.x] = lo;
     }
-    uint64_t pos = i + lo + 2;
-    row_keys[pos] = reals[i];
-    row_info[pos] = 0;
-    if (row_counts) row_counts[pos] = real_counts[i];
+    __syncthreads();
+    const uint64_t jlo = s_range[0], jhi = s_range[1];
+    const uint32_t nd = (uint32_t)(jhi - jlo < (uint64_t)MR_CAP + 1 ? jhi - jlo : MR_CAP + 1);
+    const bool in_smem = nd <= MR_CAP;
+    if (in_smem)
+        for (uint32_t t = threadIdx.x; t < nd; t += MR_THREADS) s_rank[t] = rank[jlo + t];
+    __syncthreads();
+    for (uint64_t i = i0 + threadIdx.x; i < i1; i += MR_THREADS) {
+        uint64_t cnt;
+        if (in_smem) {
+            uint32_t lo = 0, hi = nd;
+            while (lo < hi) {
+                uint32_t mid = (lo + hi) >> 1;
+                if (s_rank[mid] <= i) lo = mid + 1; else hi = mid;
+            }
+            cnt = jlo + lo;
+        } else {
+            uint64_t lo = jlo, hi = jhi;
+            while (lo < hi) {
+                uint64_t mid = (lo + hi) >> 1;
+                if (rank[mid] <= i) lo = mid + 1; else hi = mid;
+            }
+            cnt = lo;
+        }
+        uint64_t pos = i + cnt + 2;
+        row_keys[pos] = reals[i];
+        row_info[pos] = 0;
+        if (row_counts) row_counts[pos] = real_counts[i];
+    }
 }
 
 }  // namespace
 
+size_t bucket_index_words(Alpha al) {
+    uint32_t KL = al.K * al.L;
+    uint32_t B = KL < 22 ? KL : 22;
+    return ((size_t)1 << B) + 1;
+}
+static BucketIndex make_bi(Alpha al, const uint64_t *idx) {
+    uint32_t KL = al.K * al.L;
+    uint32_t B = KL < 22 ? KL : 22;
+    return BucketIndex{idx, B, KL - B};
+}
 template <typename KeyT>
-void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, KeyT *sink_keys, uint64_t sink_cap,
+void build_bucket_index(const KeyT *reals, uint64_t m, Alpha al, uint64_t *idx, cudaStream_t stream,
+                        unsigned *launches) {
+    BucketIndex bi = make_bi(al, idx);
+    size_t nthreads = ((size_t)1 << bi.B) + 1;
+    bucket_index_kernel<KeyT><<<(unsigned)div_up(nthreads, (size_t)256), 256, 0, stream>>>(reals, m, bi.B, bi.shift,
+                                                                                        idx);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+template <typename KeyT>
+void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64_t *bucket_idx,
+                           KeyT *sink_keys, uint64_t sink_cap,
                            unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
                            unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches) {
     MTG_CUDA(cudaMemsetAsync(d_num_sink, 0, sizeof(unsigned long long), stream));
     MTG_CUDA(cudaMemsetAsync(d_num_src, 0, sizeof(unsigned long long), stream));
     if (m == 0) return;
     dummy_candidates_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(
-        reals, m, al, sink_keys, sink_cap, d_num_sink, src_fwd, src_cap, d_num_src);
+        reals, m, al, make_bi(al, bucket_idx), sink_keys, sink_cap, d_num_sink, src_fwd, src_cap, d_num_src);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }
@@ -250,10 +354,10 @@ void generate_source_dummies(const KeyT *src_fwd, const uint32_t *per_entry, con
 
 template <typename KeyT>
 void dummy_ranks(const KeyT *reals, uint64_t m, const KeyT *dummy_keys, uint64_t d, Alpha al,
-                 uint64_t *rank, cudaStream_t stream, unsigned *launches) {
+                 const uint64_t *bucket_idx, uint64_t *rank, cudaStream_t stream, unsigned *launches) {
     if (d == 0) return;
-    dummy_ranks_kernel<KeyT><<<(unsigned)div_up(d, (size_t)256), 256, 0, stream>>>(reals, m, dummy_keys,
-                                                                                 d, al, rank);
+    dummy_ranks_kernel<KeyT><<<(unsigned)div_up(d, (size_t)256), 256, 0, stream>>>(
+        reals, m, dummy_keys, d, al, make_bi(al, bucket_idx), rank);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }
@@ -267,7 +371,7 @@ void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, cons
         dummy_keys, dummy_info, rank, d, al.K, row_keys, row_info, row_counts);
     *launches += 1;
     if (m) {
-        merge_reals_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(
+        merge_reals_kernel<KeyT><<<(unsigned)div_up(m, (size_t)MR_TILE), MR_THREADS, 0, stream>>>(
             reals, real_counts, m, rank, d, row_keys, row_info, row_counts);
         *launches += 1;
     }
@@ -275,7 +379,9 @@ void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, cons
 }
 
 #define INSTANTIATE(KeyT)                                                                          \
-    template void find_dummy_candidates<KeyT>(const KeyT *, uint64_t, Alpha, KeyT *, uint64_t,     \
+    template void build_bucket_index<KeyT>(const KeyT *, uint64_t, Alpha, uint64_t *, cudaStream_t, \
+                                           unsigned *);                                           \
+    template void find_dummy_candidates<KeyT>(const KeyT *, uint64_t, Alpha, const uint64_t *, KeyT *, uint64_t, \
                                               unsigned long long *, KeyT *, uint64_t,              \
                                               unsigned long long *, cudaStream_t, unsigned *);     \
     template void source_prefix_counts<KeyT>(const KeyT *, uint64_t, Alpha, uint32_t *,            \
@@ -284,7 +390,7 @@ void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, cons
                                                 uint64_t, Alpha, KeyT *, uint32_t *,               \
                                                 unsigned long long *, cudaStream_t, unsigned *);   \
     template void dummy_ranks<KeyT>(const KeyT *, uint64_t, const KeyT *, uint64_t, Alpha,         \
-                                    uint64_t *, cudaStream_t, unsigned *);                         \
+                                    const uint64_t *, uint64_t *, cudaStream_t, unsigned *);                         \
     template void merge_rows<KeyT>(const KeyT *, const uint32_t *, uint64_t, const KeyT *,         \
                                    const uint32_t *, const uint64_t *, uint64_t, Alpha, KeyT *,    \
                                    uint8_t *, uint32_t *, cudaStream_t, unsigned *);

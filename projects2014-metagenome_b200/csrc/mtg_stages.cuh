@@ -51,13 +51,21 @@ void run_counts(const uint64_t *starts, const uint32_t *vals, uint64_t m, uint32
                 uint32_t *counts, cudaStream_t stream, unsigned *launches);
 
 // ---- K1b reverse-complement completion -----------------------------------
-// keys[0..m) distinct canonical k-mers. Appends rc(x) for every non-palindrome at
-// keys[m + slot] (slot from *d_appended), doubles (saturating at cmax) the counts of
-// palindromes (boss_chunk_construct.cpp:179-222).
+// keys[0..m) distinct canonical k-mers. Writes rc(x) of every non-palindrome to rc_out[slot]
+// (slot from *d_appended, with its count to rc_counts[slot]) and doubles (saturating at cmax)
+// the counts of palindromes (boss_chunk_construct.cpp:179-222).
 template <typename KeyT>
-void append_reverse_complements(KeyT *keys, uint32_t *counts, uint64_t m, Alpha al, uint32_t cmax,
-                                unsigned long long *d_appended, cudaStream_t stream,
-                                unsigned *launches);
+void append_reverse_complements(const KeyT *keys, KeyT *rc_out, uint32_t *counts, uint32_t *rc_counts,
+                                uint64_t m, Alpha al, uint32_t cmax, unsigned long long *d_appended,
+                                cudaStream_t stream, unsigned *launches);
+
+// Merge of two sorted arrays (A first on ties), optional count payloads. `part` is scratch of
+// merge_partition_words(na + nb) u64.
+size_t merge_partition_words(uint64_t n_total);
+template <typename KeyT>
+void merge_sorted(const KeyT *A, uint64_t na, const KeyT *B, uint64_t nb, const uint32_t *Ac,
+                  const uint32_t *Bc, KeyT *out, uint32_t *outc, uint64_t *part, cudaStream_t stream,
+                  unsigned *launches);
 
 // ---- K4 dummy k-mers -----------------------------------------------------
 // Sinks: for every real x that is the first of its (x>>2L, W) class, emit
@@ -66,8 +74,14 @@ void append_reverse_complements(KeyT *keys, uint32_t *counts, uint64_t m, Alpha 
 // forward-lexicographic packing (s_1 most significant, (K-1)*L bits).
 // Both append through atomic counters; if a counter exceeds its capacity the
 // entries beyond are dropped (the driver retries with the exact size).
+// Bucket index over the sorted reals (top min(22, K*L) key bits -> first position), used by the
+// membership probes; bucket_idx may be NULL (plain binary search).
+size_t bucket_index_words(Alpha al);
 template <typename KeyT>
-void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al,
+void build_bucket_index(const KeyT *reals, uint64_t m, Alpha al, uint64_t *idx, cudaStream_t stream,
+                        unsigned *launches);
+template <typename KeyT>
+void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64_t *bucket_idx,
                            KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink,
                            KeyT *src_fwd, uint64_t src_cap, unsigned long long *d_num_src,
                            cudaStream_t stream, unsigned *launches);
@@ -96,7 +110,7 @@ void flip_info(uint32_t *info, uint64_t n, cudaStream_t stream, unsigned *launch
 // rank[j] = #reals ordered before dummy j (dummies sorted in final order).
 template <typename KeyT>
 void dummy_ranks(const KeyT *reals, uint64_t m, const KeyT *dummy_keys, uint64_t d, Alpha al,
-                 uint64_t *rank, cudaStream_t stream, unsigned *launches);
+                 const uint64_t *bucket_idx, uint64_t *rank, cudaStream_t stream, unsigned *launches);
 // rows: [0] placeholder, [1] all-'$', then the merge of reals and dummies.
 template <typename KeyT>
 void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, const KeyT *dummy_keys,

@@ -138,7 +138,8 @@ __device__ __forceinline__ KeyT rc_boss_dna(KeyT x, unsigned K) {
 }
 
 template <typename KeyT>
-__global__ void append_rc_kernel(KeyT *keys, uint32_t *counts, uint64_t m, uint32_t K, uint32_t cmax,
+__global__ void append_rc_kernel(const KeyT *__restrict__ keys, KeyT *__restrict__ rc_out, uint32_t *counts,
+                                 uint32_t *__restrict__ rc_counts, uint64_t m, uint32_t K, uint32_t cmax,
                                  unsigned long long *d_appended) {
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
     bool emit = false;
@@ -159,9 +160,9 @@ __global__ void append_rc_kernel(KeyT *keys, uint32_t *counts, uint64_t m, uint3
     if ((threadIdx.x & 31) == 0) base = atomicAdd(d_appended, (unsigned long long)__popc(bal));
     base = __shfl_sync(0xffffffffu, base, 0);
     if (emit) {
-        uint64_t dst = m + base + __popc(bal & lanemask_lt());
-        keys[dst] = rc;
-        if (counts) counts[dst] = c;
+        uint64_t dst = base + __popc(bal & lanemask_lt());
+        rc_out[dst] = rc;
+        if (counts) rc_counts[dst] = c;
     }
 }
 
@@ -223,19 +224,20 @@ void flip_info(uint32_t *info, uint64_t n, cudaStream_t stream, unsigned *launch
 }
 
 template <typename KeyT>
-void append_reverse_complements(KeyT *keys, uint32_t *counts, uint64_t m, Alpha al, uint32_t cmax,
-                                unsigned long long *d_appended, cudaStream_t stream,
-                                unsigned *launches) {
+void append_reverse_complements(const KeyT *keys, KeyT *rc_out, uint32_t *counts, uint32_t *rc_counts,
+                                uint64_t m, Alpha al, uint32_t cmax, unsigned long long *d_appended,
+                                cudaStream_t stream, unsigned *launches) {
     MTG_CUDA(cudaMemsetAsync(d_appended, 0, sizeof(unsigned long long), stream));
     if (m == 0) return;
-    append_rc_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(keys, counts, m, al.K,
-                                                                               cmax, d_appended);
+    append_rc_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(keys, rc_out, counts, rc_counts,
+                                                                               m, al.K, cmax, d_appended);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }
-template void append_reverse_complements<uint64_t>(uint64_t *, uint32_t *, uint64_t, Alpha, uint32_t,
-                                                   unsigned long long *, cudaStream_t, unsigned *);
-template void append_reverse_complements<u128>(u128 *, uint32_t *, uint64_t, Alpha, uint32_t,
-                                               unsigned long long *, cudaStream_t, unsigned *);
+template void append_reverse_complements<uint64_t>(const uint64_t *, uint64_t *, uint32_t *, uint32_t *,
+                                                   uint64_t, Alpha, uint32_t, unsigned long long *,
+                                                   cudaStream_t, unsigned *);
+template void append_reverse_complements<u128>(const u128 *, u128 *, uint32_t *, uint32_t *, uint64_t, Alpha,
+                                               uint32_t, unsigned long long *, cudaStream_t, unsigned *);
 
 }  // namespace mtg
