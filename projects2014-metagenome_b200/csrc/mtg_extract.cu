@@ -12,6 +12,7 @@
 // The KMerBOSS word is the rotation  ((v << L) & mask) | (v >> L(K-1))
 // (kmer_boss.hpp:17-28) -- no rolling state, no redundant work per window.
 // Canonical mode (DNA, complement = code ^ 3): rc(v) = reverse 2-bit groups of ~v.
+#include "mtg_scan.cuh"
 #include "mtg_stages.cuh"
 
 namespace mtg {
@@ -119,40 +120,50 @@ extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut l
     }
     __syncthreads();
 
-    // ---- windows: each warp owns EX_WPW consecutive window starts ----
+    // ---- window validity bitmap: window p is valid iff no invalid char in [p, p+K) ----
+    // wvalid[q] bit s <-> window 32q+s; computed word-wise by smearing the invalid-char bitmap
+    // over K positions (K <= 97 always: 32 + K - 1 bits fit 128). No warp votes are needed
+    // afterwards: the output slot of a window is prefix[q] + popc(wvalid[q] below my lane).
+    uint32_t *wvalid = inval + ngroups * 2 + 4;          // [EX_TILE / 32]
+    uint32_t *wprefix = wvalid + EX_TILE / 32;           // [EX_TILE / 32]
+    __shared__ uint32_t scan_tmp[EX_THREADS / 32 + 1];
+    __shared__ unsigned long long sh_base;
+    uint32_t my_cnt = 0, w0 = 0, w1 = 0;
+    {
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const uint32_t q = threadIdx.x * 2 + h;
+            unsigned __int128 x = (unsigned __int128)inval[q] | ((unsigned __int128)inval[q + 1] << 32)
+                                  | ((unsigned __int128)inval[q + 2] << 64) | ((unsigned __int128)inval[q + 3] << 96);
+            unsigned __int128 r = x;
+            uint32_t covered = 1;
+            while (covered * 2 <= K) { r |= r >> covered; covered *= 2; }
+            if (K > covered) r |= r >> (K - covered);
+            uint32_t ok = ~(uint32_t)r;
+            if (h == 0) w0 = ok; else w1 = ok;
+            wvalid[q] = ok;
+        }
+        my_cnt = __popc(w0) + __popc(w1);
+    }
+    uint32_t excl = block_exclusive_scan<EX_THREADS>(my_cnt, scan_tmp);
+    wprefix[threadIdx.x * 2] = excl;
+    wprefix[threadIdx.x * 2 + 1] = excl + __popc(w0);
+    const uint32_t block_total = scan_tmp[EX_THREADS / 32];
+    if (threadIdx.x == 0)
+        sh_base = block_total ? atomicAdd(out_counter, (unsigned long long)block_total) : 0ull;
+    __syncthreads();
+    if (block_total == 0) return;
+    const unsigned long long base = sh_base;
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const uint32_t wbase = warp * EX_WPW;
-    uint64_t myvalid = 0;
-    uint32_t total = 0;
-#pragma unroll 4
-    for (int it = 0; it < EX_WPW / 32; ++it) {
-        uint32_t p = wbase + it * 32 + lane;
-        uint32_t q = p >> 5, s = p & 31;
-        int remaining = (int)K;
-        int take = 32 - (int)s < remaining ? 32 - (int)s : remaining;
-        uint32_t m = take >= 32 ? ~0u : ((1u << take) - 1);
-        bool bad = ((inval[q] >> s) & m) != 0;
-        remaining -= take;
-        while (remaining > 0) {
-            ++q;
-            take = remaining < 32 ? remaining : 32;
-            m = take >= 32 ? ~0u : ((1u << take) - 1);
-            bad |= (inval[q] & m) != 0;
-            remaining -= take;
-        }
-        if (!bad) myvalid |= 1ull << it;
-        total += __popc(__ballot_sync(0xffffffffu, !bad));
-    }
-    if (total == 0) return;
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd(out_counter, (unsigned long long)total);
-    base = __shfl_sync(0xffffffffu, base, 0);
+    const unsigned lt = lanemask_lt();
 
     const unsigned KL = K * L;
+#pragma unroll 4
     for (int it = 0; it < EX_WPW / 32; ++it) {
-        bool ok = (myvalid >> it) & 1;
-        unsigned bal = __ballot_sync(0xffffffffu, ok);
-        if (ok) {
+        const uint32_t q = (wbase >> 5) + it;
+        const uint32_t word = wvalid[q];
+        if ((word >> lane) & 1) {
             uint32_t p = wbase + it * 32 + lane;
             KeyT v = Win<KeyT>::load(codes, p * L, KL);
             KeyT key = boss_rotate(v, L, K);
@@ -162,7 +173,7 @@ extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut l
                 KeyT rkey = boss_rotate(r, L, K);
                 if (w_lt(rkey, key)) key = rkey;   // forward <= reverse keeps forward
             }
-            uint64_t dst = base + __popc(bal & lanemask_lt());
+            uint64_t dst = base + wprefix[q] + __popc(word & lt);
             out_keys[dst] = key;
             if (HAS_COUNT) {
                 // read containing this window: last start <= global position
@@ -175,7 +186,6 @@ extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut l
                 out_counts[dst] = read_counts[lo];
             }
         }
-        base += __popc(bal);
     }
 }
 
@@ -183,7 +193,7 @@ template <typename KeyT, int L, bool CANON>
 void launch_extract(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream) {
     const uint32_t halo_groups = (a.K - 1 + EX_GROUP - 1) / EX_GROUP;
     const uint32_t ngroups = EX_THREADS + halo_groups;
-    size_t smem = sizeof(uint32_t) * ((size_t)ngroups * 2 * L + 4 + (size_t)ngroups * 2 + 4);
+    size_t smem = sizeof(uint32_t) * ((size_t)ngroups * 2 * L + 4 + (size_t)ngroups * 2 + 4 + 2 * (EX_TILE / 32));
     unsigned grid = (unsigned)div_up(a.nbytes, (size_t)EX_TILE);
     if (a.read_counts) {
         auto k = extract_kernel<KeyT, L, CANON, true>;

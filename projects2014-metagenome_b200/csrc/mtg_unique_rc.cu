@@ -13,45 +13,75 @@ constexpr int UQ_THREADS = 256;
 constexpr int UQ_IPT = 8;
 constexpr int UQ_TILE = UQ_THREADS * UQ_IPT;
 
-// Single-pass compaction of run heads with decoupled look-back.
+// Single-pass compaction of run heads with decoupled look-back. Warp-striped (coalesced)
+// loads; the previous key comes from the neighbouring lane, heads are compacted with one ballot
+// per row so that consecutive heads are stored to consecutive addresses.
 template <typename KeyT>
 __global__ void __launch_bounds__(UQ_THREADS)
 unique_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_keys,
               uint64_t *__restrict__ out_starts, unsigned long long *d_num_out,
               unsigned long long *status, unsigned int *tile_counter) {
+    constexpr int WARPS = UQ_THREADS / 32;
     __shared__ unsigned int sh_tile;
-    __shared__ uint32_t warp_tot[UQ_THREADS / 32 + 1];
+    __shared__ uint32_t warp_cnt[WARPS + 1];
     __shared__ uint64_t slot;
     if (threadIdx.x == 0) sh_tile = atomicAdd(tile_counter, 1u);
     __syncthreads();
     const uint32_t tile = sh_tile;
-    const uint64_t base = (uint64_t)tile * UQ_TILE + (uint64_t)threadIdx.x * UQ_IPT;
-    // blocked arrangement: thread owns UQ_IPT consecutive keys
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint64_t wbase = (uint64_t)tile * UQ_TILE + (uint64_t)warp * (32 * UQ_IPT);
     KeyT k[UQ_IPT];
-    KeyT prev = WordTraits<KeyT>::zero();
-    if (base > 0 && base <= n) prev = keys[base - 1];
-    uint32_t heads = 0, cnt = 0;
 #pragma unroll
-    for (int i = 0; i < UQ_IPT; ++i) {
-        uint64_t idx = base + i;
-        if (idx < n) {
-            k[i] = keys[idx];
-            bool head = idx == 0 || !w_eq(k[i], prev);
-            prev = k[i];
-            if (head) { heads |= 1u << i; ++cnt; }
-        }
+    for (int r = 0; r < UQ_IPT; ++r) {
+        uint64_t idx = wbase + r * 32 + lane;
+        k[r] = idx < n ? keys[idx] : WordTraits<KeyT>::zero();
     }
-    uint32_t excl = block_exclusive_scan<UQ_THREADS>(cnt, warp_tot);
-    uint32_t tile_total = warp_tot[UQ_THREADS / 32];
-    uint64_t tile_excl = lookback_exclusive(status, tile, tile_total, &slot);
-    uint64_t pos = tile_excl + excl;
+    KeyT carry = WordTraits<KeyT>::zero();   // key just before this warp's chunk
+    if (lane == 0 && wbase > 0 && wbase <= n) carry = keys[wbase - 1];
+    unsigned bal[UQ_IPT];
+    uint32_t wcount = 0;
 #pragma unroll
-    for (int i = 0; i < UQ_IPT; ++i) {
-        if (heads & (1u << i)) {
-            out_keys[pos] = k[i];
-            if (out_starts) out_starts[pos] = base + i;
-            ++pos;
+    for (int r = 0; r < UQ_IPT; ++r) {
+        uint64_t idx = wbase + r * 32 + lane;
+        KeyT prev;
+        if constexpr (sizeof(KeyT) == 8) {
+            uint64_t up = __shfl_up_sync(0xffffffffu, w_low64(k[r]), 1);
+            uint64_t last = __shfl_sync(0xffffffffu, r ? w_low64(k[r ? r - 1 : 0]) : 0ull, 31);
+            uint64_t pv = lane ? up : (r ? last : w_low64(carry));
+            prev = WordTraits<KeyT>::from_u64(pv);
+        } else {
+            const u128 cur = *reinterpret_cast<const u128 *>(&k[r]);
+            const u128 prv = *reinterpret_cast<const u128 *>(&k[r ? r - 1 : 0]);
+            const u128 cr = *reinterpret_cast<const u128 *>(&carry);
+            u128 up = make_u128(__shfl_up_sync(0xffffffffu, cur.lo, 1), __shfl_up_sync(0xffffffffu, cur.hi, 1));
+            u128 last = make_u128(__shfl_sync(0xffffffffu, prv.lo, 31), __shfl_sync(0xffffffffu, prv.hi, 31));
+            u128 pv = lane ? up : (r ? last : cr);
+            prev = *reinterpret_cast<const KeyT *>(&pv);
         }
+        bool head = idx < n && (idx == 0 || !w_eq(k[r], prev));
+        bal[r] = __ballot_sync(0xffffffffu, head);
+        wcount += __popc(bal[r]);
+    }
+    if (lane == 0) warp_cnt[warp] = wcount;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int w = 0; w < WARPS; ++w) { uint32_t t = warp_cnt[w]; warp_cnt[w] = run; run += t; }
+        warp_cnt[WARPS] = run;
+    }
+    __syncthreads();
+    const uint32_t tile_total = warp_cnt[WARPS];
+    const uint64_t tile_excl = lookback_exclusive(status, tile, tile_total, &slot);
+    uint64_t pos = tile_excl + warp_cnt[warp];
+    const unsigned lt = lanemask_lt();
+#pragma unroll
+    for (int r = 0; r < UQ_IPT; ++r) {
+        if (bal[r] & (1u << lane)) {
+            uint64_t dst = pos + __popc(bal[r] & lt);
+            out_keys[dst] = k[r];
+            if (out_starts) out_starts[dst] = wbase + r * 32 + lane;
+        }
+        pos += __popc(bal[r]);
     }
     // the tile holding the last element publishes the total and the end marker
     if (threadIdx.x == 0 && (uint64_t)(tile + 1) * UQ_TILE >= n) {
@@ -137,32 +167,57 @@ __device__ __forceinline__ KeyT rc_boss_dna(KeyT x, unsigned K) {
     return w_or(hi, w_shr(r, L * (K - 1)));
 }
 
+constexpr int RC_THREADS = 256;
+constexpr int RC_IPT = 8;
+constexpr int RC_TILE = RC_THREADS * RC_IPT;
+
+// One global atomic per block (a per-warp atomic on the single counter serialises in L2:
+// 5.8 ms for 231 M keys); the block's reverse complements are staged in shared memory and
+// written out coalesced. Their order is irrelevant: they are sorted afterwards.
 template <typename KeyT>
-__global__ void append_rc_kernel(const KeyT *__restrict__ keys, KeyT *__restrict__ rc_out, uint32_t *counts,
-                                 uint32_t *__restrict__ rc_counts, uint64_t m, uint32_t K, uint32_t cmax,
-                                 unsigned long long *d_appended) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    bool emit = false;
-    KeyT rc = WordTraits<KeyT>::zero();
-    uint32_t c = 0;
-    if (i < m) {
-        KeyT x = keys[i];
-        rc = rc_boss_dna(x, K);
-        emit = !w_eq(rc, x);
-        if (counts) {
-            c = counts[i];
-            if (!emit) counts[i] = c > cmax / 2 ? cmax : 2 * c;   // palindrome (:205-211)
+__global__ void __launch_bounds__(RC_THREADS)
+append_rc_kernel(const KeyT *__restrict__ keys, KeyT *__restrict__ rc_out, uint32_t *counts,
+                 uint32_t *__restrict__ rc_counts, uint64_t m, uint32_t K, uint32_t cmax,
+                 unsigned long long *d_appended) {
+    __shared__ KeyT s_keys[RC_TILE];
+    __shared__ uint32_t s_cnt[RC_TILE];
+    __shared__ uint32_t warp_tot[RC_THREADS / 32 + 1];
+    __shared__ unsigned long long s_base;
+    const uint64_t base = (uint64_t)blockIdx.x * RC_TILE;
+    KeyT rc[RC_IPT];
+    uint32_t c[RC_IPT];
+    uint32_t flags = 0, n_emit = 0;
+#pragma unroll
+    for (int it = 0; it < RC_IPT; ++it) {
+        uint64_t i = base + it * RC_THREADS + threadIdx.x;
+        c[it] = 0;
+        rc[it] = WordTraits<KeyT>::zero();
+        if (i < m) {
+            KeyT x = keys[i];
+            rc[it] = rc_boss_dna(x, K);
+            bool emit = !w_eq(rc[it], x);
+            if (counts) {
+                c[it] = counts[i];
+                if (!emit) counts[i] = c[it] > cmax / 2 ? cmax : 2 * c[it];   // palindrome (:205-211)
+            }
+            if (emit) { flags |= 1u << it; ++n_emit; }
         }
     }
-    unsigned bal = __ballot_sync(0xffffffffu, emit);
-    if (bal == 0) return;
-    unsigned long long base = 0;
-    if ((threadIdx.x & 31) == 0) base = atomicAdd(d_appended, (unsigned long long)__popc(bal));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (emit) {
-        uint64_t dst = base + __popc(bal & lanemask_lt());
-        rc_out[dst] = rc;
-        if (counts) rc_counts[dst] = c;
+    uint32_t excl = block_exclusive_scan<RC_THREADS>(n_emit, warp_tot);
+    const uint32_t total = warp_tot[RC_THREADS / 32];
+    if (threadIdx.x == 0) s_base = total ? atomicAdd(d_appended, (unsigned long long)total) : 0ull;
+#pragma unroll
+    for (int it = 0; it < RC_IPT; ++it)
+        if (flags & (1u << it)) {
+            s_keys[excl] = rc[it];
+            if (counts) s_cnt[excl] = c[it];
+            ++excl;
+        }
+    __syncthreads();
+    const unsigned long long gbase = s_base;
+    for (uint32_t j = threadIdx.x; j < total; j += RC_THREADS) {
+        rc_out[gbase + j] = s_keys[j];
+        if (counts) rc_counts[gbase + j] = s_cnt[j];
     }
 }
 
@@ -229,7 +284,7 @@ void append_reverse_complements(const KeyT *keys, KeyT *rc_out, uint32_t *counts
                                 cudaStream_t stream, unsigned *launches) {
     MTG_CUDA(cudaMemsetAsync(d_appended, 0, sizeof(unsigned long long), stream));
     if (m == 0) return;
-    append_rc_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(keys, rc_out, counts, rc_counts,
+    append_rc_kernel<KeyT><<<(unsigned)div_up(m, (size_t)RC_TILE), RC_THREADS, 0, stream>>>(keys, rc_out, counts, rc_counts,
                                                                                m, al.K, cmax, d_appended);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
