@@ -1,0 +1,163 @@
+// mtg_build: command-line front end with the `metagraph build` flag surface for the BOSS path
+// (cli/config/config.cpp:123-195,279,339; cli/build.cpp:58-157). It runs the GPU chunk build
+// and writes <out>.dbg.chunk{,.W,.last,.weights} exactly as `metagraph build --suffix ...` does
+// (boss_chunk.cpp:372-386); `mtg_build concatenate` joins chunk files (build_boss_from_chunks,
+// boss_chunk.cpp:286-328). The wavelet-tree / rank-select construction that turns a chunk into
+// a .dbg (BOSS::initialize, boss.cpp:99-122) stays with the reference host code.
+#include <zlib.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "boss_chunk_construct_gpu.hpp"
+
+using namespace mtg::gpu;
+
+namespace {
+
+// FASTA / FASTQ (optionally gzip) reader in the spirit of read_fasta_file_critical
+// (seq_io/sequence_io.cpp:364-405): calls `cb` with every sequence.
+template <class F>
+void read_sequences(const std::string &path, F cb) {
+    gzFile f = gzopen(path.c_str(), "rb");
+    if (!f) {
+        fprintf(stderr, "ERROR: cannot open %s\n", path.c_str());
+        exit(1);
+    }
+    gzbuffer(f, 1 << 20);
+    std::string line, seq;
+    std::vector<char> buf(1 << 20);
+    int state = 0;   // 0: header expected / FASTA body, 1: FASTQ sequence, 2: FASTQ '+', 3: FASTQ quality
+    bool fastq = false, first = true;
+    auto handle = [&](const std::string &l) {
+        if (first) { fastq = !l.empty() && l[0] == '@'; first = false; }
+        if (fastq) {
+            if (state == 0) state = 1;
+            else if (state == 1) { seq = l; state = 2; }
+            else if (state == 2) state = 3;
+            else { cb(seq); seq.clear(); state = 0; }
+        } else if (!l.empty() && l[0] == '>') {
+            if (!seq.empty()) cb(seq);
+            seq.clear();
+        } else {
+            seq += l;
+        }
+    };
+    while (gzgets(f, buf.data(), (int)buf.size())) {
+        size_t n = strlen(buf.data());
+        bool eol = n && buf[n - 1] == '\n';
+        line.append(buf.data(), n - (eol ? 1 : 0));
+        if (!eol) continue;
+        if (!line.empty() && line.back() == '\r') line.pop_back();
+        handle(line);
+        line.clear();
+    }
+    if (!line.empty()) handle(line);
+    if (!fastq && !seq.empty()) cb(seq);
+    gzclose(f);
+}
+
+int usage() {
+    fprintf(stderr,
+            "Usage: mtg_build build -k <k> [--mode basic|canonical] [--count-kmers] [--count-width <bits>]\n"
+            "                       [-p <threads>] [--mem-cap-gb <G>] [--alphabet DNA|Protein] [--device <id>]\n"
+            "                       [-v] -o <outbase> FILE1 [FILE2 ...]\n"
+            "       mtg_build concatenate -o <outbase> CHUNK1 [CHUNK2 ...]\n");
+    return 1;
+}
+
+}  // namespace
+
+int main(int argc, char **argv) {
+    if (argc < 2) return usage();
+    const std::string cmd = argv[1];
+    size_t k = 3, threads = 1;
+    bool canonical = false, count_kmers = false, verbose = false;
+    int count_width = 8, device = 0;   // config.hpp:103 default --count-width 8
+    double mem_cap_gb = 1;
+    Alphabet alphabet = Alphabet::DNA;
+    std::string out;
+    std::vector<std::string> files;
+    for (int i = 2; i < argc; ++i) {
+        const std::string a = argv[i];
+        auto next = [&]() -> const char * {
+            if (i + 1 >= argc) exit(usage());
+            return argv[++i];
+        };
+        if (a == "-k" || a == "--kmer-length") k = atoi(next());
+        else if (a == "--mode") {
+            const std::string m = next();
+            if (m == "canonical") canonical = true;
+            else if (m != "basic") { fprintf(stderr, "Error: unsupported --mode %s\n", m.c_str()); return 1; }
+        } else if (a == "--count-kmers") count_kmers = true;
+        else if (a == "--count-width") count_width = atoi(next());
+        else if (a == "-p" || a == "--parallel") threads = atoi(next());
+        else if (a == "--mem-cap-gb") mem_cap_gb = atof(next());
+        else if (a == "--alphabet") alphabet = std::string(next()) == "Protein" ? Alphabet::Protein : Alphabet::DNA;
+        else if (a == "--device") device = atoi(next());
+        else if (a == "-o" || a == "--outfile-base") out = next();
+        else if (a == "-v" || a == "--verbose") verbose = true;
+        else if (a[0] == '-') { fprintf(stderr, "Error: unknown option %s\n", a.c_str()); return usage(); }
+        else files.push_back(a);
+    }
+    if (out.empty() || files.empty()) return usage();
+    try {
+        if (cmd == "concatenate") {
+            Chunk c = BOSSConstructor::build_graph_from_chunks(files, verbose);
+            c.serialize(out);
+            printf("Graph chunks concatenated: %llu rows\n", (unsigned long long)c.size());
+            return 0;
+        }
+        if (cmd != "build") return usage();
+        // config.cpp:421-434
+        if (!count_kmers) count_width = 0;
+        else if (count_width < 2 || count_width > 32) {
+            fprintf(stderr, "Error: bad value for --count-width, use [2..32]\n");
+            return 1;
+        }
+        if (k < 2) { fprintf(stderr, "Error: k must be at least 2\n"); return 1; }
+        auto t0 = std::chrono::steady_clock::now();
+        // cli/build.cpp:100,122-134: BOSS node length = k - 1
+        BOSSConstructor constructor(k - 1, canonical, (uint8_t)count_width, "", threads, mem_cap_gb * 1e9,
+                                    ContainerType::VECTOR, "/tmp/", 1e9, alphabet, device);
+        std::vector<std::string> batch;
+        size_t batch_bytes = 0, n_seq = 0;
+        for (const auto &f : files) {
+            if (verbose) fprintf(stderr, "Parsing %s\n", f.c_str());
+            read_sequences(f, [&](const std::string &s) {
+                batch_bytes += s.size();
+                batch.push_back(s);
+                ++n_seq;
+                if (batch_bytes > (32u << 20)) {
+                    constructor.add_sequences(std::move(batch));
+                    batch = {};
+                    batch_bytes = 0;
+                }
+            });
+        }
+        if (!batch.empty()) constructor.add_sequences(std::move(batch));
+        auto t1 = std::chrono::steady_clock::now();
+        Chunk chunk = constructor.build_graph();
+        auto t2 = std::chrono::steady_clock::now();
+        if (verbose) {   // the counters boss_chunk_construct.cpp:267-302 logs
+            fprintf(stderr, "Total number of real k-mers: %llu\n", (unsigned long long)chunk.stats.n_real);
+            fprintf(stderr, "Added %llu dummy sink k-mers\n", (unsigned long long)chunk.stats.n_dummy_sink);
+            for (size_t i = 0; i < chunk.stats.n_dummy_source.size(); ++i)
+                fprintf(stderr, "Number of dummy k-mers with dummy prefix of length %zu: %llu\n", i + 1,
+                        (unsigned long long)chunk.stats.n_dummy_source[i]);
+        }
+        printf("Graph chunk with %llu k-mers was built in %.3f sec (parse %.3f sec, device %.3f ms, %u kernels)\n",
+               (unsigned long long)(chunk.size() - 1), std::chrono::duration<double>(t2 - t0).count(),
+               std::chrono::duration<double>(t1 - t0).count(), chunk.stats.device_ms,
+               chunk.stats.kernel_launches);
+        chunk.serialize(out);
+    } catch (const std::exception &e) {   // logger->error + exit(1) in the reference
+        fprintf(stderr, "%s\n", e.what());
+        return 1;
+    }
+    return 0;
+}
