@@ -134,6 +134,34 @@ int mtg_debug_sort_u64(int device, uint64_t *keys, uint32_t *vals /*nullable*/, 
 int mtg_debug_sort_u128(int device, uint64_t *keys_lohi, uint32_t *vals /*nullable*/, uint64_t n,
                         uint32_t key_bits);
 
+/* ---- Range-partitioned build across several GPUs (one context per GPU) --------------------
+ * The reference shards this path by the leading characters of the sort key
+ * (boss_chunk_construct.cpp:366-397 split by F/W, :462-525 and :754-792 routing, :917-931
+ * ordered extend). Here the routing bucket of a k-mer is the top mtg_mg_part_bits() bits of
+ * its word; bucket ranges are assigned to contexts by the caller, which moves the data
+ * between contexts (NCCL all-to-all / all-gather in multi_gpu.py). All buffers are device
+ * memory; element size is 8 bytes if (k+1)*L <= 64, else 16. Sequence of calls per context:
+ *   mtg_push_reads* -> mtg_mg_extract -> [all-to-all by bucket] -> mtg_mg_collect
+ *   -> mtg_mg_targets -> [all-to-all by bucket] -> mtg_mg_dummies -> [all-gather]
+ *   -> mtg_mg_build  (chunk of this range; the host concatenates with Chunk::extend). */
+uint32_t mtg_mg_part_bits(const mtg_ctx *ctx);
+/* Extracts the pushed reads (both strands in canonical mode) and groups the k-mers by bucket:
+ * bucket_counts[2^part_bits] (host), *d_keys library-owned until mtg_mg_collect. */
+int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_t *n);
+/* Sort + fold the k-mers routed to this context (d_keys NULL: the context's own extraction). */
+int mtg_mg_collect(mtg_ctx *ctx, const void *d_keys, uint64_t n, uint64_t *n_real);
+/* Sorted distinct target nodes (k-mer minus first char) of this range's k-mers, with the
+ * per-bucket counts for routing them to the owner of the node. */
+int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint64_t *n);
+/* d_targets_in: all target nodes that fall into this range. Finds the range's dummy sinks
+ * (kept inside) and returns its source nodes without incoming edge (forward-lex packing). */
+int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, void **d_src_nodes,
+                   uint64_t *n_src, uint64_t *n_sink);
+/* d_all_src_nodes: the gathered source nodes of every range. Emits the chunk of bucket range
+ * [lo_bucket, hi_bucket); first_range adds the all-'$' row (boss_chunk_construct.cpp:310-315). */
+int mtg_mg_build(mtg_ctx *ctx, const void *d_all_src_nodes, uint64_t n_all, uint64_t lo_bucket,
+                 uint64_t hi_bucket, int first_range, int device_output, mtg_chunk *out);
+
 /* Device-resident timing of the radix sort alone on n pseudo-random keys of key_bits bits
  * (tuning aid): ms_out[0] = digit-histogram kernel, [1] = mean onesweep pass, [2] = whole sort. */
 int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_vals, int iters,

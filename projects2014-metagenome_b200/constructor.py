@@ -262,6 +262,62 @@ class BOSSChunkConstructor:
         finally:
             self._lib.mtg_free_chunk(ctypes.byref(c))
 
+    # ---- range-partitioned (multi-GPU) phases, include/mtg_gpu.h mtg_mg_* ----------------
+    def mg_part_bits(self):
+        return int(self._lib.mtg_mg_part_bits(self._ctx))
+
+    def mg_extract(self):
+        """-> (bucket_counts uint64[2^part_bits], device pointer, n k-mers)"""
+        counts = np.zeros(1 << self.mg_part_bits(), dtype=np.uint64)
+        ptr, n = ctypes.c_void_p(), ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_extract(self._ctx, counts.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
+                                             ctypes.byref(ptr), ctypes.byref(n)))
+        return counts, ptr.value or 0, n.value
+
+    def mg_collect(self, dptr, n):
+        m = ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_collect(self._ctx, ctypes.c_void_p(dptr), n, ctypes.byref(m)))
+        return m.value
+
+    def mg_targets(self):
+        counts = np.zeros(1 << self.mg_part_bits(), dtype=np.uint64)
+        ptr, n = ctypes.c_void_p(), ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_targets(self._ctx, counts.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
+                                             ctypes.byref(ptr), ctypes.byref(n)))
+        return counts, ptr.value or 0, n.value
+
+    def mg_dummies(self, dptr, n_in):
+        ptr, n_src, n_sink = ctypes.c_void_p(), ctypes.c_uint64(), ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_dummies(self._ctx, ctypes.c_void_p(dptr), n_in, ctypes.byref(ptr),
+                                             ctypes.byref(n_src), ctypes.byref(n_sink)))
+        return ptr.value or 0, n_src.value, n_sink.value
+
+    def mg_build(self, dptr, n_all, lo_bucket, hi_bucket, first_range, device_output=False):
+        c = MtgChunk()
+        self._check(self._lib.mtg_mg_build(self._ctx, ctypes.c_void_p(dptr), n_all, lo_bucket, hi_bucket,
+                                           int(first_range), int(device_output), ctypes.byref(c)))
+        try:
+            if device_output:
+                st = self._stats(c)
+                st["F"] = [int(c.F[i]) for i in range(c.sigma)]
+                return st
+            return self._chunk_from(c)
+        finally:
+            self._lib.mtg_free_chunk(ctypes.byref(c))
+
+    def _chunk_from(self, c):
+        n = c.n_rows
+        nW = (n * c.W_width + 63) // 64
+        nl = (n + 63) // 64
+        W = np.ctypeslib.as_array(c.W, (nW,)).copy()
+        last = np.ctypeslib.as_array(c.last, (nl,)).copy()
+        wts = None
+        if c.weights_width:
+            nw = (n * c.weights_width + 63) // 64
+            wts = np.ctypeslib.as_array(c.weights, (nw,)).copy()
+        F = np.array(c.F[: c.sigma], dtype=np.uint64)
+        return Chunk(c.sigma, c.k, n, W, last, F, c.W_width, wts, c.weights_width, self._stats(c))
+
     def debug_sorted_kmers(self):
         u64p = ctypes.POINTER(ctypes.c_uint64)
         words = u64p()

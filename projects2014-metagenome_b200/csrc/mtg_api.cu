@@ -183,6 +183,11 @@ struct PinnedCache {
 };
 PinnedCache g_pinned_cache;
 
+struct RealSet {   // sorted distinct real k-mers (both strands in canonical mode)
+    DevBuf keys, counts;
+    uint64_t m = 0, n_input = 0;
+};
+
 }  // namespace
 
 struct mtg_ctx {
@@ -200,6 +205,12 @@ struct mtg_ctx {
     uint32_t cmax = 0;   // container count type max (boss_chunk_construct.cpp:1147-1160)
     std::string error;
     unsigned launches = 0;
+    // range-partitioned (multi-GPU) build state, see mtg_mg_* below
+    struct Mg {
+        DevBuf keys, targets, tset, sinks, src;
+        RealSet reals;
+        uint64_t nt = 0, n_sink = 0, n_src = 0, n_input = 0;
+    } mg;
 };
 
 namespace {
@@ -498,10 +509,6 @@ struct SortProfile {   // CUDA events around every kernel of the main sort
     ~SortProfile() { for (auto &e : ev) cudaEventDestroy(e); }
 };
 
-struct RealSet {   // sorted distinct real k-mers (both strands in canonical mode)
-    DevBuf keys, counts;
-    uint64_t m = 0, n_input = 0;
-};
 
 template <typename KeyT>
 void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const SortPlan &plan,
@@ -524,25 +531,12 @@ void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const S
     }
 }
 
-// extraction + sort + unique/count (+ rc completion): KmerCollector::data()
-// (kmer_collector.hpp:94) followed by add_reverse_complements.
+// K1 over every pushed read segment; returns through *d_ctr (device) the number of k-mers
 template <typename KeyT>
-void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nullptr) {
+void run_extraction(mtg_ctx *ctx, bool both, bool payload, KeyT *out_keys, uint32_t *out_counts,
+                    unsigned long long *d_ctr) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
-    const bool counting = ctx->prm.bits_per_count > 0;
-    const bool payload = counting && ctx->any_explicit_counts;
-    uint64_t n_ub = 0;
-    for (auto &seg : ctx->segs) n_ub += seg.n_windows_max;
-
-    DevBuf ctr(64, s);
-    unsigned long long *d_ctr = ctr.as<unsigned long long>();   // [0] extract, [1] unique, [2] rc
-    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
-    DevBuf keysA(sizeof(KeyT) * n_ub, s), keysB(sizeof(KeyT) * n_ub, s);
-    DevBuf valsA, valsB;
-    if (payload) { valsA.alloc(4 * n_ub, s); valsB.alloc(4 * n_ub, s); }
-
-    if (tm) tm->mark();
     std::vector<DevBuf> ones;
     for (auto &seg : ctx->segs) {
         ExtractArgs a;
@@ -552,7 +546,8 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
         a.K = al.K;
         a.L = al.L;
         a.canonical = ctx->prm.both_strands != 0;
-        a.out_counts = payload ? valsA.as<uint32_t>() : nullptr;
+        a.both = both;
+        a.out_counts = payload ? out_counts : nullptr;
         a.out_counter = d_ctr;
         a.read_starts = nullptr;
         a.read_counts = nullptr;
@@ -569,12 +564,44 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
                 a.read_counts = ones.back().as<uint32_t>();
             }
         }
-        extract_kmers<KeyT>(a, keysA.as<KeyT>(), s);
+        extract_kmers<KeyT>(a, out_keys, s);
         ctx->launches += 1;
+    }
+    MTG_CUDA(cudaStreamSynchronize(s));   // `ones` must outlive the kernels
+}
+
+// extraction + sort + unique/count (+ rc completion): KmerCollector::data()
+// (kmer_collector.hpp:94) followed by add_reverse_complements.
+// With ext_keys (multi-GPU: the k-mers routed to this key range, both strands already present)
+// extraction and rc completion are skipped.
+template <typename KeyT>
+void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nullptr,
+                   const void *ext_keys = nullptr, uint64_t ext_n = 0) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    const bool payload = counting && ctx->any_explicit_counts && !ext_keys;
+    uint64_t n_ub = ext_n;
+    if (!ext_keys)
+        for (auto &seg : ctx->segs) n_ub += seg.n_windows_max;
+
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();   // [0] extract, [1] unique, [2] rc
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
+    DevBuf keysA(sizeof(KeyT) * n_ub, s), keysB(sizeof(KeyT) * n_ub, s);
+    DevBuf valsA, valsB;
+    if (payload) { valsA.alloc(4 * n_ub, s); valsB.alloc(4 * n_ub, s); }
+
+    if (tm) tm->mark();
+    if (ext_keys) {
+        MTG_CUDA(cudaMemcpyAsync(keysA.p, ext_keys, sizeof(KeyT) * ext_n, cudaMemcpyDeviceToDevice, s));
+        unsigned long long hn = ext_n;
+        MTG_CUDA(cudaMemcpyAsync(d_ctr, &hn, 8, cudaMemcpyHostToDevice, s));
+    } else {
+        run_extraction<KeyT>(ctx, false, payload, keysA.as<KeyT>(), valsA.as<uint32_t>(), d_ctr);
     }
     const uint64_t n = read_counter(d_ctr, s);
     rs->n_input = n;
-    ones.clear();
     if (tm) tm->mark();
 
     SortPlan plan;
@@ -653,7 +680,7 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
     const uint64_t cap = canon ? 2 * m : m;
     if (tm) tm->mark();
 
-    if (!canon) {
+    if (!canon || ext_keys) {
         rs->keys = std::move(keysB);
         rs->counts = std::move(counts);
         rs->m = m;
@@ -690,44 +717,15 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
     if (tm) tm->mark();
 }
 
+// sources-1 nodes (forward-lex, unsorted) -> all dummy source k-mers; the result arrays hold
+// [n_sink dummy sinks | d_src dummy sources] with their info bytes. d_ctr + 8 = level histogram.
 template <typename KeyT>
-void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
+void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64_t n_sink,
+                    unsigned long long *d_ctr, DevBuf &dk0, DevBuf &di0, uint64_t *d_out) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const uint32_t K = al.K, L = al.L;
-    const bool counting = ctx->prm.bits_per_count > 0;
-    ctx->launches = 0;
-    Timer tm(s);
-    RealSet rs;
-    SortProfile prof;
-    collect_reals<KeyT>(ctx, &rs, &tm, &prof);   // marks 0..4: start, extract, sort, unique, rc
-    const uint64_t m = rs.m;
-    const KeyT *reals = rs.keys.as<KeyT>();
-
-    // ---- dummy k-mers ----
-    DevBuf ctr(64 + 8 * MTG_MAX_K, s);
-    unsigned long long *d_ctr = ctr.as<unsigned long long>();   // [0] sinks [1] sources-1 [8..] levels
-    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64 + 8 * MTG_MAX_K, s));
-    uint64_t cap = std::max<uint64_t>(1024, m / 8);
-    DevBuf bidx;
-    const bool use_index = m >= (1u << 16);
-    if (use_index) {
-        bidx.alloc(8 * bucket_index_words(al), s);
-        build_bucket_index<KeyT>(reals, m, al, bidx.as<uint64_t>(), s, &ctx->launches);
-    }
-    const uint64_t *d_bidx = use_index ? bidx.as<uint64_t>() : nullptr;
-    DevBuf sink, src, srcB;
-    uint64_t n_sink = 0, d1 = 0;
-    while (true) {
-        sink.alloc(sizeof(KeyT) * cap, s);
-        src.alloc(sizeof(KeyT) * cap, s);
-        find_dummy_candidates<KeyT>(reals, m, al, d_bidx, sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap,
-                                    d_ctr + 1, s, &ctx->launches);
-        n_sink = read_counter(d_ctr, s);
-        d1 = read_counter(d_ctr + 1, s);
-        if (n_sink <= cap && d1 <= cap) break;
-        cap = std::max(n_sink, d1);
-    }
+    DevBuf srcB;
     // sources-1 in forward-lex order, then all their distinct prefixes
     srcB.alloc(sizeof(KeyT) * std::max<uint64_t>(d1, 1), s);
     {
@@ -746,14 +744,31 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     }
     const uint64_t d_src = read_counter(offsets.as<unsigned long long>() + d1, s);
     const uint64_t d = n_sink + d_src;
-    DevBuf dk0(sizeof(KeyT) * std::max<uint64_t>(d, 1), s), dk1(sizeof(KeyT) * std::max<uint64_t>(d, 1), s);
-    DevBuf di0(4 * std::max<uint64_t>(d, 1), s), di1(4 * std::max<uint64_t>(d, 1), s);
+    dk0.alloc(sizeof(KeyT) * std::max<uint64_t>(d, 1), s);
+    di0.alloc(4 * std::max<uint64_t>(d, 1), s);
     MTG_CUDA(cudaMemcpyAsync(dk0.p, sink.p, sizeof(KeyT) * n_sink, cudaMemcpyDeviceToDevice, s));
     fill_u32(di0.as<uint32_t>(), INFO_W_DOLLAR, n_sink, s, &ctx->launches);
     generate_source_dummies<KeyT>(src.as<KeyT>(), per_entry.as<uint32_t>(), offsets.as<uint64_t>(), d1, al,
                                   dk0.as<KeyT>() + n_sink, di0.as<uint32_t>() + n_sink, d_ctr + 8, s,
                                   &ctx->launches);
     sink.release(); src.release(); per_entry.release(); offsets.release();
+    *d_out = d;
+}
+
+// dummy k-mers (sinks + sources, any order) + sorted reals -> rows -> W / last / F / weights.
+// row_off = 2: rows 0 (placeholder) and 1 (the all-'$' k-mer) precede the merge; 1: placeholder
+// only (a key range other than the first one, multi-GPU).
+template <typename KeyT>
+void finish_chunk(mtg_ctx *ctx, RealSet &rs, DevBuf &dk0, DevBuf &di0, uint64_t d, uint64_t n_sink,
+                  unsigned long long *d_ctr, const uint64_t *d_bidx, Timer &tm, SortProfile &prof,
+                  mtg_chunk *out, bool device_output, uint32_t row_off) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint32_t K = al.K, L = al.L;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    const uint64_t m = rs.m;
+    const KeyT *reals = rs.keys.as<KeyT>();
+    DevBuf dk1(sizeof(KeyT) * std::max<uint64_t>(d, 1), s), di1(4 * std::max<uint64_t>(d, 1), s);
     // final order: node bits, then more '$' first, then W  (LSD: W, nd, node)
     flip_info(di0.as<uint32_t>(), d, s, &ctx->launches);
     {
@@ -768,17 +783,16 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     dk1.release(); di1.release();
     DevBuf rank(8 * std::max<uint64_t>(d, 1), s);
     dummy_ranks<KeyT>(reals, m, dk0.as<KeyT>(), d, al, d_bidx, rank.as<uint64_t>(), s, &ctx->launches);
-    bidx.release();
     tm.mark();   // 5: dummies done
 
     // ---- merge + emit ----
-    const uint64_t E = m + d + 2;
+    const uint64_t E = m + d + row_off;
     DevBuf row_keys(sizeof(KeyT) * E, s), row_info(E, s), row_counts;
     if (counting) row_counts.alloc(4 * E, s);
     merge_rows<KeyT>(reals, counting ? rs.counts.as<uint32_t>() : nullptr, m, dk0.as<KeyT>(),
                      di0.as<uint32_t>(), rank.as<uint64_t>(), d, al, row_keys.as<KeyT>(),
                      row_info.as<uint8_t>(), counting ? row_counts.as<uint32_t>() : nullptr, s,
-                     &ctx->launches);
+                     &ctx->launches, row_off);
     rs.keys.release(); rs.counts.release(); dk0.release(); di0.release(); rank.release();
     const uint32_t ww = ctx->prm.bits_per_count;
     const size_t tiles = div_up(E, (size_t)2048);
@@ -851,6 +865,48 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     out->ms_total = tm.ms(0, 6);
     out->n_kernel_launches = ctx->launches;
     out->impl = impl;
+}
+
+template <typename KeyT>
+void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    ctx->launches = 0;
+    Timer tm(s);
+    RealSet rs;
+    SortProfile prof;
+    collect_reals<KeyT>(ctx, &rs, &tm, &prof);   // marks 0..4: start, extract, sort, unique, rc
+    const uint64_t m = rs.m;
+    const KeyT *reals = rs.keys.as<KeyT>();
+
+    // ---- dummy k-mers ----
+    DevBuf ctr(64 + 8 * MTG_MAX_K, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();   // [0] sinks [1] sources-1 [8..] levels
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64 + 8 * MTG_MAX_K, s));
+    uint64_t cap = std::max<uint64_t>(1024, m / 8);
+    DevBuf bidx;
+    const bool use_index = m >= (1u << 16);
+    if (use_index) {
+        bidx.alloc(8 * bucket_index_words(al), s);
+        build_bucket_index<KeyT>(reals, m, al, bidx.as<uint64_t>(), s, &ctx->launches);
+    }
+    const uint64_t *d_bidx = use_index ? bidx.as<uint64_t>() : nullptr;
+    DevBuf sink, src, srcB;
+    uint64_t n_sink = 0, d1 = 0;
+    while (true) {
+        sink.alloc(sizeof(KeyT) * cap, s);
+        src.alloc(sizeof(KeyT) * cap, s);
+        find_dummy_candidates<KeyT>(reals, m, al, d_bidx, sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap,
+                                    d_ctr + 1, s, &ctx->launches);
+        n_sink = read_counter(d_ctr, s);
+        d1 = read_counter(d_ctr + 1, s);
+        if (n_sink <= cap && d1 <= cap) break;
+        cap = std::max(n_sink, d1);
+    }
+    uint64_t d = 0;
+    DevBuf dk0, di0;
+    expand_sources<KeyT>(ctx, src, d1, sink, n_sink, d_ctr, dk0, di0, &d);
+    finish_chunk<KeyT>(ctx, rs, dk0, di0, d, n_sink, d_ctr, d_bidx, tm, prof, out, device_output, 2);
 }
 
 void clear_ctx(mtg_ctx *ctx) {
@@ -1031,6 +1087,274 @@ int mtg_debug_sort_u64(int device, uint64_t *keys, uint32_t *vals, uint64_t n, u
 }
 int mtg_debug_sort_u128(int device, uint64_t *keys, uint32_t *vals, uint64_t n, uint32_t key_bits) {
     return debug_sort(device, keys, vals, n, key_bits, true);
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------
+// Range-partitioned (multi-GPU) build, SURVEY.md 8e. Each context owns the k-mers whose top
+// `part_bits` bits fall in its bucket range; the caller (multi_gpu.py) moves data between
+// contexts with NCCL all-to-all / all-gather. part_bits <= min(8, (K-2)*L) so that no group
+// of rows sharing kmer[2..K] straddles two ranges.
+// ---------------------------------------------------------------------------
+namespace {
+
+template <typename KeyT>
+void mg_extract_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **d_keys, uint64_t *n_out) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const bool both = ctx->prm.both_strands != 0;
+    uint64_t n_ub = 0;
+    for (auto &seg : ctx->segs) n_ub += seg.n_windows_max;
+    if (both) n_ub *= 2;
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
+    DevBuf a(sizeof(KeyT) * std::max<uint64_t>(n_ub, 1), s), b(sizeof(KeyT) * std::max<uint64_t>(n_ub, 1), s);
+    ctx->launches = 0;
+    run_extraction<KeyT>(ctx, both, false, a.as<KeyT>(), nullptr, d_ctr);
+    const uint64_t n = read_counter(d_ctr, s);
+    for (uint32_t i = 0; i < (1u << pb); ++i) bucket_counts[i] = 0;
+    if (pb == 0 || n == 0) {
+        bucket_counts[0] = n;
+    } else {
+        // one MSD pass on the top pb bits groups the k-mers by bucket; the digit offsets of
+        // the pass are the bucket boundaries
+        SortPlan plan;
+        plan.n = 0;
+        plan.p[plan.n++] = DigitPass{0, (int)(al.K * al.L - pb), (int)pb};
+        SortWorkspace ws;
+        DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
+        DevBuf hist(sizeof(unsigned long long) * MAX_SORT_PASSES * RADIX, s);
+        DevBuf tc(sizeof(unsigned int) * MAX_SORT_PASSES, s);
+        ws.status = status.as<unsigned long long>();
+        ws.hist = hist.as<unsigned long long>();
+        ws.tile_counters = tc.as<unsigned int>();
+        KeyT *keys[2] = {a.as<KeyT>(), b.as<KeyT>()};
+        int cur = radix_sort<KeyT>(keys, nullptr, n, plan, ws, s, &ctx->launches);
+        std::vector<unsigned long long> off(RADIX);
+        MTG_CUDA(cudaMemcpyAsync(off.data(), ws.hist, 8 * RADIX, cudaMemcpyDeviceToHost, s));
+        MTG_CUDA(cudaStreamSynchronize(s));
+        const uint32_t nb = 1u << pb;
+        for (uint32_t i = 0; i < nb; ++i) bucket_counts[i] = (i + 1 < nb ? off[i + 1] : n) - off[i];
+        if (cur == 1) std::swap(a, b);
+    }
+    ctx->mg.keys = std::move(a);
+    ctx->mg.n_input = both ? n / 2 : n;
+    *d_keys = ctx->mg.keys.p;
+    *n_out = n;
+    ctx->segs.clear();
+}
+
+template <typename KeyT>
+void mg_targets_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **d_targets, uint64_t *n_out) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint32_t K = al.K, L = al.L;
+    const uint64_t m = ctx->mg.reals.m;
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    DevBuf t0(sizeof(KeyT) * std::max<uint64_t>(m, 1), s), t1(sizeof(KeyT) * std::max<uint64_t>(m, 1), s);
+    target_nodes<KeyT>(ctx->mg.reals.keys.as<KeyT>(), m, al, t0.as<KeyT>(), s, &ctx->launches);
+    {   // per edge label the targets are already sorted: one stable pass on the leading char
+        SortPlan plan;
+        plan.n = 0;
+        plan.p[plan.n++] = DigitPass{0, (int)((K - 2) * L), (int)L};
+        sort_keys<KeyT>(t0, t1, nullptr, nullptr, m, plan, s, &ctx->launches);
+    }
+    {
+        DevBuf status(sizeof(unsigned long long) * unique_status_words(m), s), tctr(sizeof(unsigned int), s);
+        unique_keys<KeyT>(t0.as<KeyT>(), m, t1.as<KeyT>(), nullptr, d_ctr, status.as<unsigned long long>(),
+                          tctr.as<unsigned int>(), s, &ctx->launches);
+    }
+    const uint64_t nt = read_counter(d_ctr, s);
+    const uint32_t nb = 1u << pb;
+    std::vector<uint64_t> bounds(nb + 1, 0);
+    if (pb == 0) {
+        bounds[1] = nt;
+    } else {
+        DevBuf db(8 * (nb + 1), s);
+        bucket_bounds<KeyT>(t1.as<KeyT>(), nt, pb, (K - 1) * L - pb, db.as<uint64_t>(), s, &ctx->launches);
+        MTG_CUDA(cudaMemcpyAsync(bounds.data(), db.p, 8 * (nb + 1), cudaMemcpyDeviceToHost, s));
+        MTG_CUDA(cudaStreamSynchronize(s));
+    }
+    for (uint32_t i = 0; i < nb; ++i) bucket_counts[i] = bounds[i + 1] - bounds[i];
+    ctx->mg.targets = std::move(t1);
+    *d_targets = ctx->mg.targets.p;
+    *n_out = nt;
+}
+
+template <typename KeyT>
+void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, void **d_src, uint64_t *n_src,
+                     uint64_t *n_sink_out) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint32_t K = al.K, L = al.L;
+    const uint64_t m = ctx->mg.reals.m;
+    const KeyT *reals = ctx->mg.reals.keys.as<KeyT>();
+    ctx->mg.targets.release();
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    // targets received from every range: sort, fold -> T_i
+    DevBuf t0(sizeof(KeyT) * std::max<uint64_t>(n_in, 1), s), t1(sizeof(KeyT) * std::max<uint64_t>(n_in, 1), s);
+    MTG_CUDA(cudaMemcpyAsync(t0.p, d_in, sizeof(KeyT) * n_in, cudaMemcpyDeviceToDevice, s));
+    {
+        SortPlan plan;
+        plan.n = 0;
+        plan_add_key_bits(plan, 0, (K - 1) * L);
+        sort_keys<KeyT>(t0, t1, nullptr, nullptr, n_in, plan, s, &ctx->launches);
+        DevBuf status(sizeof(unsigned long long) * unique_status_words(n_in), s), tctr(sizeof(unsigned int), s);
+        unique_keys<KeyT>(t0.as<KeyT>(), n_in, t1.as<KeyT>(), nullptr, d_ctr, status.as<unsigned long long>(),
+                          tctr.as<unsigned int>(), s, &ctx->launches);
+    }
+    const uint64_t nt = read_counter(d_ctr, s);
+    t0.release();
+    DevBuf bidx;
+    const bool use_index = m >= (1u << 16);
+    if (use_index) {
+        bidx.alloc(8 * bucket_index_words(al), s);
+        build_bucket_index<KeyT>(reals, m, al, bidx.as<uint64_t>(), s, &ctx->launches);
+    }
+    uint64_t cap = std::max<uint64_t>(1024, std::max(m, nt) / 8);
+    DevBuf sink, src;
+    uint64_t n_sink = 0, d1 = 0;
+    while (true) {
+        sink.alloc(sizeof(KeyT) * cap, s);
+        src.alloc(sizeof(KeyT) * cap, s);
+        ranged_dummy_candidates<KeyT>(reals, m, t1.as<KeyT>(), nt, al, use_index ? bidx.as<uint64_t>() : nullptr,
+                                      sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap, d_ctr + 1, s,
+                                      &ctx->launches);
+        n_sink = read_counter(d_ctr, s);
+        d1 = read_counter(d_ctr + 1, s);
+        if (n_sink <= cap && d1 <= cap) break;
+        cap = std::max(n_sink, d1);
+    }
+    ctx->mg.sinks = std::move(sink);
+    ctx->mg.src = std::move(src);
+    ctx->mg.n_sink = n_sink;
+    ctx->mg.n_src = d1;
+    *d_src = ctx->mg.src.p;
+    *n_src = d1;
+    *n_sink_out = n_sink;
+}
+
+}  // namespace
+
+namespace {
+
+template <typename KeyT>
+void mg_build_impl(mtg_ctx *ctx, const void *d_all_src, uint64_t n_all, uint64_t lo_bucket, uint64_t hi_bucket,
+                   uint32_t pb, bool first, mtg_chunk *out, bool device_output) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint32_t KL = al.K * al.L;
+    Timer tm(s);
+    SortProfile prof;
+    for (int i = 0; i < 5; ++i) tm.mark();   // phases 0..4 ran in the earlier mg calls
+    RealSet rs = std::move(ctx->mg.reals);
+    DevBuf ctr(64 + 8 * MTG_MAX_K, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64 + 8 * MTG_MAX_K, s));
+    // every range expands the global list of source-1 nodes (small) and keeps its own share
+    DevBuf src(sizeof(KeyT) * std::max<uint64_t>(n_all, 1), s);
+    MTG_CUDA(cudaMemcpyAsync(src.p, d_all_src, sizeof(KeyT) * n_all, cudaMemcpyDeviceToDevice, s));
+    const uint64_t n_sink = ctx->mg.n_sink;
+    uint64_t d_all = 0;
+    DevBuf ak, ai;
+    expand_sources<KeyT>(ctx, src, n_all, ctx->mg.sinks, n_sink, d_ctr, ak, ai, &d_all);
+    const uint64_t n_srcd = d_all - n_sink;
+    DevBuf dk0(sizeof(KeyT) * std::max<uint64_t>(d_all, 1), s), di0(4 * std::max<uint64_t>(d_all, 1), s);
+    MTG_CUDA(cudaMemcpyAsync(dk0.p, ak.p, sizeof(KeyT) * n_sink, cudaMemcpyDeviceToDevice, s));
+    MTG_CUDA(cudaMemcpyAsync(di0.p, ai.p, 4 * n_sink, cudaMemcpyDeviceToDevice, s));
+    const uint64_t nb = 1ull << pb;
+    const bool has_hi = pb > 0 && hi_bucket < nb;
+    KeyT lo = pb ? w_shl(WordTraits<KeyT>::from_u64(lo_bucket), KL - pb) : WordTraits<KeyT>::zero();
+    KeyT hi = has_hi ? w_shl(WordTraits<KeyT>::from_u64(hi_bucket), KL - pb) : WordTraits<KeyT>::zero();
+    filter_key_range<KeyT>(ak.as<KeyT>() + n_sink, ai.as<uint32_t>() + n_sink, n_srcd, lo, hi, has_hi ? 1 : 0,
+                           dk0.as<KeyT>() + n_sink, di0.as<uint32_t>() + n_sink, d_ctr + 2, s, &ctx->launches);
+    const uint64_t kept = read_counter(d_ctr + 2, s);
+    ak.release(); ai.release();
+    DevBuf bidx;
+    const bool use_index = rs.m >= (1u << 16);
+    if (use_index) {
+        bidx.alloc(8 * bucket_index_words(al), s);
+        build_bucket_index<KeyT>(rs.keys.as<KeyT>(), rs.m, al, bidx.as<uint64_t>(), s, &ctx->launches);
+    }
+    const uint64_t n_input = ctx->mg.n_input;
+    finish_chunk<KeyT>(ctx, rs, dk0, di0, n_sink + kept, n_sink, d_ctr, use_index ? bidx.as<uint64_t>() : nullptr,
+                       tm, prof, out, device_output, first ? 2 : 1);
+    out->n_input_kmers = n_input;
+    ctx->mg = mtg_ctx::Mg();
+}
+
+uint32_t mg_part_bits(const mtg_ctx *ctx) {
+    uint32_t lim = (ctx->al.K - 2) * ctx->al.L;
+    return lim < 8 ? lim : 8;
+}
+
+}  // namespace
+
+extern "C" {
+
+#define MG_GUARD(ctx, body)                                                  \
+    if (!ctx) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");           \
+    std::lock_guard<std::mutex> lk(ctx->mu);                                 \
+    try {                                                                    \
+        MTG_CUDA(cudaSetDevice(ctx->device));                                \
+        t_arena = ctx->arena;                                                \
+        const bool wide = ctx->al.K * ctx->al.L > 64;                        \
+        (void)wide;                                                          \
+        body                                                                 \
+    } catch (const CudaError &e) {                                           \
+        int rc = fail_cuda(ctx, e);                                          \
+        cudaStreamSynchronize(ctx->stream);                                  \
+        return rc;                                                           \
+    }                                                                        \
+    return MTG_OK;
+
+uint32_t mtg_mg_part_bits(const mtg_ctx *ctx) { return ctx ? mg_part_bits(ctx) : 0; }
+
+int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_t *n) {
+    MG_GUARD(ctx, {
+        if (ctx->any_explicit_counts)
+            return fail(ctx, MTG_ERR_UNSUPPORTED, "per-read counts are not supported by the range-partitioned build");
+        if (wide) mg_extract_impl<u128>(ctx, mg_part_bits(ctx), bucket_counts, d_keys, n);
+        else mg_extract_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_counts, d_keys, n);
+    })
+}
+
+int mtg_mg_collect(mtg_ctx *ctx, const void *d_keys, uint64_t n, uint64_t *n_real) {
+    MG_GUARD(ctx, {
+        if (wide) collect_reals<u128>(ctx, &ctx->mg.reals, nullptr, nullptr, d_keys ? d_keys : ctx->mg.keys.p, n);
+        else collect_reals<uint64_t>(ctx, &ctx->mg.reals, nullptr, nullptr, d_keys ? d_keys : ctx->mg.keys.p, n);
+        ctx->mg.keys.release();
+        *n_real = ctx->mg.reals.m;
+    })
+}
+
+int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint64_t *n) {
+    MG_GUARD(ctx, {
+        if (wide) mg_targets_impl<u128>(ctx, mg_part_bits(ctx), bucket_counts, d_targets, n);
+        else mg_targets_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_counts, d_targets, n);
+    })
+}
+
+int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, void **d_src_nodes, uint64_t *n_src,
+                   uint64_t *n_sink) {
+    MG_GUARD(ctx, {
+        if (wide) mg_dummies_impl<u128>(ctx, d_targets_in, n_in, d_src_nodes, n_src, n_sink);
+        else mg_dummies_impl<uint64_t>(ctx, d_targets_in, n_in, d_src_nodes, n_src, n_sink);
+    })
+}
+
+int mtg_mg_build(mtg_ctx *ctx, const void *d_all_src_nodes, uint64_t n_all, uint64_t lo_bucket,
+                 uint64_t hi_bucket, int first_range, int device_output, mtg_chunk *out) {
+    MG_GUARD(ctx, {
+        if (wide) mg_build_impl<u128>(ctx, d_all_src_nodes, n_all, lo_bucket, hi_bucket, mg_part_bits(ctx),
+                                      first_range != 0, out, device_output != 0);
+        else mg_build_impl<uint64_t>(ctx, d_all_src_nodes, n_all, lo_bucket, hi_bucket, mg_part_bits(ctx),
+                                     first_range != 0, out, device_output != 0);
+    })
 }
 
 }  // extern "C"

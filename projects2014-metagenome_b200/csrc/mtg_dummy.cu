@@ -217,10 +217,15 @@ template <typename KeyT>
 __global__ void merge_dummies_kernel(const KeyT *__restrict__ dummy_keys,
                                      const uint32_t *__restrict__ dummy_info,
                                      const uint64_t *__restrict__ rank, uint64_t d, uint32_t K,
-                                     KeyT *__restrict__ row_keys, uint8_t *__restrict__ row_info,
-                                     uint32_t *__restrict__ row_counts) {
+                                     uint32_t row_off, KeyT *__restrict__ row_keys,
+                                     uint8_t *__restrict__ row_info, uint32_t *__restrict__ row_counts) {
     uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j == 0) {
+    if (j == 0 && row_off == 1) {   // not the first key range: only the placeholder row
+        row_keys[0] = WordTraits<KeyT>::zero();
+        row_info[0] = (uint8_t)((K - 1) | INFO_W_DOLLAR);
+        if (row_counts) row_counts[0] = 0;
+    }
+    if (j == 0 && row_off == 2) {
         // row 0: placeholder; row 1: the all-'$' k-mer (boss_chunk_construct.cpp:310-315)
         row_keys[0] = WordTraits<KeyT>::zero();
         row_keys[1] = WordTraits<KeyT>::zero();
@@ -229,7 +234,7 @@ __global__ void merge_dummies_kernel(const KeyT *__restrict__ dummy_keys,
         if (row_counts) { row_counts[0] = 0; row_counts[1] = 0; }
     }
     if (j >= d) return;
-    uint64_t pos = rank[j] + j + 2;
+    uint64_t pos = rank[j] + j + row_off;
     row_keys[pos] = dummy_keys[j];
     row_info[pos] = (uint8_t)dummy_info[j];
     if (row_counts) row_counts[pos] = 0;
@@ -245,8 +250,9 @@ constexpr int MR_CAP = 1024;
 template <typename KeyT>
 __global__ void __launch_bounds__(MR_THREADS)
 merge_reals_kernel(const KeyT *__restrict__ reals, const uint32_t *__restrict__ real_counts, uint64_t m,
-                   const uint64_t *__restrict__ rank, uint64_t d, KeyT *__restrict__ row_keys,
-                   uint8_t *__restrict__ row_info, uint32_t *__restrict__ row_counts) {
+                   const uint64_t *__restrict__ rank, uint64_t d, uint32_t row_off,
+                   KeyT *__restrict__ row_keys, uint8_t *__restrict__ row_info,
+                   uint32_t *__restrict__ row_counts) {
     __shared__ uint64_t s_rank[MR_CAP];
     __shared__ uint64_t s_range[2];
     const uint64_t i0 = (uint64_t)blockIdx.x * MR_TILE;
@@ -286,10 +292,90 @@ merge_reals_kernel(const KeyT *__restrict__ reals, const uint32_t *__restrict__ 
             }
             cnt = lo;
         }
-        uint64_t pos = i + cnt + 2;
+        uint64_t pos = i + cnt + row_off;
         row_keys[pos] = reals[i];
         row_info[pos] = 0;
         if (row_counts) row_counts[pos] = real_counts[i];
+    }
+}
+
+// ---- range-partitioned (multi-GPU) variants, SURVEY.md 8e ----------------------------------
+// Target node of x = s_1..s_K is t = s_2..s_K, as a (K-1)-char node word in the layout of
+// (key >> L): t = (W << L(K-2)) | (x >> 2L). One entry per real (duplicates are folded later).
+template <typename KeyT>
+__global__ void target_nodes_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al,
+                                    KeyT *__restrict__ out) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    const uint32_t L = al.L, K = al.K;
+    KeyT x = reals[i];
+    KeyT W = w_and(x, WordTraits<KeyT>::low_mask(L));
+    out[i] = w_or(w_shl(W, L * (K - 2)), w_shr(x, 2 * L));
+}
+
+// reals: the sorted real k-mers of THIS key range; targets: sorted distinct target nodes that
+// fall into this range (collected from all ranges). sinks = targets \ source nodes,
+// sources-1 = source nodes \ targets (forward-lex packing, like dummy_candidates_kernel).
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+ranged_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, const KeyT *__restrict__ targets,
+                         uint64_t nt, Alpha al, BucketIndex bi, KeyT *sink_keys, uint64_t sink_cap,
+                         unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
+                         unsigned long long *d_num_src) {
+    using WT = WordTraits<KeyT>;
+    const uint32_t L = al.L, K = al.K;
+    const KeyT maskL = WT::low_mask(L);
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool emit_sink = false, emit_src = false;
+    KeyT sink = WT::zero(), fwd = WT::zero();
+    if (i < nt) {
+        sink = w_shl(targets[i], L);   // k-mer t$ : node t, W = '$' (zero slot)
+        uint64_t p = lower_bound_idx(reals, m, bi, sink);
+        emit_sink = !(p < m && w_eq(w_shr(reals[p], L), targets[i]));
+    }
+    if (i < m) {
+        KeyT x = reals[i];
+        KeyT node = w_shr(x, L);
+        bool node_head = i == 0 || !w_eq(w_shr(reals[i - 1], L), node);
+        if (node_head) {
+            uint64_t p = lower_bound_dev(targets, nt, node);
+            if (!(p < nt && w_eq(targets[p], node))) {
+                emit_src = true;
+                for (uint32_t c = 1; c < K; ++c) {
+                    KeyT ch = w_and(w_shr(x, L * c), maskL);
+                    fwd = w_or(fwd, w_shl(ch, L * (K - 1 - c)));
+                }
+            }
+        }
+    }
+    warp_append(emit_sink, sink, sink_keys, sink_cap, d_num_sink);
+    warp_append(emit_src, fwd, src_fwd, src_cap, d_num_src);
+}
+
+// keep the (key, info) pairs whose key lies in [lo, hi) (hi ignored when !has_hi); order is
+// irrelevant (the dummies are sorted afterwards)
+template <typename KeyT>
+__global__ void filter_key_range_kernel(const KeyT *__restrict__ keys, const uint32_t *__restrict__ info,
+                                        uint64_t n, KeyT lo, KeyT hi, int has_hi, KeyT *out_keys,
+                                        uint32_t *out_info, unsigned long long *d_num) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool keep = false;
+    KeyT k = WordTraits<KeyT>::zero();
+    uint32_t v = 0;
+    if (i < n) {
+        k = keys[i];
+        v = info[i];
+        keep = !w_lt(k, lo) && (!has_hi || w_lt(k, hi));
+    }
+    unsigned bal = __ballot_sync(0xffffffffu, keep);
+    if (bal == 0) return;
+    unsigned long long base = 0;
+    if ((threadIdx.x & 31) == 0) base = atomicAdd(d_num, (unsigned long long)__popc(bal));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (keep) {
+        uint64_t dst = base + __popc(bal & lanemask_lt());
+        out_keys[dst] = k;
+        out_info[dst] = v;
     }
 }
 
@@ -366,16 +452,64 @@ template <typename KeyT>
 void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, const KeyT *dummy_keys,
                 const uint32_t *dummy_info, const uint64_t *rank, uint64_t d, Alpha al,
                 KeyT *row_keys, uint8_t *row_info, uint32_t *row_counts, cudaStream_t stream,
-                unsigned *launches) {
+                unsigned *launches, uint32_t row_off) {
     merge_dummies_kernel<KeyT><<<(unsigned)div_up(d ? d : 1, (size_t)256), 256, 0, stream>>>(
-        dummy_keys, dummy_info, rank, d, al.K, row_keys, row_info, row_counts);
+        dummy_keys, dummy_info, rank, d, al.K, row_off, row_keys, row_info, row_counts);
     *launches += 1;
     if (m) {
         merge_reals_kernel<KeyT><<<(unsigned)div_up(m, (size_t)MR_TILE), MR_THREADS, 0, stream>>>(
-            reals, real_counts, m, rank, d, row_keys, row_info, row_counts);
+            reals, real_counts, m, rank, d, row_off, row_keys, row_info, row_counts);
         *launches += 1;
     }
     MTG_CUDA(cudaGetLastError());
+}
+
+template <typename KeyT>
+void target_nodes(const KeyT *reals, uint64_t m, Alpha al, KeyT *out, cudaStream_t stream,
+                  unsigned *launches) {
+    if (m == 0) return;
+    target_nodes_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(reals, m, al, out);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+template <typename KeyT>
+void ranged_dummy_candidates(const KeyT *reals, uint64_t m, const KeyT *targets, uint64_t nt, Alpha al,
+                             const uint64_t *bucket_idx, KeyT *sink_keys, uint64_t sink_cap,
+                             unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
+                             unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches) {
+    MTG_CUDA(cudaMemsetAsync(d_num_sink, 0, sizeof(unsigned long long), stream));
+    MTG_CUDA(cudaMemsetAsync(d_num_src, 0, sizeof(unsigned long long), stream));
+    uint64_t n = m > nt ? m : nt;
+    if (n == 0) return;
+    ranged_candidates_kernel<KeyT><<<(unsigned)div_up(n, (size_t)256), 256, 0, stream>>>(
+        reals, m, targets, nt, al, make_bi(al, bucket_idx), sink_keys, sink_cap, d_num_sink, src_fwd, src_cap,
+        d_num_src);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+template <typename KeyT>
+void filter_key_range(const KeyT *keys, const uint32_t *info, uint64_t n, KeyT lo, KeyT hi, int has_hi,
+                      KeyT *out_keys, uint32_t *out_info, unsigned long long *d_num, cudaStream_t stream,
+                      unsigned *launches) {
+    MTG_CUDA(cudaMemsetAsync(d_num, 0, sizeof(unsigned long long), stream));
+    if (n == 0) return;
+    filter_key_range_kernel<KeyT><<<(unsigned)div_up(n, (size_t)256), 256, 0, stream>>>(
+        keys, info, n, lo, hi, has_hi, out_keys, out_info, d_num);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+
+// bounds[b] = first position of the sorted array whose value >> shift is >= b, b = 0..2^B
+template <typename KeyT>
+void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, uint64_t *bounds,
+                   cudaStream_t stream, unsigned *launches) {
+    size_t nthreads = ((size_t)1 << B) + 1;
+    bucket_index_kernel<KeyT><<<(unsigned)div_up(nthreads, (size_t)256), 256, 0, stream>>>(sorted, n, B, shift,
+                                                                                        bounds);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
 }
 
 #define INSTANTIATE(KeyT)                                                                          \
@@ -393,7 +527,17 @@ void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, cons
                                     const uint64_t *, uint64_t *, cudaStream_t, unsigned *);                         \
     template void merge_rows<KeyT>(const KeyT *, const uint32_t *, uint64_t, const KeyT *,         \
                                    const uint32_t *, const uint64_t *, uint64_t, Alpha, KeyT *,    \
-                                   uint8_t *, uint32_t *, cudaStream_t, unsigned *);
+                                   uint8_t *, uint32_t *, cudaStream_t, unsigned *, uint32_t);     \
+    template void target_nodes<KeyT>(const KeyT *, uint64_t, Alpha, KeyT *, cudaStream_t, unsigned *); \
+    template void ranged_dummy_candidates<KeyT>(const KeyT *, uint64_t, const KeyT *, uint64_t, Alpha, \
+                                                const uint64_t *, KeyT *, uint64_t,               \
+                                                unsigned long long *, KeyT *, uint64_t,            \
+                                                unsigned long long *, cudaStream_t, unsigned *);   \
+    template void filter_key_range<KeyT>(const KeyT *, const uint32_t *, uint64_t, KeyT, KeyT, int, \
+                                         KeyT *, uint32_t *, unsigned long long *, cudaStream_t,   \
+                                         unsigned *);                                              \
+    template void bucket_bounds<KeyT>(const KeyT *, uint64_t, uint32_t, uint32_t, uint64_t *,      \
+                                      cudaStream_t, unsigned *);
 INSTANTIATE(uint64_t)
 INSTANTIATE(u128)
 

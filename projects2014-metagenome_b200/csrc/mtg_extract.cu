@@ -61,7 +61,7 @@ __device__ __forceinline__ KeyT boss_rotate(KeyT v, unsigned L, unsigned K) {
     return w_or(hi, w_shr(v, L * (K - 1)));
 }
 
-template <typename KeyT, int L, bool CANON, bool HAS_COUNT>
+template <typename KeyT, int L, int CANON, bool HAS_COUNT>   // CANON: 0 forward, 1 min(fwd, rc), 2 both strands
 __global__ void __launch_bounds__(EX_THREADS)
 extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut lut, uint32_t K,
                KeyT *__restrict__ out_keys, uint32_t *__restrict__ out_counts,
@@ -150,7 +150,8 @@ extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut l
     wprefix[threadIdx.x * 2 + 1] = excl + __popc(w0);
     const uint32_t block_total = scan_tmp[EX_THREADS / 32];
     if (threadIdx.x == 0)
-        sh_base = block_total ? atomicAdd(out_counter, (unsigned long long)block_total) : 0ull;
+        sh_base = block_total ? atomicAdd(out_counter, (unsigned long long)block_total * (CANON == 2 ? 2 : 1))
+                              : 0ull;
     __syncthreads();
     if (block_total == 0) return;
     const unsigned long long base = sh_base;
@@ -167,14 +168,16 @@ extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut l
             uint32_t p = wbase + it * 32 + lane;
             KeyT v = Win<KeyT>::load(codes, p * L, KL);
             KeyT key = boss_rotate(v, L, K);
+            KeyT rkey = key;
             if (CANON) {
                 // complement = ^3 on every 2-bit group, then reverse the groups
                 KeyT r = w_shr(rev2(w_not(v)), WordTraits<KeyT>::BITS - KL);
-                KeyT rkey = boss_rotate(r, L, K);
-                if (w_lt(rkey, key)) key = rkey;   // forward <= reverse keeps forward
+                rkey = boss_rotate(r, L, K);
+                if (CANON == 1 && w_lt(rkey, key)) key = rkey;   // forward <= reverse keeps forward
             }
-            uint64_t dst = base + wprefix[q] + __popc(word & lt);
+            uint64_t dst = base + (uint64_t)(wprefix[q] + __popc(word & lt)) * (CANON == 2 ? 2 : 1);
             out_keys[dst] = key;
+            if (CANON == 2) out_keys[dst + 1] = rkey;   // a palindrome is emitted twice (its count doubles)
             if (HAS_COUNT) {
                 // read containing this window: last start <= global position
                 uint64_t gp = tile_start + p;
@@ -184,12 +187,13 @@ extract_kernel(const uint8_t *__restrict__ packed, uint64_t nbytes, ExtractLut l
                     if (read_starts[mid] <= gp) lo = mid; else hi = mid;
                 }
                 out_counts[dst] = read_counts[lo];
+                if (CANON == 2) out_counts[dst + 1] = read_counts[lo];
             }
         }
     }
 }
 
-template <typename KeyT, int L, bool CANON>
+template <typename KeyT, int L, int CANON>
 void launch_extract(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream) {
     const uint32_t halo_groups = (a.K - 1 + EX_GROUP - 1) / EX_GROUP;
     const uint32_t ngroups = EX_THREADS + halo_groups;
@@ -213,12 +217,13 @@ template <typename KeyT>
 void extract_kmers(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream) {
     if (a.nbytes == 0) return;
     if (a.L == 2) {
-        if (a.canonical) launch_extract<KeyT, 2, true>(a, out_keys, stream);
-        else launch_extract<KeyT, 2, false>(a, out_keys, stream);
+        if (a.canonical && a.both) launch_extract<KeyT, 2, 2>(a, out_keys, stream);
+        else if (a.canonical) launch_extract<KeyT, 2, 1>(a, out_keys, stream);
+        else launch_extract<KeyT, 2, 0>(a, out_keys, stream);
     } else if (a.L == 5) {
-        launch_extract<KeyT, 5, false>(a, out_keys, stream);
+        launch_extract<KeyT, 5, 0>(a, out_keys, stream);
     } else {
-        launch_extract<KeyT, 3, false>(a, out_keys, stream);
+        launch_extract<KeyT, 3, 0>(a, out_keys, stream);
     }
 }
 

@@ -17,6 +17,7 @@ struct ExtractArgs {
     const ExtractLut *lut;        // host pointer, passed by value to the kernel
     uint32_t K, L;
     bool canonical;
+    bool both = false;            // canonical only: emit the window AND its reverse complement
     uint32_t *out_counts;         // nullable: per-k-mer multiplicity payload
     unsigned long long *out_counter;   // device: running number of emitted k-mers
     const uint64_t *read_starts;  // device, packed start of each read (count mode)
@@ -116,7 +117,26 @@ template <typename KeyT>
 void merge_rows(const KeyT *reals, const uint32_t *real_counts, uint64_t m, const KeyT *dummy_keys,
                 const uint32_t *dummy_info, const uint64_t *rank, uint64_t d, Alpha al,
                 KeyT *row_keys, uint8_t *row_info, uint32_t *row_counts, cudaStream_t stream,
-                unsigned *launches);
+                unsigned *launches, uint32_t row_off = 2);
+
+// ---- range-partitioned (multi-GPU) build, SURVEY.md 8e ----------------------------------------
+// out[i] = target node of reals[i] (node word, (K-1)*L bits)
+template <typename KeyT>
+void target_nodes(const KeyT *reals, uint64_t m, Alpha al, KeyT *out, cudaStream_t stream,
+                  unsigned *launches);
+// sinks = targets \ source nodes of `reals`; sources-1 = source nodes \ targets (forward-lex)
+template <typename KeyT>
+void ranged_dummy_candidates(const KeyT *reals, uint64_t m, const KeyT *targets, uint64_t nt, Alpha al,
+                             const uint64_t *bucket_idx, KeyT *sink_keys, uint64_t sink_cap,
+                             unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
+                             unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches);
+template <typename KeyT>
+void filter_key_range(const KeyT *keys, const uint32_t *info, uint64_t n, KeyT lo, KeyT hi, int has_hi,
+                      KeyT *out_keys, uint32_t *out_info, unsigned long long *d_num, cudaStream_t stream,
+                      unsigned *launches);
+template <typename KeyT>
+void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, uint64_t *bounds,
+                   cudaStream_t stream, unsigned *launches);
 
 // ---- K6 chunk emit -------------------------------------------------------
 // Writes W / last / weights in sdsl int_vector word layout and F[sigma].
