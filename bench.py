@@ -356,7 +356,7 @@ def run_ours(args, wl):
 
 def main():
     args = parse_args()
-    wl = dict(WORKLOADS[args.workload or ("cfg2" if args.gpus == 1 else "cfg3")])
+    wl = dict(WORKLOADS[args.workload or "cfg2"])
     if args.reads:
         wl["G"] = max(2 * wl["read_len"], int(wl["G"] * args.reads / wl["n_reads"]))
         wl["n_reads"] = args.reads

@@ -245,3 +245,126 @@ def gather_chunks(chunk, dist, group=None, dst=0):
     if objs is None:
         return None
     return concat_chunks(objs)
+
+
+# ---- bench.py --gpus N (N > 1) -------------------------------------------------------------------
+
+def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_bytes):
+    """Weak scaling of the bench workload: every rank holds its own shard of wl['n_reads'] reads
+    of a genome that grows with the number of ranks (same coverage, same duplication), generated
+    straight into HBM. value = k-mers of all ranks / max-over-ranks time."""
+    import json
+    import os
+    import time
+    import torch
+    import torch.distributed as dist
+    from . import synth
+
+    K, L = wl["K"], wl["read_len"]
+    n_local = wl["n_reads"]
+    n_total = n_local * world
+    G = wl["G"] * world
+    # rows [rank*n_local, (rank+1)*n_local) of the world-sized read set
+    packed = synth.dna_reads_packed_torch(wl["seed"], n_total, L, G, wl["e"], device=dev,
+                                          r0=rank * n_local, r1=(rank + 1) * n_local)
+    n_bytes = packed.numel()
+    n_windows = n_local * (L - K + 1)
+    db = DistBuild(K, wl["canonical"], wl["bpc"], device=dev.index)
+    stream = torch.cuda.current_stream()
+    db.rank.ctor.set_stream(stream.cuda_stream)
+
+    def step():
+        db.rank.ctor.add_packed_device(packed.data_ptr(), n_bytes, n_windows)
+        return db.build(device_output=True)
+
+    for _ in range(args.warmup):
+        st = step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    sampler = ClockSampler(dev.index)
+    if rank == 0:
+        sampler.start()
+    db.a2a_bytes, db.a2a_ms = 0, 0.0
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ev0.record(stream)
+    stats = [step() for _ in range(args.steps)]
+    ev1.record(stream)
+    torch.cuda.synchronize()
+    dist.barrier()
+    ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    counters = torch.tensor([stats[-1]["n_input_kmers"], stats[-1]["n_real"], stats[-1]["n_rows"] - 1,
+                             db.a2a_bytes, sum(s["n_kernel_launches"] for s in stats)],
+                            dtype=torch.int64, device=dev)
+    dist.all_reduce(counters)
+    a2a = torch.tensor([db.a2a_ms], dtype=torch.float64, device=dev)
+    dist.all_reduce(a2a, op=dist.ReduceOp.MAX)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # end to end: host reads in (pinned), per-rank chunk out to host memory
+    e2e = None
+    if not args.no_e2e:
+        host = torch.empty((n_local, L), dtype=torch.uint8, pin_memory=True)
+        host.copy_(packed[:, :L])
+        torch.cuda.synchronize()
+        bases = host.numpy().reshape(-1)
+        offsets = np.arange(n_local + 1, dtype=np.uint64) * np.uint64(L)
+
+        def step_host():
+            db.rank.ctor.add_packed(bases, offsets)
+            return db.build(device_output=False)
+
+        chunk = step_host()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e_steps = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(e_steps):
+            chunk = step_host()
+        torch.cuda.synchronize()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        d2h = torch.tensor([chunk.stats["chunk_bytes"]], dtype=torch.int64, device=dev)
+        dist.all_reduce(d2h)
+        e2e = {"value": int(counters[0]) * e_steps / float(dt), "unit": UNIT,
+               "h2d_bytes_per_step": int(n_total * (L + 1)), "d2h_bytes_per_step": int(d2h),
+               "ms_per_step": 1e3 * float(dt) / e_steps, "steps": e_steps,
+               "api": "per rank: mtg_push_reads(host) + mtg_mg_* phases + NCCL all-to-all, chunk to host"}
+    db.close()
+    if rank != 0:
+        return
+    ms_total = float(ms)
+    N = int(counters[0])
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))),
+                                            "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    a2a_gbs = (int(counters[3]) / world / args.steps) / (float(a2a) / args.steps * 1e-3) / 1e9 if float(a2a) else 0.0
+    line = {
+        "metric": METRIC, "value": N * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u64" if K * 2 <= 64 else "u128", "data": "synthetic",
+        "config": {"workload": wl["name"] + " per GPU (weak scaling: %d reads, genome %d bp in total)"
+                               % (n_total, G),
+                   "n_reads_per_gpu": n_local, "read_len": L, "k": K,
+                   "mode": "canonical" if wl["canonical"] else "basic", "count_width": wl["bpc"],
+                   "input_kmers": N, "real_kmers": int(counters[1]), "rows": int(counters[2]) + 1,
+                   "partitioning": "key range (top 8 bits of the k-mer word), NCCL all-to-all of k-mers "
+                                   "and target nodes, all-gather of source nodes",
+                   "l2_policy": "inputs larger than L2 (%.2f GB of keys per GPU and step)"
+                                % (n_windows * 8 * (2 if wl["canonical"] else 1) / 1e9)},
+        "clocks": clocks, "e2e": e2e, "gpu_launches": int(counters[4]),
+        "roofline": {"bound": "hbm", "kernel": "whole path per GPU (SURVEY 8d byte model)",
+                     "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None,
+                     "alltoall": {"bytes_sent_per_gpu_per_step": int(counters[3]) / world / args.steps,
+                                  "ms_per_step": float(a2a) / args.steps, "achieved_GBps": a2a_gbs,
+                                  "peak_GBps": 900.0, "frac": a2a_gbs / 900.0}},
+        "cpu_baseline": None,
+    }
+    print(json.dumps(line))

@@ -108,20 +108,23 @@ def _h_t(seed, stream, idx):
     return _mix_t(idx + _to_i64((seed * _C1) + (stream * _C2)))
 
 
-def dna_reads_packed_torch(seed, n_reads, read_len, G, e=0.005, device="cuda", chunk=1 << 20):
-    """Packed (n_reads, read_len+1) uint8 tensor generated on `device`."""
+def dna_reads_packed_torch(seed, n_reads, read_len, G, e=0.005, device="cuda", chunk=1 << 20, r0=0,
+                           r1=None):
+    """Rows r0..r1 of the packed (n_reads, read_len+1) uint8 matrix, generated on `device`."""
     import torch
     gen = torch.empty(G, dtype=torch.uint8, device=device)
     for lo in range(0, G, 1 << 26):
         hi = min(G, lo + (1 << 26))
         j = torch.arange(lo, hi, dtype=torch.int64, device=device)
         gen[lo:hi] = _lsr(_h_t(seed, 0, j), 62).to(torch.uint8)
-    out = torch.zeros((n_reads, read_len + 1), dtype=torch.uint8, device=device)
+    r_end = n_reads if r1 is None else r1
+    r_begin = r0
+    out = torch.zeros((r_end - r_begin, read_len + 1), dtype=torch.uint8, device=device)
     lut = torch.tensor(list(b"ACGT"), dtype=torch.uint8, device=device)
     pos = torch.arange(read_len, dtype=torch.int64, device=device)
     thr = int(e * (1 << 24))
-    for r0 in range(0, n_reads, chunk):
-        r1 = min(n_reads, r0 + chunk)
+    for r0 in range(r_begin, r_end, chunk):
+        r1 = min(r_end, r0 + chunk)
         r = torch.arange(r0, r1, dtype=torch.int64, device=device)
         start = _lsr(_h_t(seed, 1, r), 1) % (G - read_len + 1)
         rc = _lsr(_h_t(seed, 2, r), 63).to(torch.bool)
@@ -131,7 +134,7 @@ def dna_reads_packed_torch(seed, n_reads, read_len, G, e=0.005, device="cuda", c
         codes = torch.where(sub, _lsr(u, 10) & 3, codes)
         codes_rc = (3 - codes).flip(1)
         codes = torch.where(rc[:, None], codes_rc, codes)
-        out[r0:r1, :read_len] = lut[codes]
+        out[r0 - r_begin:r1 - r_begin, :read_len] = lut[codes]
     return out
 
 

@@ -1,0 +1,101 @@
+"""CPU tests of the host-side logic of the multi-GPU path (multi_gpu.py): range planning, split
+sizes, and -- over a world_size-2 gloo group -- the size exchange + routing invariants and the
+gathering/concatenation of per-rank chunks (BOSS::Chunk::extend order)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import mtg_b200
+from mtg_b200 import multi_gpu
+from test_host_chunk import chunk_from_arrays
+from test_oracle_golden import load_golden
+
+
+def test_plan_ranges_properties():
+    rng = np.random.default_rng(0)
+    for world in (1, 2, 3, 4, 8):
+        for hist in (np.ones(256), rng.integers(0, 1000, 256), np.r_[np.zeros(200), 1e9, np.zeros(55)],
+                     np.zeros(256), rng.integers(0, 5, 16), np.array([7.0])):
+            r = multi_gpu.plan_ranges(hist, world)
+            assert len(r) == world and r[0][0] == 0 and r[-1][1] == len(hist)
+            assert all(r[i][1] == r[i + 1][0] for i in range(world - 1))
+            assert all(lo <= hi for lo, hi in r)
+            assert sum(multi_gpu.split_sizes(hist, r)) == int(np.sum(hist))
+    # uniform data is split evenly
+    assert multi_gpu.plan_ranges(np.ones(256), 8) == [(32 * i, 32 * i + 32) for i in range(8)]
+    sizes = multi_gpu.split_sizes(np.random.default_rng(1).integers(900, 1100, 256), multi_gpu.plan_ranges(
+        np.random.default_rng(1).integers(900, 1100, 256), 8))
+    assert max(sizes) < 1.05 * (sum(sizes) / 8)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, tmp):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        # --- routing plan: every rank has bucket-grouped keys; plan on the summed histogram ---
+        rng = np.random.default_rng(100 + rank)
+        keys = np.sort(rng.integers(0, 1 << 16, 5000 + 1000 * rank).astype(np.int64))   # 16-bit "k-mers"
+        buckets = keys >> 8
+        counts = np.bincount(buckets, minlength=256)
+        hist = torch.from_numpy(counts.copy())
+        dist.all_reduce(hist)
+        ranges = multi_gpu.plan_ranges(hist.numpy(), world)
+        send = multi_gpu.split_sizes(counts, ranges)
+        all_sizes = [torch.empty(world, dtype=torch.int64) for _ in range(world)]
+        dist.all_gather(all_sizes, torch.tensor(send, dtype=torch.int64))
+        recv_sizes = [int(all_sizes[s][rank]) for s in range(world)]
+        # exchange by all_gather + slicing (the NCCL path uses all_to_all_single with these sizes)
+        gathered = [None] * world
+        dist.all_gather_object(gathered, keys)
+        mine = []
+        for s in range(world):
+            c = np.bincount(gathered[s] >> 8, minlength=256)
+            offs = multi_gpu._bucket_offsets(c, ranges)
+            part = gathered[s][offs[rank][0]:offs[rank][1]]
+            assert len(part) == recv_sizes[s]
+            mine.append(part)
+        mine = np.concatenate(mine)
+        lo, hi = ranges[rank]
+        assert ((mine >> 8) >= lo).all() and ((mine >> 8) < hi).all()
+        total = torch.tensor([len(mine)])
+        dist.all_reduce(total)
+        assert int(total) == sum(len(g) for g in gathered)
+        # --- chunks: rank r holds rows of a golden chunk; rank 0 concatenates in rank order ---
+        g = load_golden("cfg3_k31_count8")
+        n = len(g["W"])
+        cut = [0, n // 3, n] if world == 2 else np.linspace(0, n, world + 1).astype(int)
+        a, b = int(cut[rank]), int(cut[rank + 1])
+        part = {k: (np.concatenate([[0], g[k][a:b]]) if rank else g[k][a:b]) for k in ("W", "last", "weights")}
+        part["F"] = g["F"] if rank == 0 else np.zeros_like(g["F"])
+        part["sigma"] = g["sigma"]
+        chunk = chunk_from_arrays(part, 30, 8)
+        full = multi_gpu.gather_chunks(chunk, dist)
+        if rank == 0:
+            assert full.n_rows == n
+            assert np.array_equal(full.W, g["W"]) and np.array_equal(full.last, g["last"])
+            assert np.array_equal(full.weights, g["weights"]) and np.array_equal(full.F, g["F"])
+            open(os.path.join(tmp, "ok"), "w").write("ok")
+        else:
+            assert full is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2])
+def test_gloo_world2_routing_and_chunk_gather(world, tmp_path):
+    mp.spawn(_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert os.path.exists(tmp_path / "ok")
