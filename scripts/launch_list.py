@@ -3,7 +3,7 @@ import csv, re, sys
 rows = [r for r in csv.reader(open(sys.argv[1])) if len(r) > 10]
 h = rows[0]; ki = h.index('Kernel Name'); vi = h.index('Metric Value')
 seq = [(re.sub(r'\(.*', '', r[ki]).replace('mtg::<unnamed>::', '').replace('void ', ''), float(r[vi].replace(',', ''))) for r in rows[1:]]
-idx = [i for i, s in enumerate(seq) if s[0].startswith('extract')]
+idx = [i for i, s in enumerate(seq) if "extract_kernel" in s[0] or "extract_suffix" in s[0]]
 start = idx[-1] if idx else 0
 tot = 0
 prev = None; acc = 0; cnt = 0
