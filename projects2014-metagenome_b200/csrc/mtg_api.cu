@@ -892,17 +892,19 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     }
     const uint64_t *d_bidx = use_index ? bidx.as<uint64_t>() : nullptr;
     DevBuf sink, src, srcB;
+    DevBuf dscratch(dummy_scratch_bytes(m, al), s);
     uint64_t n_sink = 0, d1 = 0;
     while (true) {
         sink.alloc(sizeof(KeyT) * cap, s);
         src.alloc(sizeof(KeyT) * cap, s);
-        find_dummy_candidates<KeyT>(reals, m, al, d_bidx, sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap,
+        find_dummy_candidates<KeyT>(reals, m, al, d_bidx, dscratch.p, sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap,
                                     d_ctr + 1, s, &ctx->launches);
         n_sink = read_counter(d_ctr, s);
         d1 = read_counter(d_ctr + 1, s);
         if (n_sink <= cap && d1 <= cap) break;
         cap = std::max(n_sink, d1);
     }
+    dscratch.release();
     uint64_t d = 0;
     DevBuf dk0, di0;
     expand_sources<KeyT>(ctx, src, d1, sink, n_sink, d_ctr, dk0, di0, &d);

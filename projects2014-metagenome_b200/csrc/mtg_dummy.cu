@@ -71,61 +71,153 @@ __device__ __forceinline__ void warp_append(bool emit, KeyT v, KeyT *out, uint64
     }
 }
 
+// ---- windowed merge-join version of the candidate search (single-GPU path) ------------------
+// The sink probe of a real x with edge label c is  sink(x, c) = [c, s_{K-1}..s_2 | 0]: for a
+// fixed c it is monotone in the position of x, so the probes of DC_TILE consecutive reals with
+// label c fall into one contiguous window of the reals (inside the range whose last node
+// character is c) -- the cursor it[c] of add_dummy_sink_kmers (boss_chunk_construct.cpp:66-93),
+// tile by tile. dc_partition_kernel finds the window bounds, dc_sinks_kernel stages the windows
+// in shared memory and searches there. A hit at position p (the head of node t) also records
+// "node p has an incoming real edge" in a bitmap, which turns the redundancy test of
+// add_dummy_source_kmers (:151-163) into one bit lookup per node head (dc_sources_kernel).
+constexpr int DC_THREADS = 256;
+constexpr int DC_IPT = 8;
+constexpr int DC_TILE = DC_THREADS * DC_IPT;
+constexpr int DC_POOL = 3 * DC_TILE;          // window keys staged per tile (all labels together)
+constexpr int DC_MAX_CH = 32;
+
+template <typename KeyT>
+__device__ __forceinline__ KeyT sink_probe(KeyT x, KeyT c, uint32_t L, uint32_t K) {
+    return w_and(w_or(w_shr(x, L), w_shl(c, L * (K - 1))), w_not(WordTraits<KeyT>::low_mask(L)));
+}
+
+// part[j * nch + c] = lower_bound(reals, sink(reals[min(j * DC_TILE, m - 1)], c)), j = 0..tiles
+template <typename KeyT>
+__global__ void dc_partition_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t nch,
+                                    BucketIndex bi, uint64_t tiles, uint64_t *__restrict__ part) {
+    uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (tiles + 1) * nch) return;
+    uint64_t j = t / nch;
+    uint32_t c = (uint32_t)(t % nch);
+    uint64_t pos = j * DC_TILE < m ? j * DC_TILE : m - 1;
+    KeyT probe = sink_probe(reals[pos], WordTraits<KeyT>::from_u64(c), al.L, al.K);
+    part[t] = lower_bound_idx(reals, m, bi, probe);
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(DC_THREADS)
+dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t nch, BucketIndex bi,
+                const uint64_t *__restrict__ part, uint32_t *__restrict__ incoming,
+                KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink) {
+    using WT = WordTraits<KeyT>;
+    extern __shared__ __align__(16) unsigned char dc_smem[];
+    KeyT *win = reinterpret_cast<KeyT *>(dc_smem);       // [DC_POOL]
+    __shared__ uint64_t w_lo[DC_MAX_CH];
+    __shared__ uint32_t w_off[DC_MAX_CH + 1];           // pool offset of the window, ~0u = not staged
+    __shared__ uint32_t w_len[DC_MAX_CH];
+    const uint32_t L = al.L, K = al.K;
+    const KeyT maskL = WT::low_mask(L);
+    const uint64_t j = blockIdx.x;
+    const uint64_t i0 = j * DC_TILE;
+    if (threadIdx.x < nch) {
+        uint64_t lo = part[j * nch + threadIdx.x];
+        uint64_t hi = part[(j + 1) * nch + threadIdx.x] + 1;
+        if (hi > m) hi = m;
+        w_lo[threadIdx.x] = lo;
+        w_len[threadIdx.x] = hi > lo ? (uint32_t)(hi - lo < 0xffffffffull ? hi - lo : 0xffffffffull) : 0;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t off = 0;
+        for (uint32_t c = 0; c < nch; ++c) {
+            if (w_len[c] <= (uint32_t)DC_POOL - off) { w_off[c] = off; off += w_len[c]; }
+            else w_off[c] = ~0u;
+        }
+        w_off[nch] = off;
+    }
+    __syncthreads();
+    for (uint32_t c = 0; c < nch; ++c) {
+        if (w_off[c] == ~0u) continue;
+        const uint64_t lo = w_lo[c];
+        KeyT *dst = win + w_off[c];
+        for (uint32_t t = threadIdx.x; t < w_len[c]; t += DC_THREADS) dst[t] = reals[lo + t];
+    }
+    __syncthreads();
+
+#pragma unroll 2
+    for (int r = 0; r < DC_IPT; ++r) {
+        const uint64_t i = i0 + (uint64_t)r * DC_THREADS + threadIdx.x;
+        bool emit_sink = false;
+        KeyT sink = WT::zero();
+        if (i < m) {
+            KeyT x = reals[i];
+            KeyT W = w_and(x, maskL);
+            KeyT grp = w_shr(x, 2 * L);
+            bool first = true;   // first element of its (x >> 2L, W) class = distinct target node
+            for (uint64_t q = i; q-- > 0;) {
+                KeyT y = reals[q];
+                if (!w_eq(w_shr(y, 2 * L), grp)) break;
+                if (w_eq(w_and(y, maskL), W)) { first = false; break; }
+            }
+            if (first) {
+                sink = sink_probe(x, W, L, K);
+                const uint32_t c = (uint32_t)w_low64(W);
+                uint64_t p;
+                KeyT at = WT::zero();
+                bool have = false;
+                if (w_off[c] != ~0u) {
+                    const KeyT *wk = win + w_off[c];
+                    uint32_t lo = 0, hi = w_len[c];
+                    while (lo < hi) {
+                        uint32_t mid = (lo + hi) >> 1;
+                        if (w_lt(wk[mid], sink)) lo = mid + 1; else hi = mid;
+                    }
+                    p = w_lo[c] + lo;
+                    if (lo < w_len[c]) { at = wk[lo]; have = true; }
+                    else if (p < m) { at = reals[p]; have = true; }
+                } else {
+                    p = lower_bound_idx(reals, m, bi, sink);
+                    if (p < m) { at = reals[p]; have = true; }
+                }
+                if (have && w_eq(w_shr(at, L), w_shr(sink, L)))
+                    atomicOr(&incoming[p >> 5], 1u << (p & 31));   // node at p has an incoming edge
+                else
+                    emit_sink = true;
+            }
+        }
+        warp_append(emit_sink, sink, sink_keys, sink_cap, d_num_sink);
+    }
+}
+
+// node heads without an incoming real edge -> source-1 candidates (forward-lex packing)
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
-dummy_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, BucketIndex bi,
-                        KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink,
-                        KeyT *src_fwd, uint64_t src_cap, unsigned long long *d_num_src) {
+dc_sources_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al,
+                  const uint32_t *__restrict__ incoming, KeyT *src_fwd, uint64_t src_cap,
+                  unsigned long long *d_num_src) {
     using WT = WordTraits<KeyT>;
     const uint32_t L = al.L, K = al.K;
     const KeyT maskL = WT::low_mask(L);
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    bool emit_sink = false, emit_src = false;
-    KeyT sink = WT::zero(), fwd = WT::zero();
-    if (i < m) {
-        KeyT x = reals[i];
-        KeyT W = w_and(x, maskL);
-        // ---- sink: first element of its (x >> 2L, W) class? ----
-        KeyT grp = w_shr(x, 2 * L);
-        bool first = true;
-        for (uint64_t j = i; j-- > 0;) {
-            KeyT y = reals[j];
-            if (!w_eq(w_shr(y, 2 * L), grp)) break;
-            if (w_eq(w_and(y, maskL), W)) { first = false; break; }
-        }
-        if (first) {
-            // to_next(K, 0): [s_K, s_{K-1}..s_2 | 0]
-            sink = w_and(w_or(w_shr(x, L), w_shl(W, L * (K - 1))), w_not(maskL));
-            uint64_t p = lower_bound_idx(reals, m, bi, sink);
-            emit_sink = !(p < m && w_eq(w_shr(reals[p], L), w_shr(sink, L)));
-        }
-        // ---- source-1: first k-mer of its node? ----
-        KeyT node = w_shr(x, L);
-        bool node_head = i == 0 || !w_eq(w_shr(reals[i - 1], L), node);
-        if (node_head) {
-            // to_prev(K, 0): [s_{K-2}..s_1, 0 | s_{K-1}]; group prefix = s_{K-2}..s_1
-            KeyT top = w_shr(x, L * (K - 1));   // s_{K-1}
-            KeyT prev = w_and(w_shl(w_and(x, w_not(maskL)), L), WT::low_mask(L * K));
-            KeyT g = w_shr(prev, 2 * L);
-            uint64_t p = lower_bound_idx(reals, m, bi, prev);   // prev has W = 0, x_1 = 0
-            bool redundant = false;
-            for (; p < m; ++p) {
-                KeyT y = reals[p];
-                if (!w_eq(w_shr(y, 2 * L), g)) break;
-                if (w_eq(w_and(y, maskL), top)) { redundant = true; break; }
-            }
-            if (!redundant) {
+    const uint64_t base = ((uint64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) * 4;
+    const unsigned lane = threadIdx.x & 31;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const uint64_t i = base + r * 32 + lane;   // the warp covers one bitmap word per round
+        bool emit_src = false;
+        KeyT fwd = WT::zero();
+        if (i < m) {
+            KeyT x = reals[i];
+            bool node_head = i == 0 || !w_eq(w_shr(reals[i - 1], L), w_shr(x, L));
+            if (node_head && !((incoming[i >> 5] >> (i & 31)) & 1u)) {
                 emit_src = true;
-                // forward-lex packing of the node: s_1 most significant
                 for (uint32_t c = 1; c < K; ++c) {
                     KeyT ch = w_and(w_shr(x, L * c), maskL);
                     fwd = w_or(fwd, w_shl(ch, L * (K - 1 - c)));
                 }
             }
         }
+        warp_append(emit_src, fwd, src_fwd, src_cap, d_num_src);
     }
-    warp_append(emit_sink, sink, sink_keys, sink_cap, d_num_sink);
-    warp_append(emit_src, fwd, src_fwd, src_cap, d_num_src);
 }
 
 template <typename KeyT>
@@ -402,18 +494,41 @@ void build_bucket_index(const KeyT *reals, uint64_t m, Alpha al, uint64_t *idx, 
     *launches += 1;
 }
 
+size_t dummy_scratch_bytes(uint64_t m, Alpha al) {
+    const uint64_t tiles = div_up(m, (size_t)DC_TILE);
+    const uint32_t nch = al.sigma - 1;
+    return 8 * (tiles + 1) * nch + 4 * (m / 32 + 2);
+}
+
 template <typename KeyT>
 void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64_t *bucket_idx,
-                           KeyT *sink_keys, uint64_t sink_cap,
+                           void *scratch, KeyT *sink_keys, uint64_t sink_cap,
                            unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
                            unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches) {
     MTG_CUDA(cudaMemsetAsync(d_num_sink, 0, sizeof(unsigned long long), stream));
     MTG_CUDA(cudaMemsetAsync(d_num_src, 0, sizeof(unsigned long long), stream));
     if (m == 0) return;
-    dummy_candidates_kernel<KeyT><<<(unsigned)div_up(m, (size_t)256), 256, 0, stream>>>(
-        reals, m, al, make_bi(al, bucket_idx), sink_keys, sink_cap, d_num_sink, src_fwd, src_cap, d_num_src);
+    const uint64_t tiles = div_up(m, (size_t)DC_TILE);
+    const uint32_t nch = al.sigma - 1;
+    uint64_t *part = reinterpret_cast<uint64_t *>(scratch);
+    uint32_t *incoming = reinterpret_cast<uint32_t *>(part + (tiles + 1) * nch);
+    MTG_CUDA(cudaMemsetAsync(incoming, 0, 4 * (m / 32 + 2), stream));
+    const BucketIndex bi = make_bi(al, bucket_idx);
+    dc_partition_kernel<KeyT><<<(unsigned)div_up((tiles + 1) * nch, (size_t)256), 256, 0, stream>>>(
+        reals, m, al, nch, bi, tiles, part);
+    const size_t smem = sizeof(KeyT) * DC_POOL;
+    auto kern = dc_sinks_kernel<KeyT>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    kern<<<(unsigned)tiles, DC_THREADS, smem, stream>>>(reals, m, al, nch, bi, part, incoming, sink_keys,
+                                                       sink_cap, d_num_sink);
+    dc_sources_kernel<KeyT><<<(unsigned)div_up(m, (size_t)1024), 256, 0, stream>>>(reals, m, al, incoming,
+                                                                                 src_fwd, src_cap, d_num_src);
     MTG_CUDA(cudaGetLastError());
-    *launches += 1;
+    *launches += 3;
 }
 
 template <typename KeyT>
@@ -515,7 +630,7 @@ void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, u
 #define INSTANTIATE(KeyT)                                                                          \
     template void build_bucket_index<KeyT>(const KeyT *, uint64_t, Alpha, uint64_t *, cudaStream_t, \
                                            unsigned *);                                           \
-    template void find_dummy_candidates<KeyT>(const KeyT *, uint64_t, Alpha, const uint64_t *, KeyT *, uint64_t, \
+    template void find_dummy_candidates<KeyT>(const KeyT *, uint64_t, Alpha, const uint64_t *, void *, KeyT *, uint64_t, \
                                               unsigned long long *, KeyT *, uint64_t,              \
                                               unsigned long long *, cudaStream_t, unsigned *);     \
     template void source_prefix_counts<KeyT>(const KeyT *, uint64_t, Alpha, uint32_t *,            \

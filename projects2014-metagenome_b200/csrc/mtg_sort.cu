@@ -540,6 +540,179 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     }
 }
 
+// ---------------------------------------------------------------------------
+// Kernel S3 (v4): ballot-ranked onesweep pass.
+// The ncu capture of v3 (profiles/r01_ncu_full_v2_101ms.txt) shows the pass bound by the
+// shared-memory pipe (L1TEX 80 %, 35 wavefronts per warp-row of keys, 57 % of them bank
+// conflicts of the two atomics + mask read-back + mask reset per key). Here the peer mask of a
+// key is built from 8 warp ballots (one per digit bit; VOTE does not touch shared memory), so a
+// key costs one counter read, one leader write, and the tile-order scatter:
+//   peers = AND_b (bit_b(d) ? ballot(bit_b) : ~ballot(bit_b))
+//   rank  = my_hist[d] + popc(peers & lanemask_lt);  leader: my_hist[d] += popc(peers)
+// The tile's digit counts are known after the ranking loop (no separate counting pass).
+// ---------------------------------------------------------------------------
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
+__global__ void __launch_bounds__(THREADS, MINB)
+onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out_keys,
+                        const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
+                        uint64_t n, DigitPass dp, const unsigned long long *__restrict__ digit_offsets,
+                        unsigned long long *__restrict__ status, unsigned int *tile_counter,
+                        unsigned epoch) {
+    constexpr int WARPS = THREADS / 32;
+    constexpr int TILE = THREADS * IPT;
+    static_assert(THREADS >= RADIX, "one digit per thread in the scan phases");
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    KeyT *sh_keys = reinterpret_cast<KeyT *>(smem_raw);                       // [TILE]
+    uint32_t *sh_vals = reinterpret_cast<uint32_t *>(sh_keys + TILE);        // [HAS_VAL ? TILE : 0]
+    uint32_t *whist = sh_vals + (HAS_VAL ? TILE : 0);                        // [WARPS][RADIX]
+    long long *goff = reinterpret_cast<long long *>(whist + WARPS * RADIX);  // [RADIX]
+    uint32_t *warp_tot = reinterpret_cast<uint32_t *>(goff + RADIX);         // [WARPS + 1]
+    __shared__ unsigned int sh_tile;
+
+    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) sh_tile = atomicAdd(tile_counter, 1u);
+    for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;
+    __syncthreads();
+    const unsigned tile = sh_tile;
+    const uint64_t tile_base = (uint64_t)tile * TILE;
+    const uint32_t tile_valid = (uint32_t)(n - tile_base < (uint64_t)TILE ? n - tile_base : TILE);
+    const bool full = tile_valid == TILE;
+
+    KeyT key[IPT];
+    uint32_t val[IPT];
+    uint32_t *my_hist = whist + warp * RADIX;
+    const uint32_t warp_base = warp * (IPT * 32);
+#pragma unroll
+    for (int r = 0; r < IPT; ++r) {
+        uint32_t idx = warp_base + r * 32 + lane;
+        if (full || idx < tile_valid) {
+            key[r] = in_keys[tile_base + idx];
+            val[r] = HAS_VAL ? in_vals[tile_base + idx] : 0;
+        } else {
+            key[r] = WordTraits<KeyT>::zero();
+            val[r] = 0;
+        }
+    }
+
+    // ---- rank inside the warp: 8 ballots per row, running per-warp digit counters ----
+    const unsigned lt = lanemask_lt();
+    uint32_t rank[IPT];
+#pragma unroll
+    for (int r = 0; r < IPT; ++r) {
+        const uint32_t idx = warp_base + r * 32 + lane;
+        const bool valid = full || idx < tile_valid;
+        const uint32_t d = digit_of(key[r], val[r], dp);
+        unsigned peers = full ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
+#pragma unroll
+        for (int b = 0; b < RADIX_BITS; ++b) {
+            const bool bit = (d >> b) & 1u;
+            const unsigned bal = __ballot_sync(0xffffffffu, bit);
+            peers &= bit ? bal : ~bal;
+        }
+        uint32_t before = 0;
+        if (valid) before = my_hist[d];
+        __syncwarp();
+        if (valid && (peers & lt) == 0) my_hist[d] = before + __popc(peers);
+        __syncwarp();
+        rank[r] = before + __popc(peers & lt);
+    }
+    __syncthreads();
+
+    // ---- per digit: exclusive prefix over warps, tile count, publish, tile-local digit start ----
+    uint32_t count = 0;
+    if (tid < RADIX) {
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) count += whist[w * RADIX + tid];
+        if (tile > 0)
+            st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(1, epoch, count));
+    }
+    uint32_t inc = count;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= (unsigned)o) inc += t;
+    }
+    if (lane == 31) warp_tot[warp] = inc;
+    __syncthreads();
+    uint32_t local_base = 0;
+    if (tid < RADIX) {
+        for (unsigned w = 0; w < warp; ++w) local_base += warp_tot[w];
+        local_base += inc - count;
+        uint32_t run = local_base;   // whist[w][d] := tile position of warp w's first key with digit d
+#pragma unroll
+        for (int w = 0; w < WARPS; ++w) {
+            uint32_t t = whist[w * RADIX + tid];
+            whist[w * RADIX + tid] = run;
+            run += t;
+        }
+    }
+    __syncthreads();
+
+    // ---- scatter into shared memory in tile-sorted order ----
+#pragma unroll
+    for (int r = 0; r < IPT; ++r) {
+        const uint32_t idx = warp_base + r * 32 + lane;
+        if (full || idx < tile_valid) {
+            const uint32_t d = digit_of(key[r], val[r], dp);
+            const uint32_t pos = my_hist[d] + rank[r];
+            sh_keys[pos] = key[r];
+            if (HAS_VAL) sh_vals[pos] = val[r];
+        }
+    }
+
+    // ---- decoupled look-back per digit ----
+    if (tid < RADIX) {
+        unsigned long long excl = 0;
+        if (LB == 0) {
+            if (tile > 0) {
+                long long t = (long long)tile - 1;
+                while (true) {
+                    unsigned long long s = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
+                    unsigned flag = (unsigned)(s >> 62);
+                    if (flag == 0 || ((s >> 56) & 63) != epoch) continue;   // not published yet
+                    excl += s & OS_VALUE_MASK;
+                    if (flag == 2) break;
+                    --t;
+                }
+            }
+        } else {
+            excl = lookback_digit<(LB > 0 ? LB : 1)>(status, tile, tid, epoch);
+        }
+        st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(2, epoch, excl + count));
+        goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
+    }
+    __syncthreads();
+
+    // ---- coalesced write-out ----
+#pragma unroll 4
+    for (uint32_t p = tid; p < tile_valid; p += THREADS) {
+        KeyT k = sh_keys[p];
+        uint32_t v = HAS_VAL ? sh_vals[p] : 0;
+        uint32_t d = digit_of(k, v, dp);
+        size_t dst = (size_t)(goff[d] + (long long)p);
+        out_keys[dst] = k;
+        if (HAS_VAL) out_vals[dst] = v;
+    }
+}
+
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
+void launch_v4(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
+               uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
+               unsigned int *ctr, unsigned epoch, cudaStream_t stream) {
+    constexpr int TILE = THREADS * IPT;
+    size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
+                  + sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
+                  + sizeof(uint32_t) * (THREADS / 32 + 1);
+    auto kern = onesweep_pass_v4_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB, LB>;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    kern<<<(unsigned)div_up(n, (size_t)TILE), THREADS, smem, stream>>>(in_keys, out_keys, in_vals, out_vals, n,
+                                                                      dp, offs, status, ctr, epoch);
+}
+
 template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
 void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
                uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
@@ -591,7 +764,7 @@ template <typename KeyT>
 static int variant_tile(int v) {
     constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;   // u128 tiles hold half the keys
     switch (v) {
-        case 5: case 22: return 8192 / S;
+        case 5: case 22: case 31: case 33: return 8192 / S;
         case 6: return 2048 / S;
         default: return 4096 / S;
     }
@@ -650,10 +823,16 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
                                                       ctr, ep);                                      \
     } while (0)
 #define V3(T, I, B, LBW) launch_v3<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
+#define V4(T, I, B, LBW) launch_v4<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
 #define V2(T, I, B, LBW) launch_v2<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
         switch (variant) {
             case 1: V1(4, 1); break;
             case 20: V3(256, 16, 3, 0); break;
+            case 30: V4(256, 16, 3, 0); break;
+            case 31: V4(512, 16, 2, 0); break;
+            case 32: V4(256, 16, 3, 4); break;
+            case 33: V4(512, 16, 2, 4); break;
+            case 34: V4(256, 16, 4, 0); break;
             case 21: V3(256, 16, 4, 0); break;
             case 22: V3(512, 16, 2, 0); break;
             case 25: V3(256, 16, 3, 4); break;
@@ -679,6 +858,7 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
 #undef V1
 #undef V2
 #undef V3
+#undef V4
         if (ws.events) cudaEventRecord(ws.events[2 * p + 1], stream);
         *launches += 1;
         cur ^= 1;

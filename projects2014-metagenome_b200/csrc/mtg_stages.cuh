@@ -81,9 +81,11 @@ size_t bucket_index_words(Alpha al);
 template <typename KeyT>
 void build_bucket_index(const KeyT *reals, uint64_t m, Alpha al, uint64_t *idx, cudaStream_t stream,
                         unsigned *launches);
+// scratch: dummy_scratch_bytes(m, al) bytes of device memory (window bounds + incoming-edge bitmap)
+size_t dummy_scratch_bytes(uint64_t m, Alpha al);
 template <typename KeyT>
 void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64_t *bucket_idx,
-                           KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink,
+                           void *scratch, KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink,
                            KeyT *src_fwd, uint64_t src_cap, unsigned long long *d_num_src,
                            cudaStream_t stream, unsigned *launches);
 

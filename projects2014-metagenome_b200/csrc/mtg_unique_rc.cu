@@ -2,6 +2,8 @@
 // Replaces std::unique / the saturating count merge of SortedSet / SortedMultiset
 // (common/sorted_sets/sorted_set.cpp:41-48, sorted_multiset.cpp:54-84) and
 // add_reverse_complements (boss_chunk_construct.cpp:179-222).
+#include <cstdlib>
+
 #include "mtg_scan.cuh"
 #include "mtg_stages.cuh"
 
@@ -85,6 +87,86 @@ unique_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_
     }
     // the tile holding the last element publishes the total and the end marker
     if (threadIdx.x == 0 && (uint64_t)(tile + 1) * UQ_TILE >= n) {
+        uint64_t m = tile_excl + tile_total;
+        *d_num_out = m;
+        if (out_starts) out_starts[m] = n;
+    }
+}
+
+// Same contract as unique_kernel, tile staged in shared memory by one TMA bulk copy (keys are
+// never held in registers while in flight): 64 KB tiles, 3 resident blocks per SM = 192 KB of
+// loads outstanding per SM, which hides the look-back latency that bound unique_kernel (61 % of
+// its stall samples at the barrier after the look-back, profiles/r01_ncu_full_v2_101ms.txt).
+// The 16-byte left halo holds keys[tile_base - 1], so a head is simply sk[i] != sk[i - 1].
+constexpr int UB_THREADS = 256;
+constexpr int UB_TILE_BYTES = 64 * 1024;
+
+template <typename KeyT>
+__global__ void __launch_bounds__(UB_THREADS)
+unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_keys,
+                   uint64_t *__restrict__ out_starts, unsigned long long *d_num_out,
+                   unsigned long long *status, unsigned int *tile_counter) {
+    constexpr int TILE = UB_TILE_BYTES / sizeof(KeyT);
+    constexpr int HALO = 16 / sizeof(KeyT);
+    constexpr int WARPS = UB_THREADS / 32;
+    constexpr int ROWS = TILE / UB_THREADS;          // rows of 32 keys per warp
+    extern __shared__ __align__(128) unsigned char ub_smem[];
+    KeyT *sk = reinterpret_cast<KeyT *>(ub_smem) + HALO;   // sk[-1] = key before the tile
+    __shared__ __align__(8) unsigned long long bar;
+    __shared__ unsigned int sh_tile;
+    __shared__ uint32_t warp_cnt[WARPS + 1];
+    __shared__ uint64_t slot;
+    if (threadIdx.x == 0) {
+        sh_tile = atomicAdd(tile_counter, 1u);
+        mbar_init(&bar, 1);
+    }
+    __syncthreads();
+    const uint32_t tile = sh_tile;
+    const uint64_t tile_base = (uint64_t)tile * TILE;
+    const uint32_t valid = (uint32_t)(n - tile_base < (uint64_t)TILE ? n - tile_base : TILE);
+    if (threadIdx.x == 0) {
+        const uint32_t halo = tile ? 16u : 0u;
+        const uint32_t bytes = ((valid * (uint32_t)sizeof(KeyT) + 15u) & ~15u) + halo;
+        bulk_load_g2s(reinterpret_cast<unsigned char *>(sk) - halo,
+                      reinterpret_cast<const unsigned char *>(keys + tile_base) - halo, bytes, &bar);
+    }
+    mbar_wait(&bar, 0);
+
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t wbase = warp * (32 * ROWS);
+    uint32_t wcount = 0;
+#pragma unroll 8
+    for (int r = 0; r < ROWS; ++r) {
+        const uint32_t idx = wbase + r * 32 + lane;
+        bool head = idx < valid && ((tile_base + idx) == 0 || !w_eq(sk[idx], sk[(int)idx - 1]));
+        wcount += __popc(__ballot_sync(0xffffffffu, head));
+    }
+    if (lane == 0) warp_cnt[warp] = wcount;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t run = 0;
+        for (int w = 0; w < WARPS; ++w) { uint32_t t = warp_cnt[w]; warp_cnt[w] = run; run += t; }
+        warp_cnt[WARPS] = run;
+    }
+    __syncthreads();
+    const uint32_t tile_total = warp_cnt[WARPS];
+    const uint64_t tile_excl = lookback_exclusive(status, tile, tile_total, &slot);
+    uint64_t pos = tile_excl + warp_cnt[warp];
+    const unsigned lt = lanemask_lt();
+#pragma unroll 8
+    for (int r = 0; r < ROWS; ++r) {
+        const uint32_t idx = wbase + r * 32 + lane;
+        KeyT k = sk[idx];
+        bool head = idx < valid && ((tile_base + idx) == 0 || !w_eq(k, sk[(int)idx - 1]));
+        const unsigned bal = __ballot_sync(0xffffffffu, head);
+        if (head) {
+            uint64_t dst = pos + __popc(bal & lt);
+            out_keys[dst] = k;
+            if (out_starts) out_starts[dst] = tile_base + idx;
+        }
+        pos += __popc(bal);
+    }
+    if (threadIdx.x == 0 && tile_base + TILE >= n) {
         uint64_t m = tile_excl + tile_total;
         *d_num_out = m;
         if (out_starts) out_starts[m] = n;
@@ -223,7 +305,7 @@ append_rc_kernel(const KeyT *__restrict__ keys, KeyT *__restrict__ rc_out, uint3
 
 }  // namespace
 
-size_t unique_status_words(uint64_t n) { return div_up(n, (size_t)UQ_TILE) + 1; }
+size_t unique_status_words(uint64_t n) { return div_up(n, (size_t)UQ_TILE) + 1; }   // >= bulk tiles
 
 template <typename KeyT>
 void unique_keys(const KeyT *keys, uint64_t n, KeyT *out_keys, uint64_t *out_starts,
@@ -234,6 +316,22 @@ void unique_keys(const KeyT *keys, uint64_t n, KeyT *out_keys, uint64_t *out_sta
     MTG_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream));
     MTG_CUDA(cudaMemsetAsync(d_num_out, 0, sizeof(unsigned long long), stream));
     if (n == 0) return;
+    if (((uintptr_t)keys & 15) == 0 && !getenv("MTG_UNIQUE_NO_BULK")) {
+        // TMA-staged tiles (the input buffer is an arena block: readable up to the next 16 bytes)
+        constexpr size_t TILE = UB_TILE_BYTES / sizeof(KeyT);
+        const size_t smem = UB_TILE_BYTES + 16;
+        auto kern = unique_bulk_kernel<KeyT>;
+        static bool attr_set = false;
+        if (!attr_set) {
+            MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set = true;
+        }
+        kern<<<(unsigned)div_up(n, TILE), UB_THREADS, smem, stream>>>(keys, n, out_keys, out_starts, d_num_out,
+                                                                    scan_status, tile_counter);
+        MTG_CUDA(cudaGetLastError());
+        *launches += 1;
+        return;
+    }
     unique_kernel<KeyT><<<(unsigned)tiles, UQ_THREADS, 0, stream>>>(keys, n, out_keys, out_starts,
                                                                    d_num_out, scan_status, tile_counter);
     MTG_CUDA(cudaGetLastError());

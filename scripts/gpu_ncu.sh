@@ -5,7 +5,7 @@
 set -u
 TAG=${1:-cur}
 mkdir -p gpurun_out
-OURS='extract|sort_|onesweep|unique|run_counts|append_rc|merge|dummy|source_prefix|scan_u32|fill_u32|flip_info|bucket_index|emit|target_nodes|ranged|filter_key'
+OURS='extract|sort_|onesweep|unique|run_counts|append_rc|merge|dummy|dc_|source_prefix|scan_u32|fill_u32|flip_info|bucket_index|emit|target_nodes|ranged|filter_key'
 CMD="python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain_$TAG.json 2> gpurun_out/plain_$TAG.err || { echo "plain run failed"; tail -5 gpurun_out/plain_$TAG.err; exit 1; }
 cat gpurun_out/plain_$TAG.json
