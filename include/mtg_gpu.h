@@ -48,7 +48,10 @@ typedef struct mtg_params {
     uint32_t alphabet;        /* MTG_ALPHABET_* (a compile-time macro in the reference) */
     uint32_t both_strands;    /* canonical mode: CANONICAL_ONLY collection + rc completion */
     uint32_t bits_per_count;  /* 0 = no weights, else 1..32 (--count-width) */
-    const char *filter_suffix;/* NULL or "" ; non-empty suffix (--suffix) => MTG_ERR_UNSUPPORTED for now */
+    const char *filter_suffix;/* NULL or "": default build. Else `--suffix S` over "$ACGT" / "$ABC..": only the
+                               * framed k-mers whose characters before the last equal S are kept and the
+                               * chunk is built straight from them (KmerExtractorBOSS,
+                               * kmer/kmer_extractor.cpp:317-381; boss_chunk_construct.cpp:961-1013) */
     int32_t device;           /* CUDA device ordinal */
     uint32_t reserved;
     double memory_preallocated; /* bytes; hint for the initial read-staging capacity */

@@ -203,6 +203,7 @@ struct mtg_ctx {
     std::shared_ptr<Arena> arena = std::make_shared<Arena>();
     bool any_explicit_counts = false;
     uint32_t cmax = 0;   // container count type max (boss_chunk_construct.cpp:1147-1160)
+    std::vector<uint8_t> suffix;   // --suffix filter in BOSS codes (0 = '$'); empty = default build
     std::string error;
     unsigned launches = 0;
     // range-partitioned (multi-GPU) build state, see mtg_mg_* below
@@ -317,13 +318,14 @@ int mtg_create(const mtg_params *p, mtg_ctx **out) {
                                                + std::to_string(256 / L2));
     if (p->bits_per_count > 32)   // :1157-1159
         return fail(nullptr, MTG_ERR_BAD_ARG, "Error: trying to allocate too many bits per k-mer count");
-    if (p->filter_suffix && p->filter_suffix[0])
-        return fail(nullptr, MTG_ERR_UNSUPPORTED, "suffix-filtered chunks (--suffix) are not on the GPU path yet");
+    const size_t suffix_len = p->filter_suffix ? strlen(p->filter_suffix) : 0;
     if (p->both_strands && p->alphabet != MTG_ALPHABET_DNA)
         return fail(nullptr, MTG_ERR_BAD_ARG, "canonical mode requires a DNA alphabet");
     const uint32_t K = p->k + 1;
-    if (K * L1 > 128)
+    if (K * L1 + (suffix_len ? 8 : 0) > 128)
         return fail(nullptr, MTG_ERR_UNSUPPORTED, "k-mers wider than 128 bits are not supported yet");
+    if (suffix_len >= K || suffix_len > MTG_SUFFIX_MAX)   // kmer_extractor.cpp:326
+        return fail(nullptr, MTG_ERR_BAD_ARG, "the suffix must be shorter than k + 1 (it does not include the last character)");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         cudaGetLastError();
@@ -343,6 +345,15 @@ int mtg_create(const mtg_params *p, mtg_ctx **out) {
         ctx->cmax = p->bits_per_count == 0 ? 0xffffffffu
                     : p->bits_per_count <= 8 ? 0xffu : p->bits_per_count <= 16 ? 0xffffu : 0xffffffffu;
         build_lut(p->alphabet, &ctx->lut);
+        for (size_t i = 0; i < suffix_len; ++i) {   // encode_filter_suffix_boss (boss_chunk_construct.cpp:934-945)
+            const unsigned char ch = (unsigned char)p->filter_suffix[i];
+            uint8_t code = ch == '$' ? 0xfe : ctx->lut.code[ch];
+            if (code == 0xff) {
+                delete ctx;
+                return fail(nullptr, MTG_ERR_BAD_ARG, "the suffix holds a character outside the alphabet");
+            }
+            ctx->suffix.push_back(code == 0xfe ? 0 : code + 1);
+        }
         MTG_CUDA(cudaSetDevice(ctx->device));
         cudaDeviceProp prop;
         MTG_CUDA(cudaGetDeviceProperties(&prop, ctx->device));
@@ -755,6 +766,88 @@ void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64
     *d_out = d;
 }
 
+// rows -> W / last / F / weights (K6) -> mtg_chunk (pinned host copy or device-resident)
+template <typename KeyT>
+void emit_deliver(mtg_ctx *ctx, DevBuf &row_keys, DevBuf &row_info, DevBuf *row_counts, uint64_t E,
+                  const unsigned long long *d_levels, Timer &tm, SortProfile &prof, mtg_chunk *out,
+                  bool device_output, uint64_t n_input, uint64_t n_real, uint64_t n_sink) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint32_t K = al.K;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    const uint32_t ww = ctx->prm.bits_per_count;
+    const size_t tiles = div_up(E, (size_t)2048);
+    const size_t W_words = tiles * 32 * al.W_width, last_words = tiles * 32, wt_words = tiles * 32 * ww;
+    DevBuf outbuf(8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA), s);
+    uint64_t *dW = outbuf.as<uint64_t>(), *dLast = dW + W_words, *dWt = dLast + last_words;
+    unsigned long long *dF = (unsigned long long *)(dWt + wt_words);
+    emit_chunk<KeyT>(row_keys.as<KeyT>(), row_info.as<uint8_t>(),
+                     row_counts ? row_counts->as<uint32_t>() : nullptr, E, al, ww, dW, dLast,
+                     counting ? dWt : nullptr, dF, s, &ctx->launches);
+    tm.mark();   // 6: emit done
+
+    // ---- results to pinned host memory ----
+    ChunkImpl *impl = new ChunkImpl();
+    const size_t arr_words = device_output ? 0 : W_words + last_words + wt_words;
+    size_t hbytes = 8 * (arr_words + MTG_MAX_SIGMA + MTG_MAX_K + 16);
+    impl->pinned = g_pinned_cache.acquire(hbytes, &impl->pinned_bytes);
+    if (!impl->pinned) {
+        delete impl;
+        throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
+    }
+    uint64_t *h = (uint64_t *)impl->pinned;
+    MTG_CUDA(cudaMemcpyAsync(h, dW + (device_output ? W_words + last_words + wt_words : 0),
+                             8 * (arr_words + MTG_MAX_SIGMA), cudaMemcpyDeviceToHost, s));
+    uint64_t *h_levels = h + arr_words + MTG_MAX_SIGMA;
+    MTG_CUDA(cudaMemcpyAsync(h_levels, d_levels, 8 * MTG_MAX_K, cudaMemcpyDeviceToHost, s));
+    MTG_CUDA(cudaStreamSynchronize(s));
+
+    memset(out, 0, sizeof(*out));
+    out->n_rows = E;
+    out->sigma = al.sigma;
+    out->k = K - 1;
+    out->W_width = al.W_width;
+    out->weights_width = ww;
+    if (device_output) {
+        out->W = dW;
+        out->last = dLast;
+        out->weights = counting ? dWt : nullptr;
+        out->device_resident = 1;
+        impl->dev = std::move(outbuf);
+    } else {
+        out->W = h;
+        out->last = h + W_words;
+        out->weights = counting ? h + W_words + last_words : nullptr;
+    }
+    const uint64_t *hF = h + arr_words;
+    if (prof.n) {
+        float t = 0;
+        for (int p = 0; p < prof.npasses; ++p) {
+            cudaEventElapsedTime(&t, prof.ev[2 * p], prof.ev[2 * p + 1]);
+            out->ms_onesweep_sum += t;
+        }
+        cudaEventElapsedTime(&t, prof.ev[2 * MAX_SORT_PASSES], prof.ev[2 * MAX_SORT_PASSES + 1]);
+        out->ms_sort_histogram = t;
+        out->n_onesweep = prof.npasses;
+        out->onesweep_bytes_per_key = prof.bytes_per_key;
+        out->onesweep_keys = prof.n;
+    }
+    for (uint32_t c = 0; c < al.sigma; ++c) out->F[c] = hF[c];
+    out->n_input_kmers = n_input;
+    out->n_real = n_real;
+    out->n_dummy_sink = n_sink;
+    for (uint32_t c = 0; c + 1 < K && c < MTG_MAX_K; ++c) out->n_dummy_source[c] = h_levels[c];
+    out->ms_extract = tm.ms(0, 1);
+    out->ms_sort = tm.ms(1, 2);
+    out->ms_unique = tm.ms(2, 3);
+    out->ms_rc = tm.ms(3, 4);
+    out->ms_dummy = tm.ms(4, 5);
+    out->ms_emit = tm.ms(5, 6);
+    out->ms_total = tm.ms(0, 6);
+    out->n_kernel_launches = ctx->launches;
+    out->impl = impl;
+}
+
 // dummy k-mers (sinks + sources, any order) + sorted reals -> rows -> W / last / F / weights.
 // row_off = 2: rows 0 (placeholder) and 1 (the all-'$' k-mer) precede the merge; 1: placeholder
 // only (a key range other than the first one, multi-GPU).
@@ -794,77 +887,8 @@ void finish_chunk(mtg_ctx *ctx, RealSet &rs, DevBuf &dk0, DevBuf &di0, uint64_t 
                      row_info.as<uint8_t>(), counting ? row_counts.as<uint32_t>() : nullptr, s,
                      &ctx->launches, row_off);
     rs.keys.release(); rs.counts.release(); dk0.release(); di0.release(); rank.release();
-    const uint32_t ww = ctx->prm.bits_per_count;
-    const size_t tiles = div_up(E, (size_t)2048);
-    const size_t W_words = tiles * 32 * al.W_width, last_words = tiles * 32, wt_words = tiles * 32 * ww;
-    DevBuf outbuf(8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA), s);
-    uint64_t *dW = outbuf.as<uint64_t>(), *dLast = dW + W_words, *dWt = dLast + last_words;
-    unsigned long long *dF = (unsigned long long *)(dWt + wt_words);
-    emit_chunk<KeyT>(row_keys.as<KeyT>(), row_info.as<uint8_t>(),
-                     counting ? row_counts.as<uint32_t>() : nullptr, E, al, ww, dW, dLast,
-                     counting ? dWt : nullptr, dF, s, &ctx->launches);
-    tm.mark();   // 6: emit done
-
-    // ---- results to pinned host memory ----
-    ChunkImpl *impl = new ChunkImpl();
-    const size_t arr_words = device_output ? 0 : W_words + last_words + wt_words;
-    size_t hbytes = 8 * (arr_words + MTG_MAX_SIGMA + MTG_MAX_K + 16);
-    impl->pinned = g_pinned_cache.acquire(hbytes, &impl->pinned_bytes);
-    if (!impl->pinned) {
-        delete impl;
-        throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
-    }
-    uint64_t *h = (uint64_t *)impl->pinned;
-    MTG_CUDA(cudaMemcpyAsync(h, dW + (device_output ? W_words + last_words + wt_words : 0),
-                             8 * (arr_words + MTG_MAX_SIGMA), cudaMemcpyDeviceToHost, s));
-    uint64_t *h_levels = h + arr_words + MTG_MAX_SIGMA;
-    MTG_CUDA(cudaMemcpyAsync(h_levels, d_ctr + 8, 8 * MTG_MAX_K, cudaMemcpyDeviceToHost, s));
-    MTG_CUDA(cudaStreamSynchronize(s));
-
-    memset(out, 0, sizeof(*out));
-    out->n_rows = E;
-    out->sigma = al.sigma;
-    out->k = K - 1;
-    out->W_width = al.W_width;
-    out->weights_width = ww;
-    if (device_output) {
-        out->W = dW;
-        out->last = dLast;
-        out->weights = counting ? dWt : nullptr;
-        out->device_resident = 1;
-        impl->dev = std::move(outbuf);
-    } else {
-        out->W = h;
-        out->last = h + W_words;
-        out->weights = counting ? h + W_words + last_words : nullptr;
-    }
-    const uint64_t *hF = h + arr_words;
-    if (prof.n) {
-        float t = 0;
-        for (int p = 0; p < prof.npasses; ++p) {
-            cudaEventElapsedTime(&t, prof.ev[2 * p], prof.ev[2 * p + 1]);
-            out->ms_onesweep_sum += t;
-        }
-        cudaEventElapsedTime(&t, prof.ev[2 * MAX_SORT_PASSES], prof.ev[2 * MAX_SORT_PASSES + 1]);
-        out->ms_sort_histogram = t;
-        out->n_onesweep = prof.npasses;
-        out->onesweep_bytes_per_key = prof.bytes_per_key;
-        out->onesweep_keys = prof.n;
-    }
-    for (uint32_t c = 0; c < al.sigma; ++c) out->F[c] = hF[c];
-    out->n_input_kmers = rs.n_input;
-    out->n_real = m;
-    out->n_dummy_sink = n_sink;
-    for (uint32_t c = 0; c + 1 < K && c < MTG_MAX_K; ++c) out->n_dummy_source[c] = h_levels[c];
-    out->ms_extract = tm.ms(0, 1);
-    out->ms_sort = tm.ms(1, 2);
-    out->ms_unique = tm.ms(2, 3);
-    out->ms_rc = tm.ms(3, 4);
-    out->ms_dummy = tm.ms(4, 5);
-    out->ms_emit = tm.ms(5, 6);
-    out->ms_total = tm.ms(0, 6);
-    out->n_kernel_launches = ctx->launches;
-    out->impl = impl;
+    emit_deliver<KeyT>(ctx, row_keys, row_info, counting ? &row_counts : nullptr, E, d_ctr + 8, tm, prof, out,
+                       device_output, rs.n_input, m, n_sink);
 }
 
 template <typename KeyT>
@@ -911,6 +935,131 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     finish_chunk<KeyT>(ctx, rs, dk0, di0, d, n_sink, d_ctr, d_bidx, tm, prof, out, device_output, 2);
 }
 
+// `build --suffix S`: framed k-mers matching the filter -> sort -> unique / counts -> rows ->
+// chunk (BOSSChunkConstructor's KmerExtractorBOSS branch, boss_chunk_construct.cpp:1002-1013).
+template <typename KeyT>
+void build_suffix_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    const bool payload = counting && ctx->any_explicit_counts;
+    const bool both = ctx->prm.both_strands != 0;   // Mode::BOTH (:961-971)
+    ctx->launches = 0;
+    Timer tm(s);
+    SortProfile prof;
+    bool all_dollar = true;
+    for (uint8_t c : ctx->suffix) all_dollar &= c == 0;
+
+    DevBuf ctr(64 + 8 * MTG_MAX_K, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64 + 8 * MTG_MAX_K, s));
+    uint64_t nbytes = 0;
+    for (auto &seg : ctx->segs) nbytes += seg.nbytes;
+    uint64_t cap = std::max<uint64_t>(1024, nbytes / 2);
+    DevBuf keysA, keysB, valsA, valsB;
+    std::vector<DevBuf> ones;
+    uint64_t n = 0;
+    tm.mark();
+    while (true) {
+        keysA.alloc(sizeof(KeyT) * (cap + 1), s);
+        if (payload) valsA.alloc(4 * (cap + 1), s);
+        MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 8, s));
+        for (auto &seg : ctx->segs) {
+            ExtractArgs a;
+            a.packed = seg.d_packed;
+            a.nbytes = seg.nbytes;
+            a.lut = &ctx->lut;
+            a.K = al.K;
+            a.L = al.L;
+            a.canonical = false;
+            a.both = both;
+            a.out_counts = payload ? valsA.as<uint32_t>() : nullptr;
+            a.out_counter = d_ctr;
+            a.read_starts = nullptr;
+            a.read_counts = nullptr;
+            a.n_reads = 0;
+            if (payload) {
+                if (!seg.has_starts)
+                    throw CudaError{cudaErrorInvalidValue, "device-packed reads cannot be mixed with explicit counts", 0};
+                a.read_starts = seg.starts.as<uint64_t>();
+                a.n_reads = seg.n_reads;
+                if (seg.has_counts) {
+                    a.read_counts = seg.counts.as<uint32_t>();
+                } else {
+                    ones.emplace_back(4 * seg.n_reads, s);
+                    fill_u32(ones.back().as<uint32_t>(), 1, seg.n_reads, s, &ctx->launches);
+                    a.read_counts = ones.back().as<uint32_t>();
+                }
+            }
+            extract_suffix_kmers<KeyT>(a, al, ctx->suffix.data(), (uint32_t)ctx->suffix.size(), keysA.as<KeyT>(),
+                                       cap, s);
+            ctx->launches += 1;
+        }
+        n = read_counter(d_ctr, s);
+        ones.clear();
+        if (n <= cap) break;
+        cap = n;
+    }
+    const uint64_t n_input = n;
+    if (all_dollar) {   // kmer_collector_.add_kmer(all '$'), count 1 (:978-981)
+        const uint32_t sortinfo = (127u - (al.K - 1)) << 1;
+        KeyT dollar = w_shl(WordTraits<KeyT>::from_u64(sortinfo), al.L);
+        MTG_CUDA(cudaMemcpyAsync(keysA.as<KeyT>() + n, &dollar, sizeof(KeyT), cudaMemcpyHostToDevice, s));
+        if (payload) {
+            const uint32_t one = 1;
+            MTG_CUDA(cudaMemcpyAsync(valsA.as<uint32_t>() + n, &one, 4, cudaMemcpyHostToDevice, s));
+        }
+        MTG_CUDA(cudaStreamSynchronize(s));
+        ++n;
+    }
+    tm.mark();   // 1: extraction done
+
+    keysB.alloc(sizeof(KeyT) * std::max<uint64_t>(n, 1), s);
+    if (payload) valsB.alloc(4 * std::max<uint64_t>(n, 1), s);
+    SortPlan plan;
+    plan.n = 0;
+    plan_add_key_bits(plan, 0, al.K * al.L + 8);
+    sort_keys<KeyT>(keysA, keysB, payload ? &valsA : nullptr, payload ? &valsB : nullptr, n, plan, s,
+                    &ctx->launches);
+    tm.mark();   // 2: sorted
+
+    DevBuf counts, starts;
+    if (counting) starts.alloc(8 * (n + 1), s);
+    {
+        DevBuf status(sizeof(unsigned long long) * unique_status_words(n), s), tctr(sizeof(unsigned int), s);
+        unique_keys<KeyT>(keysA.as<KeyT>(), n, keysB.as<KeyT>(), counting ? starts.as<uint64_t>() : nullptr,
+                          d_ctr + 1, status.as<unsigned long long>(), tctr.as<unsigned int>(), s, &ctx->launches);
+    }
+    const uint64_t m = read_counter(d_ctr + 1, s);
+    if (counting) {
+        counts.alloc(4 * std::max<uint64_t>(m, 1), s);
+        run_counts(starts.as<uint64_t>(), payload ? valsA.as<uint32_t>() : nullptr, m, ctx->cmax,
+                   counts.as<uint32_t>(), s, &ctx->launches);
+    }
+    keysA.release(); valsA.release(); valsB.release(); starts.release();
+    tm.mark();   // 3: distinct k-mers (+ counts)
+    tm.mark();   // 4: (no reverse-complement completion in suffix mode)
+
+    DevBuf keep(4 * std::max<uint64_t>(m, 1), s), offs(8 * (m + 1), s);
+    suffix_keep_flags<KeyT>(keysB.as<KeyT>(), m, al, keep.as<uint32_t>(), s, &ctx->launches);
+    {
+        DevBuf status(8 * (m / 2048 + 2), s), tctr(4, s);
+        exclusive_scan_u32(keep.as<uint32_t>(), m, offs.as<uint64_t>(), status.as<unsigned long long>(),
+                           tctr.as<unsigned int>(), s, &ctx->launches);
+    }
+    const uint64_t kept = read_counter(offs.as<unsigned long long>() + m, s);
+    const uint64_t E = kept + 1;
+    DevBuf row_keys(sizeof(KeyT) * E, s), row_info(E, s), row_counts;
+    if (counting) row_counts.alloc(4 * E, s);
+    suffix_rows<KeyT>(keysB.as<KeyT>(), counting ? counts.as<uint32_t>() : nullptr, keep.as<uint32_t>(),
+                      offs.as<uint64_t>(), m, al, row_keys.as<KeyT>(), row_info.as<uint8_t>(),
+                      counting ? row_counts.as<uint32_t>() : nullptr, s, &ctx->launches);
+    keysB.release(); counts.release(); keep.release(); offs.release();
+    tm.mark();   // 5: rows
+    emit_deliver<KeyT>(ctx, row_keys, row_info, counting ? &row_counts : nullptr, E, d_ctr + 8, tm, prof, out,
+                       device_output, n_input, m, 0);
+}
+
 void clear_ctx(mtg_ctx *ctx) {
     ctx->segs.clear();
     ctx->any_explicit_counts = false;
@@ -927,7 +1076,10 @@ static int build_chunk_common(mtg_ctx *ctx, mtg_chunk *out, bool device_output) 
     try {
         MTG_CUDA(cudaSetDevice(ctx->device));
         t_arena = ctx->arena;
-        if (ctx->al.K * ctx->al.L <= 64) build_impl<uint64_t>(ctx, out, device_output);
+        if (!ctx->suffix.empty()) {
+            if (ctx->al.K * ctx->al.L + 8 <= 64) build_suffix_impl<uint64_t>(ctx, out, device_output);
+            else build_suffix_impl<u128>(ctx, out, device_output);
+        } else if (ctx->al.K * ctx->al.L <= 64) build_impl<uint64_t>(ctx, out, device_output);
         else build_impl<u128>(ctx, out, device_output);
     } catch (const CudaError &e) {
         rc = fail_cuda(ctx, e);
@@ -1320,6 +1472,8 @@ int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_
     MG_GUARD(ctx, {
         if (ctx->any_explicit_counts)
             return fail(ctx, MTG_ERR_UNSUPPORTED, "per-read counts are not supported by the range-partitioned build");
+        if (!ctx->suffix.empty())
+            return fail(ctx, MTG_ERR_UNSUPPORTED, "a suffix-filtered chunk is built on one GPU (mtg_build_chunk)");
         if (wide) mg_extract_impl<u128>(ctx, mg_part_bits(ctx), bucket_counts, d_keys, n);
         else mg_extract_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_counts, d_keys, n);
     })

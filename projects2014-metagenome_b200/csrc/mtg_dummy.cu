@@ -108,7 +108,8 @@ template <typename KeyT>
 __global__ void __launch_bounds__(DC_THREADS)
 dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t nch, BucketIndex bi,
                 const uint64_t *__restrict__ part, uint32_t *__restrict__ incoming,
-                KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink) {
+                uint32_t *__restrict__ heads, KeyT *sink_keys, uint64_t sink_cap,
+                unsigned long long *d_num_sink) {
     using WT = WordTraits<KeyT>;
     extern __shared__ __align__(16) unsigned char dc_smem[];
     KeyT *win = reinterpret_cast<KeyT *>(dc_smem);       // [DC_POOL]
@@ -147,15 +148,17 @@ dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t n
 #pragma unroll 2
     for (int r = 0; r < DC_IPT; ++r) {
         const uint64_t i = i0 + (uint64_t)r * DC_THREADS + threadIdx.x;
-        bool emit_sink = false;
+        bool emit_sink = false, node_head = false;
         KeyT sink = WT::zero();
         if (i < m) {
             KeyT x = reals[i];
             KeyT W = w_and(x, maskL);
             KeyT grp = w_shr(x, 2 * L);
             bool first = true;   // first element of its (x >> 2L, W) class = distinct target node
+            node_head = true;    // first k-mer of its node
             for (uint64_t q = i; q-- > 0;) {
                 KeyT y = reals[q];
+                if (q + 1 == i) node_head = !w_eq(w_shr(y, L), w_shr(x, L));
                 if (!w_eq(w_shr(y, 2 * L), grp)) break;
                 if (w_eq(w_and(y, maskL), W)) { first = false; break; }
             }
@@ -185,6 +188,9 @@ dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t n
                     emit_sink = true;
             }
         }
+        // i is a multiple of 32 at lane 0: one bitmap word per warp row
+        const unsigned hb = __ballot_sync(0xffffffffu, node_head);
+        if ((threadIdx.x & 31) == 0 && i < m) heads[i >> 5] = hb;
         warp_append(emit_sink, sink, sink_keys, sink_cap, d_num_sink);
     }
 }
@@ -193,27 +199,25 @@ dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t n
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
 dc_sources_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al,
-                  const uint32_t *__restrict__ incoming, KeyT *src_fwd, uint64_t src_cap,
-                  unsigned long long *d_num_src) {
+                  const uint32_t *__restrict__ incoming, const uint32_t *__restrict__ heads,
+                  KeyT *src_fwd, uint64_t src_cap, unsigned long long *d_num_src) {
+    // one bitmap word (32 reals) per thread; only the rare candidates touch the k-mers
     using WT = WordTraits<KeyT>;
     const uint32_t L = al.L, K = al.K;
     const KeyT maskL = WT::low_mask(L);
-    const uint64_t base = ((uint64_t)blockIdx.x * blockDim.x + (threadIdx.x & ~31u)) * 4;
-    const unsigned lane = threadIdx.x & 31;
-#pragma unroll
-    for (int r = 0; r < 4; ++r) {
-        const uint64_t i = base + r * 32 + lane;   // the warp covers one bitmap word per round
-        bool emit_src = false;
+    const uint64_t wi = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t nwords = (m + 31) / 32;
+    uint32_t cand = wi < nwords ? heads[wi] & ~incoming[wi] : 0u;
+    while (__any_sync(0xffffffffu, cand != 0)) {
+        bool emit_src = cand != 0;
         KeyT fwd = WT::zero();
-        if (i < m) {
-            KeyT x = reals[i];
-            bool node_head = i == 0 || !w_eq(w_shr(reals[i - 1], L), w_shr(x, L));
-            if (node_head && !((incoming[i >> 5] >> (i & 31)) & 1u)) {
-                emit_src = true;
-                for (uint32_t c = 1; c < K; ++c) {
-                    KeyT ch = w_and(w_shr(x, L * c), maskL);
-                    fwd = w_or(fwd, w_shl(ch, L * (K - 1 - c)));
-                }
+        if (emit_src) {
+            const uint32_t b = __ffs(cand) - 1;
+            cand &= cand - 1;
+            KeyT x = reals[wi * 32 + b];
+            for (uint32_t c = 1; c < K; ++c) {
+                KeyT ch = w_and(w_shr(x, L * c), maskL);
+                fwd = w_or(fwd, w_shl(ch, L * (K - 1 - c)));
             }
         }
         warp_append(emit_src, fwd, src_fwd, src_cap, d_num_src);
@@ -497,7 +501,7 @@ void build_bucket_index(const KeyT *reals, uint64_t m, Alpha al, uint64_t *idx, 
 size_t dummy_scratch_bytes(uint64_t m, Alpha al) {
     const uint64_t tiles = div_up(m, (size_t)DC_TILE);
     const uint32_t nch = al.sigma - 1;
-    return 8 * (tiles + 1) * nch + 4 * (m / 32 + 2);
+    return 8 * (tiles + 1) * nch + 2 * 4 * (m / 32 + 2);
 }
 
 template <typename KeyT>
@@ -512,6 +516,7 @@ void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64
     const uint32_t nch = al.sigma - 1;
     uint64_t *part = reinterpret_cast<uint64_t *>(scratch);
     uint32_t *incoming = reinterpret_cast<uint32_t *>(part + (tiles + 1) * nch);
+    uint32_t *heads = incoming + (m / 32 + 2);
     MTG_CUDA(cudaMemsetAsync(incoming, 0, 4 * (m / 32 + 2), stream));
     const BucketIndex bi = make_bi(al, bucket_idx);
     dc_partition_kernel<KeyT><<<(unsigned)div_up((tiles + 1) * nch, (size_t)256), 256, 0, stream>>>(
@@ -523,10 +528,10 @@ void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64
         MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
-    kern<<<(unsigned)tiles, DC_THREADS, smem, stream>>>(reals, m, al, nch, bi, part, incoming, sink_keys,
+    kern<<<(unsigned)tiles, DC_THREADS, smem, stream>>>(reals, m, al, nch, bi, part, incoming, heads, sink_keys,
                                                        sink_cap, d_num_sink);
-    dc_sources_kernel<KeyT><<<(unsigned)div_up(m, (size_t)1024), 256, 0, stream>>>(reals, m, al, incoming,
-                                                                                 src_fwd, src_cap, d_num_src);
+    dc_sources_kernel<KeyT><<<(unsigned)div_up(div_up(m, (size_t)32), (size_t)256), 256, 0, stream>>>(
+        reals, m, al, incoming, heads, src_fwd, src_cap, d_num_src);
     MTG_CUDA(cudaGetLastError());
     *launches += 3;
 }

@@ -33,11 +33,26 @@ sort_histogram_kernel(const KeyT *__restrict__ keys, const uint32_t *__restrict_
     const int np = plan.n;
     for (int i = threadIdx.x; i < np * RADIX; i += blockDim.x) sh_hist[i] = 0;
     __syncthreads();
-    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
-    for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-        KeyT k = keys[i];
-        uint32_t v = HAS_VAL ? vals[i] : 0;
-        for (int p = 0; p < np; ++p) atomicAdd(&sh_hist[p * RADIX + digit_of(k, v, plan.p[p])], 1u);
+    // 4 independent coalesced loads per thread and iteration (64 KB in flight per SM)
+    constexpr int HU = 4;
+    const uint64_t chunk = (uint64_t)blockDim.x * HU;
+    for (uint64_t base = (uint64_t)blockIdx.x * chunk; base < n; base += (uint64_t)gridDim.x * chunk) {
+        KeyT k[HU];
+        uint32_t v[HU];
+#pragma unroll
+        for (int u = 0; u < HU; ++u) {
+            const uint64_t i = base + (uint64_t)u * blockDim.x + threadIdx.x;
+            if (i < n) {
+                k[u] = keys[i];
+                v[u] = HAS_VAL ? vals[i] : 0;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < HU; ++u) {
+            const uint64_t i = base + (uint64_t)u * blockDim.x + threadIdx.x;
+            if (i < n)
+                for (int p = 0; p < np; ++p) atomicAdd(&sh_hist[p * RADIX + digit_of(k[u], v[u], plan.p[p])], 1u);
+        }
     }
     __syncthreads();
     for (int i = threadIdx.x; i < np * RADIX; i += blockDim.x) {

@@ -140,6 +140,25 @@ template <typename KeyT>
 void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, uint64_t *bounds,
                    cudaStream_t stream, unsigned *launches);
 
+// ---- K1s suffix-filtered chunks (--suffix), mtg_suffix.cu ---------------------------------
+// Framed k-mers ('$'^(K-1) seg '$' per valid segment, both strands when a.both) that match the
+// suffix filter, as composite sort keys  node << (L+8) | ((127-nd) << 1 | W!='$') << L | W.
+// suffix_codes: BOSS codes (0 = '$', tight + 1 otherwise). Appends through a.out_counter; entries
+// beyond `cap` are dropped (the driver retries with the exact size).
+constexpr uint32_t MTG_SUFFIX_MAX = 32;
+template <typename KeyT>
+void extract_suffix_kmers(const ExtractArgs &a, Alpha al, const uint8_t *suffix_codes, uint32_t suffix_len,
+                          KeyT *out_keys, uint64_t cap, cudaStream_t stream);
+// keep[i] = 0 for the redundant dummy sinks initialize_chunk drops (boss_chunk.cpp:80-85)
+template <typename KeyT>
+void suffix_keep_flags(const KeyT *comp, uint64_t m, Alpha al, uint32_t *keep, cudaStream_t stream,
+                       unsigned *launches);
+// composite keys -> rows (row 0 = placeholder, row offsets[i] + 1 for every kept k-mer)
+template <typename KeyT>
+void suffix_rows(const KeyT *comp, const uint32_t *counts, const uint32_t *keep, const uint64_t *offsets,
+                 uint64_t m, Alpha al, KeyT *row_keys, uint8_t *row_info, uint32_t *row_counts,
+                 cudaStream_t stream, unsigned *launches);
+
 // ---- K6 chunk emit -------------------------------------------------------
 // Writes W / last / weights in sdsl int_vector word layout and F[sigma].
 // F must be pre-set by the kernel: F[0]=0, F[c]=E-1 unless a boundary is found.

@@ -99,9 +99,10 @@ unique_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_
 // its stall samples at the barrier after the look-back, profiles/r01_ncu_full_v2_101ms.txt).
 // The 16-byte left halo holds keys[tile_base - 1], so a head is simply sk[i] != sk[i - 1].
 constexpr int UB_THREADS = 256;
-constexpr int UB_TILE_BYTES = 64 * 1024;
 
-template <typename KeyT>
+// Tiles are numbered by blockIdx.x (blocks of a 1-D grid are dispatched in index order, which is
+// what the look-back needs), so the bulk load is issued by the first instruction of the block.
+template <typename KeyT, int UB_TILE_BYTES>
 __global__ void __launch_bounds__(UB_THREADS)
 unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_keys,
                    uint64_t *__restrict__ out_starts, unsigned long long *d_num_out,
@@ -113,23 +114,19 @@ unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__
     extern __shared__ __align__(128) unsigned char ub_smem[];
     KeyT *sk = reinterpret_cast<KeyT *>(ub_smem) + HALO;   // sk[-1] = key before the tile
     __shared__ __align__(8) unsigned long long bar;
-    __shared__ unsigned int sh_tile;
     __shared__ uint32_t warp_cnt[WARPS + 1];
     __shared__ uint64_t slot;
-    if (threadIdx.x == 0) {
-        sh_tile = atomicAdd(tile_counter, 1u);
-        mbar_init(&bar, 1);
-    }
-    __syncthreads();
-    const uint32_t tile = sh_tile;
+    const uint32_t tile = blockIdx.x;
     const uint64_t tile_base = (uint64_t)tile * TILE;
     const uint32_t valid = (uint32_t)(n - tile_base < (uint64_t)TILE ? n - tile_base : TILE);
     if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
         const uint32_t halo = tile ? 16u : 0u;
         const uint32_t bytes = ((valid * (uint32_t)sizeof(KeyT) + 15u) & ~15u) + halo;
         bulk_load_g2s(reinterpret_cast<unsigned char *>(sk) - halo,
                       reinterpret_cast<const unsigned char *>(keys + tile_base) - halo, bytes, &bar);
     }
+    __syncthreads();   // the barrier is initialised before anyone waits on it
     mbar_wait(&bar, 0);
 
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -318,16 +315,20 @@ void unique_keys(const KeyT *keys, uint64_t n, KeyT *out_keys, uint64_t *out_sta
     if (n == 0) return;
     if (((uintptr_t)keys & 15) == 0 && !getenv("MTG_UNIQUE_NO_BULK")) {
         // TMA-staged tiles (the input buffer is an arena block: readable up to the next 16 bytes)
-        constexpr size_t TILE = UB_TILE_BYTES / sizeof(KeyT);
-        const size_t smem = UB_TILE_BYTES + 16;
-        auto kern = unique_bulk_kernel<KeyT>;
-        static bool attr_set = false;
-        if (!attr_set) {
-            MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            attr_set = true;
+        static int tile_kb = -1;
+        if (tile_kb < 0) {
+            const char *e = getenv("MTG_UB_TILE_KB");
+            tile_kb = e ? atoi(e) : 32;
         }
-        kern<<<(unsigned)div_up(n, TILE), UB_THREADS, smem, stream>>>(keys, n, out_keys, out_starts, d_num_out,
-                                                                    scan_status, tile_counter);
+        auto launch = [&](auto kern, size_t tile_bytes) {
+            const size_t smem = tile_bytes + 16;
+            MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            kern<<<(unsigned)div_up(n, tile_bytes / sizeof(KeyT)), UB_THREADS, smem, stream>>>(
+                keys, n, out_keys, out_starts, d_num_out, scan_status, tile_counter);
+        };
+        if (tile_kb >= 64) launch(unique_bulk_kernel<KeyT, 64 * 1024>, 64 * 1024);
+        else if (tile_kb >= 32) launch(unique_bulk_kernel<KeyT, 32 * 1024>, 32 * 1024);
+        else launch(unique_bulk_kernel<KeyT, 16 * 1024>, 16 * 1024);
         MTG_CUDA(cudaGetLastError());
         *launches += 1;
         return;

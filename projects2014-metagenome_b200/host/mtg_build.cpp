@@ -65,6 +65,7 @@ int usage() {
     fprintf(stderr,
             "Usage: mtg_build build -k <k> [--mode basic|canonical] [--count-kmers] [--count-width <bits>]\n"
             "                       [-p <threads>] [--mem-cap-gb <G>] [--alphabet DNA|Protein] [--device <id>]\n"
+            "                       [--suffix <S>]\n"
             "                       [-v] -o <outbase> FILE1 [FILE2 ...]\n"
             "       mtg_build concatenate -o <outbase> CHUNK1 [CHUNK2 ...]\n");
     return 1;
@@ -80,7 +81,7 @@ int main(int argc, char **argv) {
     int count_width = 8, device = 0;   // config.hpp:103 default --count-width 8
     double mem_cap_gb = 1;
     Alphabet alphabet = Alphabet::DNA;
-    std::string out;
+    std::string out, suffix;
     std::vector<std::string> files;
     for (int i = 2; i < argc; ++i) {
         const std::string a = argv[i];
@@ -99,6 +100,7 @@ int main(int argc, char **argv) {
         else if (a == "--mem-cap-gb") mem_cap_gb = atof(next());
         else if (a == "--alphabet") alphabet = std::string(next()) == "Protein" ? Alphabet::Protein : Alphabet::DNA;
         else if (a == "--device") device = atoi(next());
+        else if (a == "--suffix") suffix = next();   // config.cpp:279: build one chunk of the graph
         else if (a == "-o" || a == "--outfile-base") out = next();
         else if (a == "-v" || a == "--verbose") verbose = true;
         else if (a[0] == '-') { fprintf(stderr, "Error: unknown option %s\n", a.c_str()); return usage(); }
@@ -122,7 +124,7 @@ int main(int argc, char **argv) {
         if (k < 2) { fprintf(stderr, "Error: k must be at least 2\n"); return 1; }
         auto t0 = std::chrono::steady_clock::now();
         // cli/build.cpp:100,122-134: BOSS node length = k - 1
-        BOSSConstructor constructor(k - 1, canonical, (uint8_t)count_width, "", threads, mem_cap_gb * 1e9,
+        BOSSConstructor constructor(k - 1, canonical, (uint8_t)count_width, suffix, threads, mem_cap_gb * 1e9,
                                     ContainerType::VECTOR, "/tmp/", 1e9, alphabet, device);
         std::vector<std::string> batch;
         size_t batch_bytes = 0, n_seq = 0;
@@ -154,7 +156,8 @@ int main(int argc, char **argv) {
                (unsigned long long)(chunk.size() - 1), std::chrono::duration<double>(t2 - t0).count(),
                std::chrono::duration<double>(t1 - t0).count(), chunk.stats.device_ms,
                chunk.stats.kernel_launches);
-        chunk.serialize(out);
+        // cli/build.cpp:139-145: a --suffix chunk is written to <outbase>.<suffix>
+        chunk.serialize(suffix.empty() ? out : out + "." + suffix);
     } catch (const std::exception &e) {   // logger->error + exit(1) in the reference
         fprintf(stderr, "%s\n", e.what());
         return 1;

@@ -27,8 +27,8 @@ def dna_reads(seed, n, length, G, e=0.01, n_frac=0.0):
     return reads
 
 
-def gpu_build(reads, K, alphabet="DNA", canonical=False, bits_per_count=0, counts=None):
-    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, canonical, bits_per_count,
+def gpu_build(reads, K, alphabet="DNA", canonical=False, bits_per_count=0, counts=None, suffix=""):
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, canonical, bits_per_count, suffix,
                                                     alphabet=alphabet)
     if counts is not None:
         ctor.add_sequences(list(zip(reads, [int(c) for c in counts])))
@@ -42,10 +42,10 @@ def gpu_build(reads, K, alphabet="DNA", canonical=False, bits_per_count=0, count
     return chunk
 
 
-def check(reads, K, alphabet="DNA", canonical=False, bits_per_count=0, counts=None):
-    chunk = gpu_build(reads, K, alphabet, canonical, bits_per_count, counts)
+def check(reads, K, alphabet="DNA", canonical=False, bits_per_count=0, counts=None, suffix=""):
+    chunk = gpu_build(reads, K, alphabet, canonical, bits_per_count, counts, suffix)
     ref = oracle_lib.oracle_build(reads, K, alphabet=alphabet, canonical=canonical,
-                                  bits_per_count=bits_per_count, counts=counts)
+                                  bits_per_count=bits_per_count, counts=counts, suffix=suffix)
     assert chunk.n_rows == ref["n_rows"]
     assert chunk.stats["n_real"] == ref["n_real"]
     assert chunk.stats["n_dummy_sink"] == ref["n_sink"]
@@ -203,12 +203,12 @@ from golden_cases import CASES, case_reads  # noqa: E402
 from test_oracle_golden import assert_chunk_equals_golden, load_golden  # noqa: E402
 
 
-@pytest.mark.parametrize("name", sorted(n for n in CASES if not CASES[n].get("suffix")))
+@pytest.mark.parametrize("name", sorted(CASES))
 def test_gpu_matches_reference_golden(name):
     case = CASES[name]
     reads, counts = case_reads(case)
     chunk = gpu_build(reads, case["K"], case.get("alphabet", "DNA"), case.get("canonical", False),
-                      case.get("bpc", 0), counts)
+                      case.get("bpc", 0), counts, case.get("suffix", ""))
     res = {"W": chunk.W, "last": chunk.last, "F": chunk.F, "weights": chunk.weights}
     assert_chunk_equals_golden(res, load_golden(name), case.get("bpc", 0))
 
@@ -228,3 +228,47 @@ def test_midsort_fold_path(K, canonical, bpc, explicit, monkeypatch):
     monkeypatch.setenv("MTG_MIDSORT_MIN", str(1 << 60))
     d = check(reads, K, canonical=canonical, bits_per_count=bpc, counts=counts)
     assert np.array_equal(c.W_words, d.W_words)
+
+
+# ---- suffix-filtered chunks: `build --suffix S` (KmerExtractorBOSS) ----
+
+@pytest.mark.parametrize("K,suffix,canonical,bpc", [
+    (10, "$", False, 0), (10, "A", False, 0), (10, "T", True, 8), (10, "$$", False, 0),
+    (10, "$C", True, 0), (10, "GT", True, 8), (10, "A$", False, 0), (5, "$$$$", False, 4),
+    (5, "ACGT", True, 0), (31, "$", True, 8), (31, "CA", False, 0), (31, "$G", True, 0),
+    (28, "TT", False, 16), (29, "G", True, 0), (45, "AC", True, 2), (60, "$", False, 0),
+    (3, "$", True, 8), (2, "$", False, 0), (2, "C", True, 0)])
+def test_suffix_chunk_matches_oracle(K, suffix, canonical, bpc):
+    reads = dna_reads(K * 7 + len(suffix), 300, 90, 2500, e=0.01, n_frac=0.004)
+    reads += ["ACGT"[i % 4] * (K - 1) for i in range(4)] + ["A" * K, "C" * (K + 1), "N" * 40, ""]
+    check(reads, K, canonical=canonical, bits_per_count=bpc, suffix=suffix)
+
+
+def test_suffix_chunk_explicit_counts_and_protein():
+    reads = dna_reads(77, 200, 80, 1500, e=0.01, n_frac=0.005)
+    counts = np.random.default_rng(5).integers(1, 300, len(reads)).astype(np.uint64)
+    check(reads, 12, canonical=True, bits_per_count=8, counts=counts, suffix="$A")
+    check(reads, 12, canonical=False, bits_per_count=12, counts=counts, suffix="G")
+    prot = synth.packed_to_strings(synth.protein_reads_packed_np(3, 80, 70))
+    prot[0] = prot[0][:10] + "*?x" + prot[0][13:]
+    for suffix in ("$", "A", "$K", "XL"):
+        check(prot, 8, alphabet="Protein", suffix=suffix)
+
+
+def test_suffix_chunks_partition_the_kmer_set():
+    """All suffixes of length 1 together hold every framed k-mer exactly once (what
+    `build -l 1` + `concatenate` relies on, cli/build.cpp:100-138)."""
+    reads = dna_reads(91, 250, 100, 3000, e=0.01, n_frac=0.003)
+    total = 0
+    for sfx in "$ACGT":
+        c = check(reads, 15, suffix=sfx)
+        total += c.stats["n_real"]
+    ref = sum(oracle_lib.oracle_build(reads, 15, suffix=s)["n_real"] for s in "$ACGT")
+    assert total == ref and total > 0
+
+
+def test_suffix_rejects_bad_arguments():
+    with pytest.raises(mtg_b200.MtgError):
+        mtg_b200.BOSSChunkConstructor.initialize(4, filter_suffix="ACGTA")   # not shorter than k + 1
+    with pytest.raises(mtg_b200.MtgError):
+        mtg_b200.BOSSChunkConstructor.initialize(10, filter_suffix="AN")     # outside the alphabet
