@@ -169,6 +169,9 @@ int mtg_mg_build(mtg_ctx *ctx, const void *d_all_src_nodes, uint64_t n_all, uint
  * (tuning aid): ms_out[0] = digit-histogram kernel, [1] = mean onesweep pass, [2] = whole sort. */
 int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_vals, int iters,
                          float *ms_out);
+/* test/bench hook: times the unique (fold) kernel alone on keys[i] = i / dup; ms_out[0] = best ms,
+ * ms_out[1] = number of distinct keys found */
+int mtg_debug_unique_bench(int device, uint64_t n, uint32_t dup, int with_starts, int iters, float *ms_out);
 
 #ifdef __cplusplus
 }

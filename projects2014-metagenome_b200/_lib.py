@@ -42,7 +42,7 @@ class MtgChunk(ctypes.Structure):
 EXPORTS = ["mtg_create", "mtg_destroy", "mtg_last_error", "mtg_push_reads",
            "mtg_push_packed_device", "mtg_packed_size", "mtg_pack_reads", "mtg_build_chunk",
            "mtg_build_chunk_device", "mtg_set_stream", "mtg_free_chunk", "mtg_debug_sorted_kmers", "mtg_debug_free", "mtg_debug_sort_u64",
-           "mtg_debug_sort_u128", "mtg_debug_sort_bench", "mtg_mg_part_bits", "mtg_mg_extract",
+           "mtg_debug_sort_u128", "mtg_debug_sort_bench", "mtg_debug_unique_bench", "mtg_mg_part_bits", "mtg_mg_extract",
            "mtg_mg_collect", "mtg_mg_targets", "mtg_mg_dummies", "mtg_mg_build"]
 
 _lib = None
@@ -100,6 +100,9 @@ def load():
     lib.mtg_debug_sort_bench.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int,
                                          ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
     lib.mtg_debug_sort_bench.restype = ctypes.c_int
+    lib.mtg_debug_unique_bench.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint32, ctypes.c_int,
+                                           ctypes.c_int, ctypes.POINTER(ctypes.c_float)]
+    lib.mtg_debug_unique_bench.restype = ctypes.c_int
     vpp = ctypes.POINTER(ctypes.c_void_p)
     lib.mtg_mg_part_bits.argtypes = [ctypes.c_void_p]
     lib.mtg_mg_part_bits.restype = ctypes.c_uint32

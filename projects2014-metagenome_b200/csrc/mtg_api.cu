@@ -1236,6 +1236,49 @@ int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_val
     return MTG_OK;
 }
 
+// Device-resident timing of the unique / fold kernel alone: keys[i] = i / dup (u64), best of iters.
+int mtg_debug_unique_bench(int device, uint64_t n, uint32_t dup, int with_starts, int iters, float *ms_out) {
+    try {
+        MTG_CUDA(cudaSetDevice(device));
+        t_arena = std::make_shared<Arena>();
+        cudaStream_t s;
+        MTG_CUDA(cudaStreamCreate(&s));
+        {
+            DevBuf a(8 * n, s), b(8 * n, s), starts, ctr(64, s), tctr(4, s);
+            DevBuf status(sizeof(unsigned long long) * unique_status_words(n), s);
+            if (with_starts) starts.alloc(8 * (n + 1), s);
+            std::vector<uint64_t> h(1 << 20);
+            fill_random_words(a.as<uint64_t>(), n, 1, ~0ull, false, s);   // touch
+            fill_iota_div(a.as<uint64_t>(), n, dup ? dup : 1, s);
+            cudaEvent_t e0, e1;
+            cudaEventCreate(&e0); cudaEventCreate(&e1);
+            ms_out[0] = 1e30f;
+            unsigned launches = 0;
+            for (int it = 0; it < iters; ++it) {
+                cudaEventRecord(e0, s);
+                unique_keys<uint64_t>(a.as<uint64_t>(), n, b.as<uint64_t>(), with_starts ? starts.as<uint64_t>() : nullptr,
+                                      ctr.as<unsigned long long>(), status.as<unsigned long long>(),
+                                      tctr.as<unsigned int>(), s, &launches);
+                cudaEventRecord(e1, s);
+                MTG_CUDA(cudaStreamSynchronize(s));
+                float t = 0;
+                cudaEventElapsedTime(&t, e0, e1);
+                ms_out[0] = std::min(ms_out[0], t);
+            }
+            unsigned long long m = 0;
+            MTG_CUDA(cudaMemcpy(&m, ctr.p, 8, cudaMemcpyDeviceToHost));
+            ms_out[1] = (float)m;
+            cudaEventDestroy(e0); cudaEventDestroy(e1);
+        }
+        cudaStreamSynchronize(s);
+        cudaStreamDestroy(s);
+        t_arena.reset();
+    } catch (const CudaError &e) {
+        return fail_cuda(nullptr, e);
+    }
+    return MTG_OK;
+}
+
 int mtg_debug_sort_u64(int device, uint64_t *keys, uint32_t *vals, uint64_t n, uint32_t key_bits) {
     return debug_sort(device, keys, vals, n, key_bits, false);
 }

@@ -120,6 +120,18 @@ __device__ __forceinline__ void bulk_load_g2s(void *dst_smem, const void *src_gm
                  "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
                  : "memory");
 }
+// several copies on one barrier: mbar_expect(total bytes) once, then bulk_copy_g2s per piece
+__device__ __forceinline__ void mbar_expect(unsigned long long *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_copy_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
+                                              unsigned long long *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst_smem)),
+                 "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 __device__ __forceinline__ void mbar_wait(unsigned long long *bar, uint32_t phase) {
     uint32_t ok = 0;
     while (!ok) {

@@ -83,7 +83,7 @@ __device__ __forceinline__ void warp_append(bool emit, KeyT v, KeyT *out, uint64
 constexpr int DC_THREADS = 256;
 constexpr int DC_IPT = 8;
 constexpr int DC_TILE = DC_THREADS * DC_IPT;
-constexpr int DC_POOL = 3 * DC_TILE;          // window keys staged per tile (all labels together)
+constexpr int DC_POOL = 2 * DC_TILE + 64;     // window keys staged per tile (all labels together)
 constexpr int DC_MAX_CH = 32;
 
 template <typename KeyT>
@@ -104,6 +104,10 @@ __global__ void dc_partition_kernel(const KeyT *__restrict__ reals, uint64_t m, 
     part[t] = lower_bound_idx(reals, m, bi, probe);
 }
 
+// Tile and windows are staged by TMA bulk copies (one elected thread, one mbarrier): no registers
+// hold data in flight and the class / node-head tests read neighbours from shared memory.
+constexpr int DC_HALO = 16;   // reals staged before the tile (class test looks back <= sigma^2 rows)
+
 template <typename KeyT>
 __global__ void __launch_bounds__(DC_THREADS)
 dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t nch, BucketIndex bi,
@@ -111,53 +115,69 @@ dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t n
                 uint32_t *__restrict__ heads, KeyT *sink_keys, uint64_t sink_cap,
                 unsigned long long *d_num_sink) {
     using WT = WordTraits<KeyT>;
-    extern __shared__ __align__(16) unsigned char dc_smem[];
-    KeyT *win = reinterpret_cast<KeyT *>(dc_smem);       // [DC_POOL]
+    constexpr uint32_t AL = 16 / sizeof(KeyT);            // keys per 16-byte TMA granule
+    extern __shared__ __align__(128) unsigned char dc_smem[];
+    KeyT *tk = reinterpret_cast<KeyT *>(dc_smem) + DC_HALO;   // tk[-DC_HALO .. DC_TILE)
+    KeyT *win = tk + DC_TILE;                                 // [DC_POOL]
+    __shared__ __align__(8) unsigned long long bar;
     __shared__ uint64_t w_lo[DC_MAX_CH];
-    __shared__ uint32_t w_off[DC_MAX_CH + 1];           // pool offset of the window, ~0u = not staged
+    __shared__ uint32_t w_off[DC_MAX_CH];                 // pool offset of window[0], ~0u = not staged
     __shared__ uint32_t w_len[DC_MAX_CH];
     const uint32_t L = al.L, K = al.K;
     const KeyT maskL = WT::low_mask(L);
     const uint64_t j = blockIdx.x;
     const uint64_t i0 = j * DC_TILE;
-    if (threadIdx.x < nch) {
-        uint64_t lo = part[j * nch + threadIdx.x];
-        uint64_t hi = part[(j + 1) * nch + threadIdx.x] + 1;
-        if (hi > m) hi = m;
-        w_lo[threadIdx.x] = lo;
-        w_len[threadIdx.x] = hi > lo ? (uint32_t)(hi - lo < 0xffffffffull ? hi - lo : 0xffffffffull) : 0;
-    }
-    __syncthreads();
+    const uint32_t valid = (uint32_t)(m - i0 < (uint64_t)DC_TILE ? m - i0 : DC_TILE);
+    const uint32_t halo = j ? DC_HALO : 0;
     if (threadIdx.x == 0) {
-        uint32_t off = 0;
+        mbar_init(&bar, 1);
+        uint32_t off = 0, total = 0;
+        uint32_t c_off[DC_MAX_CH], c_bytes[DC_MAX_CH];
         for (uint32_t c = 0; c < nch; ++c) {
-            if (w_len[c] <= (uint32_t)DC_POOL - off) { w_off[c] = off; off += w_len[c]; }
-            else w_off[c] = ~0u;
+            uint64_t lo = part[j * nch + c];
+            uint64_t hi = part[(j + 1) * nch + c] + 1;
+            if (hi > m) hi = m;
+            const uint64_t len = hi > lo ? hi - lo : 0;
+            const uint32_t lead = (uint32_t)(lo & (AL - 1));           // keys before lo in its granule
+            const uint64_t span = (lead + len + AL - 1) & ~(uint64_t)(AL - 1);
+            w_lo[c] = lo;
+            w_len[c] = (uint32_t)(len < 0xffffffffull ? len : 0xffffffffull);
+            c_bytes[c] = 0;
+            if (span <= (uint64_t)DC_POOL - off) {
+                w_off[c] = off + lead;
+                c_off[c] = off;
+                c_bytes[c] = (uint32_t)(span * sizeof(KeyT));
+                off += (uint32_t)span;
+                total += c_bytes[c];
+            } else {
+                w_off[c] = ~0u;
+            }
         }
-        w_off[nch] = off;
+        const uint32_t tile_bytes = (((halo + valid) * (uint32_t)sizeof(KeyT)) + 15u) & ~15u;
+        mbar_expect(&bar, total + tile_bytes);
+        bulk_copy_g2s(tk - halo, reals + i0 - halo, tile_bytes, &bar);
+        for (uint32_t c = 0; c < nch; ++c)
+            if (c_bytes[c])
+                bulk_copy_g2s(win + c_off[c], reals + (w_lo[c] & ~(uint64_t)(AL - 1)), c_bytes[c], &bar);
     }
     __syncthreads();
-    for (uint32_t c = 0; c < nch; ++c) {
-        if (w_off[c] == ~0u) continue;
-        const uint64_t lo = w_lo[c];
-        KeyT *dst = win + w_off[c];
-        for (uint32_t t = threadIdx.x; t < w_len[c]; t += DC_THREADS) dst[t] = reals[lo + t];
-    }
-    __syncthreads();
+    mbar_wait(&bar, 0);
 
 #pragma unroll 2
     for (int r = 0; r < DC_IPT; ++r) {
-        const uint64_t i = i0 + (uint64_t)r * DC_THREADS + threadIdx.x;
+        const uint32_t t = (uint32_t)r * DC_THREADS + threadIdx.x;
+        const uint64_t i = i0 + t;
         bool emit_sink = false, node_head = false;
         KeyT sink = WT::zero();
-        if (i < m) {
-            KeyT x = reals[i];
-            KeyT W = w_and(x, maskL);
-            KeyT grp = w_shr(x, 2 * L);
+        if (t < valid) {
+            const KeyT x = tk[t];
+            const KeyT W = w_and(x, maskL);
+            const KeyT grp = w_shr(x, 2 * L);
             bool first = true;   // first element of its (x >> 2L, W) class = distinct target node
             node_head = true;    // first k-mer of its node
             for (uint64_t q = i; q-- > 0;) {
-                KeyT y = reals[q];
+                const long long s = (long long)t - (long long)(i - q);
+                const KeyT y = s >= -(long long)halo ? tk[s] : reals[q];
                 if (q + 1 == i) node_head = !w_eq(w_shr(y, L), w_shr(x, L));
                 if (!w_eq(w_shr(y, 2 * L), grp)) break;
                 if (w_eq(w_and(y, maskL), W)) { first = false; break; }
@@ -170,13 +190,16 @@ dc_sinks_kernel(const KeyT *__restrict__ reals, uint64_t m, Alpha al, uint32_t n
                 bool have = false;
                 if (w_off[c] != ~0u) {
                     const KeyT *wk = win + w_off[c];
-                    uint32_t lo = 0, hi = w_len[c];
-                    while (lo < hi) {
-                        uint32_t mid = (lo + hi) >> 1;
-                        if (w_lt(wk[mid], sink)) lo = mid + 1; else hi = mid;
+                    const uint32_t len = w_len[c];
+                    uint32_t base = 0, n = len;   // branch-free lower bound
+                    while (n > 1) {
+                        const uint32_t half = n >> 1;
+                        if (w_lt(wk[base + half - 1], sink)) base += half;
+                        n -= half;
                     }
-                    p = w_lo[c] + lo;
-                    if (lo < w_len[c]) { at = wk[lo]; have = true; }
+                    if (n == 1 && w_lt(wk[base], sink)) ++base;
+                    p = w_lo[c] + base;
+                    if (base < len) { at = wk[base]; have = true; }
                     else if (p < m) { at = reals[p]; have = true; }
                 } else {
                     p = lower_bound_idx(reals, m, bi, sink);
@@ -521,7 +544,7 @@ void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64
     const BucketIndex bi = make_bi(al, bucket_idx);
     dc_partition_kernel<KeyT><<<(unsigned)div_up((tiles + 1) * nch, (size_t)256), 256, 0, stream>>>(
         reals, m, al, nch, bi, tiles, part);
-    const size_t smem = sizeof(KeyT) * DC_POOL;
+    const size_t smem = sizeof(KeyT) * (DC_HALO + DC_TILE + DC_POOL);
     auto kern = dc_sinks_kernel<KeyT>;
     static bool attr_set = false;
     if (!attr_set) {

@@ -32,22 +32,39 @@ __device__ __forceinline__ uint64_t lookback_exclusive(unsigned long long *statu
             if (lane == 0) st_relaxed_u64(status, SCAN_FLAG_INCL | aggregate);
         } else {
             if (lane == 0) st_relaxed_u64(status + tile, SCAN_FLAG_AGG | aggregate);
+            // LBW x 32 predecessors are requested per round, nearest window first. Measured on B200
+            // (scripts/unique_bench.py, 1.2 G keys): LBW 1 -> 3.84 ms, 4 -> 4.21 ms; without any
+            // look-back the same kernel takes 1.66 ms, i.e. the wait is for the predecessors' tile
+            // loads (a tile cannot finish before its 32 predecessors have counted), not for the
+            // window width.
+            constexpr int LBW = 1;
             long long base = (long long)tile - 1;
-            while (true) {
-                long long idx = base - (long long)lane;
-                unsigned long long s = idx >= 0 ? ld_relaxed_u64(status + idx) : SCAN_FLAG_INCL;
-                while (__any_sync(0xffffffffu, (s >> 62) == 0)) {
-                    if ((s >> 62) == 0) s = ld_relaxed_u64(status + idx);
+            bool done = false;
+            while (!done) {
+                unsigned long long s[LBW];
+#pragma unroll
+                for (int k = 0; k < LBW; ++k) {
+                    long long idx = base - 32 * k - (long long)lane;
+                    s[k] = idx >= 0 ? ld_relaxed_u64(status + idx) : SCAN_FLAG_INCL;
                 }
-                unsigned incl = __ballot_sync(0xffffffffu, (s >> 62) == 2);
-                uint64_t v = s & SCAN_VALUE_MASK;
-                if (incl) {
-                    unsigned first = __ffs(incl) - 1;
-                    excl += warp_sum_u64(lane <= first ? v : 0);
-                    break;
+#pragma unroll
+                for (int k = 0; k < LBW; ++k) {
+                    if (done) continue;
+                    long long idx = base - 32 * k - (long long)lane;
+                    while (__any_sync(0xffffffffu, (s[k] >> 62) == 0)) {
+                        if ((s[k] >> 62) == 0) s[k] = ld_relaxed_u64(status + idx);
+                    }
+                    unsigned incl = __ballot_sync(0xffffffffu, (s[k] >> 62) == 2);
+                    uint64_t v = s[k] & SCAN_VALUE_MASK;
+                    if (incl) {
+                        unsigned first = __ffs(incl) - 1;
+                        excl += warp_sum_u64(lane <= first ? v : 0);
+                        done = true;
+                    } else {
+                        excl += warp_sum_u64(v);
+                    }
                 }
-                excl += warp_sum_u64(v);
-                base -= 32;
+                base -= 32 * LBW;
             }
             if (lane == 0) st_relaxed_u64(status + tile, SCAN_FLAG_INCL | (excl + aggregate));
         }

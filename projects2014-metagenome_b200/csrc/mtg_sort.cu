@@ -906,6 +906,17 @@ __global__ void fill_random_kernel(uint64_t *words, uint64_t nwords, uint64_t se
 }
 }  // namespace
 
+namespace {
+__global__ void fill_iota_div_kernel(uint64_t *words, uint64_t n, uint32_t div) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) words[i] = i / div;
+}
+}  // namespace
+void fill_iota_div(uint64_t *words, uint64_t n, uint32_t div, cudaStream_t stream) {
+    if (!n) return;
+    fill_iota_div_kernel<<<(unsigned)div_up(n, (size_t)256), 256, 0, stream>>>(words, n, div);
+}
+
 void fill_random_words(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask, bool wide,
                        cudaStream_t stream) {
     if (!nwords) return;

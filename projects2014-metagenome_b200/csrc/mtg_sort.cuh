@@ -48,6 +48,7 @@ size_t sort_tile_keys(bool wide);
 // test/bench helper: pseudo-random words (top word of every key masked with hi_mask)
 void fill_random_words(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask, bool wide,
                        cudaStream_t stream);   // keys per tile of the active kernel configuration
+void fill_iota_div(uint64_t *words, uint64_t n, uint32_t div, cudaStream_t stream);   // words[i] = i / div
 template <typename KeyT>
 size_t sort_status_words(uint64_t n) {
     return (div_up(n, sort_tile_keys(sizeof(KeyT) > 8)) + 1) * RADIX;

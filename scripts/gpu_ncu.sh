@@ -17,7 +17,7 @@ if [ "${2:-}" != "nofull" ]; then
 NPS=${NCU_PASSES_PER_STEP:-34}
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:onesweep_pass -s $NPS -c 1 \
    -o gpurun_out/onesweep_full_$TAG -f $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
-HEAVY='extract_kernel|sort_histogram|unique_kernel|dummy_candidates|emit_kernel|merge_tiles|merge_reals|append_rc|dummy_ranks|generate_source'
+HEAVY=${NCU_HEAVY:-'extract_kernel|unique_bulk|dc_sinks|merge_tiles|merge_reals|emit_kernel'}
 timeout 1200 ncu --set full --clock-control none --import-source on -k "regex:$HEAVY" -s ${NCU_HEAVY_SKIP:-15} -c ${NCU_HEAVY_COUNT:-15} \
    -o gpurun_out/heavy_full_$TAG -f $CMD > gpurun_out/ncu_heavy_$TAG.log 2>&1
 ls -la gpurun_out/*.ncu-rep
