@@ -145,6 +145,7 @@ int mtg_debug_sort_u128(int device, uint64_t *keys_lohi, uint32_t *vals /*nullab
  * between contexts (NCCL all-to-all / all-gather in multi_gpu.py). All buffers are device
  * memory; element size is 8 bytes if (k+1)*L <= 64, else 16. Sequence of calls per context:
  *   mtg_push_reads* -> mtg_mg_extract -> [all-to-all by bucket] -> mtg_mg_collect
+ *   [canonical: -> mtg_mg_strands -> [all-to-all of both strands by final range] -> mtg_mg_merge]
  *   -> mtg_mg_targets -> [all-to-all by bucket] -> mtg_mg_dummies -> [all-gather]
  *   -> mtg_mg_build  (chunk of this range; the host concatenates with Chunk::extend). */
 uint32_t mtg_mg_part_bits(const mtg_ctx *ctx);
@@ -153,6 +154,19 @@ uint32_t mtg_mg_part_bits(const mtg_ctx *ctx);
 int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_t *n);
 /* Sort + fold the k-mers routed to this context (d_keys NULL: the context's own extraction). */
 int mtg_mg_collect(mtg_ctx *ctx, const void *d_keys, uint64_t n, uint64_t *n_real);
+/* Canonical mode only (both_strands): mtg_mg_extract / mtg_mg_collect route and reduce the CANONICAL
+ * k-mers; the second strand is produced from the distinct ones, as add_reverse_complements does
+ * (boss_chunk_construct.cpp:179-222). mtg_mg_strands returns X = the canonical k-mers of this
+ * rank's stage-1 range (sorted, [x_bucket_counts] per routing bucket) and R = the reverse
+ * complements of the non-palindromes grouped by bucket ([r_bucket_counts]); d_xc / d_rc are their
+ * uint32 counts (NULL without --count-kmers; palindrome counts already doubled). The caller plans
+ * the FINAL ranges on x + r counts, exchanges X (keeping rank order) and R, and hands the received
+ * arrays to mtg_mg_merge, which sorts R and merges: the real k-mers of the final range. Library
+ * memory stays valid until mtg_mg_merge returns. */
+int mtg_mg_strands(mtg_ctx *ctx, uint64_t *x_bucket_counts, uint64_t *r_bucket_counts, void **d_x, void **d_xc,
+                   uint64_t *n_x, void **d_r, void **d_rc, uint64_t *n_r);
+int mtg_mg_merge(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t n_x, const void *d_r,
+                 const uint32_t *d_rc, uint64_t n_r, uint64_t *n_real);
 /* Sorted distinct target nodes (k-mer minus first char) of this range's k-mers, with the
  * per-bucket counts for routing them to the owner of the node. */
 int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint64_t *n);

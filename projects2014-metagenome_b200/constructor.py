@@ -279,6 +279,24 @@ class BOSSChunkConstructor:
         self._check(self._lib.mtg_mg_collect(self._ctx, ctypes.c_void_p(dptr), n, ctypes.byref(m)))
         return m.value
 
+    def mg_strands(self):
+        """canonical mode -> (x_counts, r_counts, (x_ptr, xc_ptr, n_x), (r_ptr, rc_ptr, n_r))"""
+        nb = 1 << self.mg_part_bits()
+        xc, rc = np.zeros(nb, dtype=np.uint64), np.zeros(nb, dtype=np.uint64)
+        u64p = ctypes.POINTER(ctypes.c_uint64)
+        px, pxc, pr, prc = ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p(), ctypes.c_void_p()
+        nx, nr = ctypes.c_uint64(), ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_strands(self._ctx, xc.ctypes.data_as(u64p), rc.ctypes.data_as(u64p),
+                                             ctypes.byref(px), ctypes.byref(pxc), ctypes.byref(nx),
+                                             ctypes.byref(pr), ctypes.byref(prc), ctypes.byref(nr)))
+        return xc, rc, (px.value or 0, pxc.value or 0, nx.value), (pr.value or 0, prc.value or 0, nr.value)
+
+    def mg_merge(self, x_ptr, xc_ptr, n_x, r_ptr, rc_ptr, n_r):
+        m = ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_merge(self._ctx, ctypes.c_void_p(x_ptr), ctypes.c_void_p(xc_ptr), n_x,
+                                           ctypes.c_void_p(r_ptr), ctypes.c_void_p(rc_ptr), n_r, ctypes.byref(m)))
+        return m.value
+
     def mg_targets(self):
         counts = np.zeros(1 << self.mg_part_bits(), dtype=np.uint64)
         ptr, n = ctypes.c_void_p(), ctypes.c_uint64()

@@ -208,7 +208,7 @@ struct mtg_ctx {
     unsigned launches = 0;
     // range-partitioned (multi-GPU) build state, see mtg_mg_* below
     struct Mg {
-        DevBuf keys, targets, tset, sinks, src;
+        DevBuf keys, targets, tset, sinks, src, rkeys, rcounts;
         RealSet reals;
         uint64_t nt = 0, n_sink = 0, n_src = 0, n_input = 0;
     } mg;
@@ -1300,10 +1300,12 @@ template <typename KeyT>
 void mg_extract_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **d_keys, uint64_t *n_out) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
-    const bool both = ctx->prm.both_strands != 0;
+    // canonical mode: only min(x, rc(x)) is routed and reduced here; the second strand is
+    // produced from the DISTINCT canonical k-mers afterwards (mtg_mg_strands), like
+    // add_reverse_complements does after the collector (boss_chunk_construct.cpp:179-222)
+    const bool both = false;
     uint64_t n_ub = 0;
     for (auto &seg : ctx->segs) n_ub += seg.n_windows_max;
-    if (both) n_ub *= 2;
     DevBuf ctr(64, s);
     unsigned long long *d_ctr = ctr.as<unsigned long long>();
     MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
@@ -1439,6 +1441,111 @@ void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, void **d_src
 
 namespace {
 
+// Canonical mode, after mg_collect: X = distinct canonical k-mers of this rank's stage-1 range
+// (sorted; palindrome counts doubled), R = reverse complements of the non-palindromes grouped by
+// routing bucket. Both are routed to the owners of the FINAL ranges (planned on x + r counts).
+template <typename KeyT>
+void mg_strands_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *x_counts, uint64_t *r_counts, void **d_x, void **d_xc,
+                     uint64_t *n_x, void **d_r, void **d_rc, uint64_t *n_r) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint32_t KL = al.K * al.L, nb = 1u << pb;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    RealSet &rs = ctx->mg.reals;
+    const uint64_t m = rs.m;
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    DevBuf rb0(sizeof(KeyT) * std::max<uint64_t>(m, 1), s), rb1(sizeof(KeyT) * std::max<uint64_t>(m, 1), s);
+    DevBuf cb0, cb1;
+    if (counting) { cb0.alloc(4 * std::max<uint64_t>(m, 1), s); cb1.alloc(4 * std::max<uint64_t>(m, 1), s); }
+    append_reverse_complements<KeyT>(rs.keys.as<KeyT>(), rb0.as<KeyT>(), counting ? rs.counts.as<uint32_t>() : nullptr,
+                                     counting ? cb0.as<uint32_t>() : nullptr, m, al, ctx->cmax, d_ctr, s,
+                                     &ctx->launches);
+    const uint64_t mb = read_counter(d_ctr, s);
+    for (uint32_t i = 0; i < nb; ++i) x_counts[i] = r_counts[i] = 0;
+    if (pb == 0) {
+        x_counts[0] = m;
+        r_counts[0] = mb;
+    } else {
+        if (mb) {   // group R by bucket: one pass on the top pb bits, its digit offsets are the bounds
+            SortPlan plan;
+            plan.n = 0;
+            plan.p[plan.n++] = DigitPass{0, (int)(KL - pb), (int)pb};
+            SortWorkspace ws;
+            DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(mb), s);
+            DevBuf hist(sizeof(unsigned long long) * MAX_SORT_PASSES * RADIX, s);
+            DevBuf tc(sizeof(unsigned int) * MAX_SORT_PASSES, s);
+            ws.status = status.as<unsigned long long>();
+            ws.hist = hist.as<unsigned long long>();
+            ws.tile_counters = tc.as<unsigned int>();
+            KeyT *keys[2] = {rb0.as<KeyT>(), rb1.as<KeyT>()};
+            uint32_t *vals[2] = {cb0.as<uint32_t>(), cb1.as<uint32_t>()};
+            int cur = radix_sort<KeyT>(keys, counting ? vals : nullptr, mb, plan, ws, s, &ctx->launches);
+            std::vector<unsigned long long> off(RADIX);
+            MTG_CUDA(cudaMemcpyAsync(off.data(), ws.hist, 8 * RADIX, cudaMemcpyDeviceToHost, s));
+            MTG_CUDA(cudaStreamSynchronize(s));
+            for (uint32_t i = 0; i < nb; ++i) r_counts[i] = (i + 1 < nb ? off[i + 1] : mb) - off[i];
+            if (cur == 1) { std::swap(rb0, rb1); std::swap(cb0, cb1); }
+        }
+        std::vector<uint64_t> bounds(nb + 1, 0);
+        DevBuf db(8 * (nb + 1), s);
+        bucket_bounds<KeyT>(rs.keys.as<KeyT>(), m, pb, KL - pb, db.as<uint64_t>(), s, &ctx->launches);
+        MTG_CUDA(cudaMemcpyAsync(bounds.data(), db.p, 8 * (nb + 1), cudaMemcpyDeviceToHost, s));
+        MTG_CUDA(cudaStreamSynchronize(s));
+        for (uint32_t i = 0; i < nb; ++i) x_counts[i] = bounds[i + 1] - bounds[i];
+    }
+    ctx->mg.rkeys = std::move(rb0);
+    ctx->mg.rcounts = std::move(cb0);
+    *d_x = rs.keys.p;
+    *d_xc = counting ? rs.counts.p : nullptr;
+    *n_x = m;
+    *d_r = ctx->mg.rkeys.p;
+    *d_rc = counting ? ctx->mg.rcounts.p : nullptr;
+    *n_r = mb;
+}
+
+// Final-range owner: X received from all ranks in rank order (= sorted as a whole, the stage-1
+// ranges are increasing key ranges), R in any order. Sorts R and merges -> the sorted distinct
+// real k-mers of this range, both strands (what add_reverse_complements leaves behind).
+template <typename KeyT>
+void mg_merge_impl(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t nx, const void *d_r,
+                   const uint32_t *d_rc, uint64_t nr, uint64_t *n_real) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    DevBuf rb0(sizeof(KeyT) * std::max<uint64_t>(nr, 1), s), rb1(sizeof(KeyT) * std::max<uint64_t>(nr, 1), s);
+    DevBuf cb0, cb1;
+    MTG_CUDA(cudaMemcpyAsync(rb0.p, d_r, sizeof(KeyT) * nr, cudaMemcpyDeviceToDevice, s));
+    if (counting) {
+        cb0.alloc(4 * std::max<uint64_t>(nr, 1), s);
+        cb1.alloc(4 * std::max<uint64_t>(nr, 1), s);
+        MTG_CUDA(cudaMemcpyAsync(cb0.p, d_rc, 4 * nr, cudaMemcpyDeviceToDevice, s));
+    }
+    SortPlan plan;
+    plan.n = 0;
+    plan_add_key_bits(plan, 0, al.K * al.L);
+    sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, nr, plan, s, &ctx->launches);
+    rb1.release(); cb1.release();
+    const uint64_t m2 = nx + nr;
+    DevBuf merged(sizeof(KeyT) * std::max<uint64_t>(m2, 1) + 16, s), merged_counts;
+    if (counting) merged_counts.alloc(4 * std::max<uint64_t>(m2, 1), s);
+    {
+        DevBuf part(8 * merge_partition_words(m2), s);
+        merge_sorted<KeyT>((const KeyT *)d_x, nx, rb0.as<KeyT>(), nr, counting ? d_xc : nullptr,
+                           counting ? cb0.as<uint32_t>() : nullptr, merged.as<KeyT>(),
+                           counting ? merged_counts.as<uint32_t>() : nullptr, part.as<uint64_t>(), s, &ctx->launches);
+        MTG_CUDA(cudaStreamSynchronize(s));   // d_x / d_r belong to the caller
+    }
+    const uint64_t n_input = ctx->mg.reals.n_input;
+    ctx->mg.rkeys.release();
+    ctx->mg.rcounts.release();
+    ctx->mg.reals.keys = std::move(merged);
+    ctx->mg.reals.counts = std::move(merged_counts);
+    ctx->mg.reals.m = m2;
+    ctx->mg.reals.n_input = n_input;
+    *n_real = m2;
+}
+
 template <typename KeyT>
 void mg_build_impl(mtg_ctx *ctx, const void *d_all_src, uint64_t n_all, uint64_t lo_bucket, uint64_t hi_bucket,
                    uint32_t pb, bool first, mtg_chunk *out, bool device_output) {
@@ -1528,6 +1635,23 @@ int mtg_mg_collect(mtg_ctx *ctx, const void *d_keys, uint64_t n, uint64_t *n_rea
         else collect_reals<uint64_t>(ctx, &ctx->mg.reals, nullptr, nullptr, d_keys ? d_keys : ctx->mg.keys.p, n);
         ctx->mg.keys.release();
         *n_real = ctx->mg.reals.m;
+    })
+}
+
+int mtg_mg_strands(mtg_ctx *ctx, uint64_t *x_bucket_counts, uint64_t *r_bucket_counts, void **d_x, void **d_xc,
+                   uint64_t *n_x, void **d_r, void **d_rc, uint64_t *n_r) {
+    MG_GUARD(ctx, {
+        if (!ctx->prm.both_strands) return fail(ctx, MTG_ERR_STATE, "mtg_mg_strands is a canonical-mode phase");
+        if (wide) mg_strands_impl<u128>(ctx, mg_part_bits(ctx), x_bucket_counts, r_bucket_counts, d_x, d_xc, n_x, d_r, d_rc, n_r);
+        else mg_strands_impl<uint64_t>(ctx, mg_part_bits(ctx), x_bucket_counts, r_bucket_counts, d_x, d_xc, n_x, d_r, d_rc, n_r);
+    })
+}
+
+int mtg_mg_merge(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t n_x, const void *d_r,
+                 const uint32_t *d_rc, uint64_t n_r, uint64_t *n_real) {
+    MG_GUARD(ctx, {
+        if (wide) mg_merge_impl<u128>(ctx, d_x, d_xc, n_x, d_r, d_rc, n_r, n_real);
+        else mg_merge_impl<uint64_t>(ctx, d_x, d_xc, n_x, d_r, d_rc, n_r, n_real);
     })
 }
 

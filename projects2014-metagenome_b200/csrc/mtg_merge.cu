@@ -93,7 +93,7 @@ void merge_sorted(const KeyT *A, uint64_t na, const KeyT *B, uint64_t nb, const 
     const uint64_t ntiles = div_up(total, (size_t)TILE);
     merge_partition_kernel<KeyT><<<(unsigned)div_up(ntiles + 1, (size_t)128), 128, 0, stream>>>(
         A, na, B, nb, TILE, ntiles, part);
-    if (Ac)
+    if (outc)   // (Ac / Bc may be NULL when their array is empty)
         merge_tiles_kernel<KeyT, true><<<(unsigned)ntiles, MG_THREADS, 0, stream>>>(A, na, B, nb, Ac, Bc, part,
                                                                                    out, outc);
     else

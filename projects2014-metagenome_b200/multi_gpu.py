@@ -8,6 +8,10 @@ of the sort key (boss_chunk_construct.cpp:366-397, :462-525, :754-792, :917-931)
      (top part_bits bits of the KMerBOSS word)                         mtg_mg_extract
   2. all-to-all #1: every bucket goes to the rank that owns its range   NCCL all_to_all_single
   3. owners sort + fold their k-mers (+ counts)                          mtg_mg_collect
+  3b. canonical mode: steps 1-3 handle the canonical k-mers only; the owners then emit both
+      strands of their DISTINCT k-mers (mtg_mg_strands), a second (small) all-to-all routes them
+      by the final ranges (planned on both strands) and the owners sort the reverse complements
+      and merge (mtg_mg_merge) -- add_reverse_complements (boss_chunk_construct.cpp:179-222)
   4. target nodes x[2..K] of the owned k-mers, grouped by bucket         mtg_mg_targets
   5. all-to-all #2: targets go to the owner of that node range          NCCL all_to_all_single
   6. owners: dummy sinks = targets \\ sources, sources-1 = sources \\ targets   mtg_mg_dummies
@@ -66,9 +70,9 @@ def concat_chunks(chunks):
 class _CudaPtr:
     """Zero-copy torch view of library-owned device memory (__cuda_array_interface__)."""
 
-    def __init__(self, ptr, n, words):
+    def __init__(self, ptr, n, words, typestr="<i8"):
         shape = (n, words) if words > 1 else (n,)
-        self.__cuda_array_interface__ = {"shape": shape, "typestr": "<i8", "data": (ptr, False),
+        self.__cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (ptr, False),
                                          "version": 2, "strides": None}
 
 
@@ -77,6 +81,16 @@ def as_tensor(ptr, n, words, device):
     if n == 0:
         return torch.empty((0, words) if words > 1 else (0,), dtype=torch.int64, device=device)
     return torch.as_tensor(_CudaPtr(ptr, n, words), device=device)
+
+
+def as_counts(ptr, n, device):
+    """uint32 k-mer counts of the library as an int32 tensor (bit pattern preserved); None if ptr is 0."""
+    import torch
+    if not ptr:
+        return None
+    if n == 0:
+        return torch.empty((0,), dtype=torch.int32, device=device)
+    return torch.as_tensor(_CudaPtr(ptr, n, 1, "<i4"), device=device)
 
 
 def key_words(K, alphabet):
@@ -108,6 +122,20 @@ class RangedRank:
         self._keep = None
         return self.n_real
 
+    def strands(self):
+        """canonical mode: (x_counts, r_counts, X, X counts, R, R counts) -- zero-copy views"""
+        xc, rc, (px, pxc, nx), (pr, prc, nr) = self.ctor.mg_strands()
+        return (xc, rc, as_tensor(px, nx, self.words, self.device), as_counts(pxc, nx, self.device),
+                as_tensor(pr, nr, self.words, self.device), as_counts(prc, nr, self.device))
+
+    def merge(self, X, Xc, R, Rc):
+        self._keep = (X, Xc, R, Rc)
+        nx, nr = X.shape[0], R.shape[0]
+        self.n_real = self.ctor.mg_merge(X.data_ptr() if nx else 0, Xc.data_ptr() if (Xc is not None and nx) else 0, nx,
+                                         R.data_ptr() if nr else 0, Rc.data_ptr() if (Rc is not None and nr) else 0, nr)
+        self._keep = None
+        return self.n_real
+
     def targets(self):
         counts, ptr, n = self.ctor.mg_targets()
         return counts, as_tensor(ptr, n, self.words, self.device)
@@ -136,6 +164,7 @@ class VirtualBuild:
 
     def __init__(self, world, K, canonical=False, bits_per_count=0, alphabet="DNA", device=0):
         self.world = world
+        self.canonical = canonical
         self.ranks = [RangedRank(K, canonical, bits_per_count, alphabet, device) for _ in range(world)]
 
     def add_sequences(self, rank, sequences):
@@ -149,14 +178,35 @@ class VirtualBuild:
         self.ranges = plan_ranges(hist, g)
         offs = [_bucket_offsets(c, self.ranges) for c, _ in ex]
         routed = [torch.cat([ex[s][1][offs[s][d][0]:offs[s][d][1]] for s in range(g)]) for d in range(g)]
+        torch.cuda.synchronize()   # the library works on its own streams
         for d, r in enumerate(self.ranks):
             r.collect(routed[d])
         del routed
+        if self.canonical:
+            # second strand from the distinct canonical k-mers, routed by the FINAL ranges
+            st = [r.strands() for r in self.ranks]
+            hist = np.sum([x + rr for x, rr, *_ in st], axis=0)
+            self.ranges = plan_ranges(hist, g)
+            xo = [_bucket_offsets(x, self.ranges) for x, *_ in st]
+            ro = [_bucket_offsets(rr, self.ranges) for _, rr, *_ in st]
+            counting = st[0][3] is not None
+
+            def route(idx, offs, d):
+                return torch.cat([st[s][idx][offs[s][d][0]:offs[s][d][1]] for s in range(g)])
+
+            recv = [(route(2, xo, d), route(3, xo, d) if counting else None,
+                     route(4, ro, d), route(5, ro, d) if counting else None) for d in range(g)]
+            torch.cuda.synchronize()
+            for d, r in enumerate(self.ranks):
+                r.merge(*recv[d])
+            del recv, st
         tg = [r.targets() for r in self.ranks]
         toffs = [_bucket_offsets(c, self.ranges) for c, _ in tg]
         recv = [torch.cat([tg[s][1][toffs[s][d][0]:toffs[s][d][1]] for s in range(g)]) for d in range(g)]
+        torch.cuda.synchronize()
         src = [r.dummies(recv[d]).clone() for d, r in enumerate(self.ranks)]
         all_src = torch.cat(src)
+        torch.cuda.synchronize()
         chunks = [r.build(all_src, self.ranges[d][0], self.ranges[d][1], d == 0)
                   for d, r in enumerate(self.ranks)]
         return chunks
@@ -181,6 +231,7 @@ class DistBuild:
         self.world = dist.get_world_size(group)
         self.rank_id = dist.get_rank(group)
         self.rank = RangedRank(K, canonical, bits_per_count, alphabet, device)
+        self.canonical = canonical
         self.a2a_bytes = 0
         self.a2a_ms = 0.0
 
@@ -193,7 +244,7 @@ class DistBuild:
         dist.all_gather_into_tensor(all_sizes, sizes, group=self.group)
         recv_sizes = all_sizes[:, self.rank_id].tolist()
         shape = (int(sum(recv_sizes)),) + tuple(send.shape[1:])
-        recv = torch.empty(shape, dtype=torch.int64, device=dev)
+        recv = torch.empty(shape, dtype=send.dtype, device=dev)
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         dist.all_to_all_single(recv, send.contiguous(), recv_sizes, list(send_sizes), group=self.group)
@@ -201,7 +252,8 @@ class DistBuild:
         ev1.synchronize()
         self.a2a_ms += ev0.elapsed_time(ev1)
         own = send_sizes[self.rank_id]
-        self.a2a_bytes += (int(sum(send_sizes)) - own) * 8 * self.rank.words
+        per_elem = send.element_size() * (send.shape[1] if send.dim() > 1 else 1)
+        self.a2a_bytes += (int(sum(send_sizes)) - own) * per_elem
         return recv
 
     def build(self, device_output=False):
@@ -212,6 +264,18 @@ class DistBuild:
         dist.all_reduce(hist, group=self.group)
         self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
         self.rank.collect(self._exchange(keys, split_sizes(counts, self.ranges)))
+        if self.canonical:
+            # second strand from the distinct canonical k-mers, routed by the FINAL ranges
+            xc, rc, X, Xc, R, Rc = self.rank.strands()
+            hist = torch.from_numpy((xc + rc).astype(np.int64)).to(dev)
+            dist.all_reduce(hist, group=self.group)
+            self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
+            xs, rs = split_sizes(xc, self.ranges), split_sizes(rc, self.ranges)
+            rX = self._exchange(X, xs)      # received in rank order = increasing stage-1 key ranges
+            rR = self._exchange(R, rs)
+            rXc = self._exchange(Xc, xs) if Xc is not None else None
+            rRc = self._exchange(Rc, rs) if Rc is not None else None
+            self.rank.merge(rX, rXc, rR, rRc)
         tcounts, tg = self.rank.targets()
         src = self.rank.dummies(self._exchange(tg, split_sizes(tcounts, self.ranges)))
         n_src = torch.tensor([src.shape[0]], dtype=torch.int64, device=dev)
