@@ -149,7 +149,7 @@ int mtg_debug_sort_u128(int device, uint64_t *keys_lohi, uint32_t *vals /*nullab
  *   -> mtg_mg_targets -> [all-to-all by bucket] -> mtg_mg_dummies -> [all-gather]
  *   -> mtg_mg_build  (chunk of this range; the host concatenates with Chunk::extend). */
 uint32_t mtg_mg_part_bits(const mtg_ctx *ctx);
-/* Extracts the pushed reads (both strands in canonical mode) and groups the k-mers by bucket:
+/* Extracts the pushed reads (the canonical k-mers in canonical mode) and groups the k-mers by bucket:
  * bucket_counts[2^part_bits] (host), *d_keys library-owned until mtg_mg_collect. */
 int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_t *n);
 /* Sort + fold the k-mers routed to this context (d_keys NULL: the context's own extraction). */
@@ -171,9 +171,11 @@ int mtg_mg_merge(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t n
  * per-bucket counts for routing them to the owner of the node. */
 int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint64_t *n);
 /* d_targets_in: all target nodes that fall into this range. Finds the range's dummy sinks
- * (kept inside) and returns its source nodes without incoming edge (forward-lex packing). */
-int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, void **d_src_nodes,
-                   uint64_t *n_src, uint64_t *n_sink);
+ * (kept inside) and returns its source nodes without incoming edge (forward-lex packing).
+ * run_lengths[n_runs] (host, may be NULL): d_targets_in is the concatenation of sorted runs of
+ * these lengths (every rank sends its targets sorted) -- they are merged instead of re-sorted. */
+int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, const uint64_t *run_lengths,
+                   uint32_t n_runs, void **d_src_nodes, uint64_t *n_src, uint64_t *n_sink);
 /* d_all_src_nodes: the gathered source nodes of every range. Emits the chunk of bucket range
  * [lo_bucket, hi_bucket); first_range adds the all-'$' row (boss_chunk_construct.cpp:310-315). */
 int mtg_mg_build(mtg_ctx *ctx, const void *d_all_src_nodes, uint64_t n_all, uint64_t lo_bucket,

@@ -1383,9 +1383,37 @@ void mg_targets_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **
     *n_out = nt;
 }
 
+// `a` holds consecutive sorted runs: pairwise merge-path rounds (ceil(log2(#runs)) passes over the
+// data instead of a full radix sort). On return `a` holds the sorted array.
 template <typename KeyT>
-void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, void **d_src, uint64_t *n_src,
-                     uint64_t *n_sink_out) {
+void merge_runs(mtg_ctx *ctx, DevBuf &a, DevBuf &b, std::vector<uint64_t> runs) {
+    cudaStream_t s = ctx->stream;
+    uint64_t total = 0;
+    for (uint64_t r : runs) total += r;
+    DevBuf part(8 * merge_partition_words(total), s);
+    while (runs.size() > 1) {
+        std::vector<uint64_t> next;
+        uint64_t off = 0;
+        for (size_t i = 0; i < runs.size(); i += 2) {
+            const uint64_t la = runs[i], lb = i + 1 < runs.size() ? runs[i + 1] : 0;
+            if (lb == 0 || la == 0) {
+                MTG_CUDA(cudaMemcpyAsync(b.as<KeyT>() + off, a.as<KeyT>() + off, sizeof(KeyT) * (la + lb),
+                                         cudaMemcpyDeviceToDevice, s));
+            } else {
+                merge_sorted<KeyT>(a.as<KeyT>() + off, la, a.as<KeyT>() + off + la, lb, nullptr, nullptr,
+                                   b.as<KeyT>() + off, nullptr, part.as<uint64_t>(), s, &ctx->launches);
+            }
+            next.push_back(la + lb);
+            off += la + lb;
+        }
+        std::swap(a, b);
+        runs.swap(next);
+    }
+}
+
+template <typename KeyT>
+void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, const uint64_t *run_lengths, uint32_t n_runs,
+                     void **d_src, uint64_t *n_src, uint64_t *n_sink_out) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const uint32_t K = al.K, L = al.L;
@@ -1398,10 +1426,17 @@ void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, void **d_src
     DevBuf t0(sizeof(KeyT) * std::max<uint64_t>(n_in, 1), s), t1(sizeof(KeyT) * std::max<uint64_t>(n_in, 1), s);
     MTG_CUDA(cudaMemcpyAsync(t0.p, d_in, sizeof(KeyT) * n_in, cudaMemcpyDeviceToDevice, s));
     {
-        SortPlan plan;
-        plan.n = 0;
-        plan_add_key_bits(plan, 0, (K - 1) * L);
-        sort_keys<KeyT>(t0, t1, nullptr, nullptr, n_in, plan, s, &ctx->launches);
+        uint64_t run_total = 0;
+        for (uint32_t i = 0; i < n_runs; ++i) run_total += run_lengths[i];
+        if (run_lengths && n_runs && run_total == n_in) {
+            // every source sends its targets sorted: merge the runs
+            merge_runs<KeyT>(ctx, t0, t1, std::vector<uint64_t>(run_lengths, run_lengths + n_runs));
+        } else {
+            SortPlan plan;
+            plan.n = 0;
+            plan_add_key_bits(plan, 0, (K - 1) * L);
+            sort_keys<KeyT>(t0, t1, nullptr, nullptr, n_in, plan, s, &ctx->launches);
+        }
         DevBuf status(sizeof(unsigned long long) * unique_status_words(n_in), s), tctr(sizeof(unsigned int), s);
         unique_keys<KeyT>(t0.as<KeyT>(), n_in, t1.as<KeyT>(), nullptr, d_ctr, status.as<unsigned long long>(),
                           tctr.as<unsigned int>(), s, &ctx->launches);
@@ -1662,11 +1697,11 @@ int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint
     })
 }
 
-int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, void **d_src_nodes, uint64_t *n_src,
-                   uint64_t *n_sink) {
+int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, const uint64_t *run_lengths,
+                   uint32_t n_runs, void **d_src_nodes, uint64_t *n_src, uint64_t *n_sink) {
     MG_GUARD(ctx, {
-        if (wide) mg_dummies_impl<u128>(ctx, d_targets_in, n_in, d_src_nodes, n_src, n_sink);
-        else mg_dummies_impl<uint64_t>(ctx, d_targets_in, n_in, d_src_nodes, n_src, n_sink);
+        if (wide) mg_dummies_impl<u128>(ctx, d_targets_in, n_in, run_lengths, n_runs, d_src_nodes, n_src, n_sink);
+        else mg_dummies_impl<uint64_t>(ctx, d_targets_in, n_in, run_lengths, n_runs, d_src_nodes, n_src, n_sink);
     })
 }
 

@@ -140,9 +140,9 @@ class RangedRank:
         counts, ptr, n = self.ctor.mg_targets()
         return counts, as_tensor(ptr, n, self.words, self.device)
 
-    def dummies(self, targets_in):
+    def dummies(self, targets_in, runs=None):
         n = targets_in.shape[0]
-        ptr, n_src, n_sink = self.ctor.mg_dummies(targets_in.data_ptr() if n else 0, n)
+        ptr, n_src, n_sink = self.ctor.mg_dummies(targets_in.data_ptr() if n else 0, n, runs)
         self.n_sink = n_sink
         return as_tensor(ptr, n_src, self.words, self.device)
 
@@ -204,7 +204,8 @@ class VirtualBuild:
         toffs = [_bucket_offsets(c, self.ranges) for c, _ in tg]
         recv = [torch.cat([tg[s][1][toffs[s][d][0]:toffs[s][d][1]] for s in range(g)]) for d in range(g)]
         torch.cuda.synchronize()
-        src = [r.dummies(recv[d]).clone() for d, r in enumerate(self.ranks)]
+        runs = [[toffs[s][d][1] - toffs[s][d][0] for s in range(g)] for d in range(g)]
+        src = [r.dummies(recv[d], runs[d]).clone() for d, r in enumerate(self.ranks)]
         all_src = torch.cat(src)
         torch.cuda.synchronize()
         chunks = [r.build(all_src, self.ranges[d][0], self.ranges[d][1], d == 0)
@@ -251,6 +252,7 @@ class DistBuild:
         ev1.record()
         ev1.synchronize()
         self.a2a_ms += ev0.elapsed_time(ev1)
+        self.last_recv_sizes = recv_sizes
         own = send_sizes[self.rank_id]
         per_elem = send.element_size() * (send.shape[1] if send.dim() > 1 else 1)
         self.a2a_bytes += (int(sum(send_sizes)) - own) * per_elem
@@ -277,7 +279,8 @@ class DistBuild:
             rRc = self._exchange(Rc, rs) if Rc is not None else None
             self.rank.merge(rX, rXc, rR, rRc)
         tcounts, tg = self.rank.targets()
-        src = self.rank.dummies(self._exchange(tg, split_sizes(tcounts, self.ranges)))
+        tin = self._exchange(tg, split_sizes(tcounts, self.ranges))
+        src = self.rank.dummies(tin, self.last_recv_sizes)   # one sorted run per source rank
         n_src = torch.tensor([src.shape[0]], dtype=torch.int64, device=dev)
         all_n = torch.empty(self.world, dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(all_n, n_src, group=self.group)
