@@ -224,6 +224,8 @@ def run_ours(args, wl):
         import torch.distributed as dist
         # all-to-all over NVLink: 64 p2p channels measured 620 GB/s per GPU and direction at 2 GPUs
         # against 425 GB/s with NCCL's default (scripts/a2a_bench.py)
+        if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line
         os.environ.setdefault("NCCL_MIN_P2P_NCHANNELS", "64")
         os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", "64")
         dist.init_process_group("nccl", device_id=dev)
@@ -232,8 +234,11 @@ def run_ours(args, wl):
     n_reads = wl["n_reads"]
     if world > 1:
         from mtg_b200 import multi_gpu
-        return multi_gpu.bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler,
-                               algorithmic_bytes)
+        try:
+            return multi_gpu.bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler,
+                                   algorithmic_bytes)
+        finally:
+            dist.destroy_process_group()
 
     # ---- synthetic reads, generated straight into HBM in the packed layout ----
     packed = synth.dna_reads_packed_torch(wl["seed"], n_reads, L, wl["G"], wl["e"], device=dev)

@@ -1443,21 +1443,15 @@ void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, const uint64
     }
     const uint64_t nt = read_counter(d_ctr, s);
     t0.release();
-    DevBuf bidx;
-    const bool use_index = m >= (1u << 16);
-    if (use_index) {
-        bidx.alloc(8 * bucket_index_words(al), s);
-        build_bucket_index<KeyT>(reals, m, al, bidx.as<uint64_t>(), s, &ctx->launches);
-    }
+    DevBuf scratch(ranged_scratch_bytes(m, nt), s);
     uint64_t cap = std::max<uint64_t>(1024, std::max(m, nt) / 8);
     DevBuf sink, src;
     uint64_t n_sink = 0, d1 = 0;
     while (true) {
         sink.alloc(sizeof(KeyT) * cap, s);
         src.alloc(sizeof(KeyT) * cap, s);
-        ranged_dummy_candidates<KeyT>(reals, m, t1.as<KeyT>(), nt, al, use_index ? bidx.as<uint64_t>() : nullptr,
-                                      sink.as<KeyT>(), cap, d_ctr, src.as<KeyT>(), cap, d_ctr + 1, s,
-                                      &ctx->launches);
+        ranged_dummy_candidates<KeyT>(reals, m, t1.as<KeyT>(), nt, al, scratch.p, sink.as<KeyT>(), cap, d_ctr,
+                                      src.as<KeyT>(), cap, d_ctr + 1, s, &ctx->launches);
         n_sink = read_counter(d_ctr, s);
         d1 = read_counter(d_ctr + 1, s);
         if (n_sink <= cap && d1 <= cap) break;

@@ -434,41 +434,121 @@ __global__ void target_nodes_kernel(const KeyT *__restrict__ reals, uint64_t m, 
 
 // reals: the sorted real k-mers of THIS key range; targets: sorted distinct target nodes that
 // fall into this range (collected from all ranges). sinks = targets \ source nodes,
-// sources-1 = source nodes \ targets (forward-lex packing, like dummy_candidates_kernel).
+// sources-1 = source nodes \ targets (forward-lex packing). Both arrays are sorted by node, so
+// the probes of RJ_TILE consecutive reals fall into one contiguous window of the targets: the
+// window is staged in shared memory by a TMA bulk copy and searched there; a hit sets the
+// target's bit, the sinks are the targets whose bit stays clear (rj_sinks_kernel).
+constexpr int RJ_THREADS = 256;
+constexpr int RJ_IPT = 8;
+constexpr int RJ_TILE = RJ_THREADS * RJ_IPT;
+constexpr int RJ_POOL = 3 * RJ_TILE;
+
+// part[j] = lower_bound(targets, node(reals[min(j * RJ_TILE, m - 1)])), j = 0..tiles
 template <typename KeyT>
-__global__ void __launch_bounds__(256)
-ranged_candidates_kernel(const KeyT *__restrict__ reals, uint64_t m, const KeyT *__restrict__ targets,
-                         uint64_t nt, Alpha al, BucketIndex bi, KeyT *sink_keys, uint64_t sink_cap,
-                         unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
-                         unsigned long long *d_num_src) {
+__global__ void rj_partition_kernel(const KeyT *__restrict__ reals, uint64_t m, const KeyT *__restrict__ targets,
+                                    uint64_t nt, uint32_t L, uint64_t tiles, uint64_t *__restrict__ part) {
+    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j > tiles) return;
+    uint64_t pos = j * RJ_TILE < m ? j * RJ_TILE : m - 1;
+    part[j] = lower_bound_dev(targets, nt, w_shr(reals[pos], L));
+}
+
+template <typename KeyT>
+__global__ void __launch_bounds__(RJ_THREADS)
+rj_join_kernel(const KeyT *__restrict__ reals, uint64_t m, const KeyT *__restrict__ targets, uint64_t nt,
+               Alpha al, const uint64_t *__restrict__ part, uint32_t *__restrict__ hits, KeyT *src_fwd,
+               uint64_t src_cap, unsigned long long *d_num_src) {
     using WT = WordTraits<KeyT>;
+    constexpr uint32_t AL = 16 / sizeof(KeyT);
+    extern __shared__ __align__(128) unsigned char rj_smem[];
+    KeyT *win = reinterpret_cast<KeyT *>(rj_smem);   // [RJ_POOL + AL]
+    __shared__ __align__(8) unsigned long long bar;
     const uint32_t L = al.L, K = al.K;
     const KeyT maskL = WT::low_mask(L);
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    bool emit_sink = false, emit_src = false;
-    KeyT sink = WT::zero(), fwd = WT::zero();
-    if (i < nt) {
-        sink = w_shl(targets[i], L);   // k-mer t$ : node t, W = '$' (zero slot)
-        uint64_t p = lower_bound_idx(reals, m, bi, sink);
-        emit_sink = !(p < m && w_eq(w_shr(reals[p], L), targets[i]));
+    const uint64_t j = blockIdx.x, i0 = j * RJ_TILE;
+    const uint64_t lo = part[j];
+    uint64_t hi = part[j + 1] + 1;   // the node of the next tile's first real may start in this tile
+    if (hi > nt) hi = nt;
+    const uint64_t len = hi > lo ? hi - lo : 0;
+    const uint32_t lead = (uint32_t)(lo & (AL - 1));
+    const uint64_t span = (lead + len + AL - 1) & ~(uint64_t)(AL - 1);
+    const bool staged = span <= (uint64_t)RJ_POOL && len > 0;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar, 1);
+        if (staged) {
+            mbar_expect(&bar, (uint32_t)(span * sizeof(KeyT)));
+            bulk_copy_g2s(win, targets + (lo - lead), (uint32_t)(span * sizeof(KeyT)), &bar);
+        }
     }
-    if (i < m) {
-        KeyT x = reals[i];
-        KeyT node = w_shr(x, L);
-        bool node_head = i == 0 || !w_eq(w_shr(reals[i - 1], L), node);
-        if (node_head) {
-            uint64_t p = lower_bound_dev(targets, nt, node);
-            if (!(p < nt && w_eq(targets[p], node))) {
-                emit_src = true;
-                for (uint32_t c = 1; c < K; ++c) {
-                    KeyT ch = w_and(w_shr(x, L * c), maskL);
-                    fwd = w_or(fwd, w_shl(ch, L * (K - 1 - c)));
+    __syncthreads();
+    if (staged) mbar_wait(&bar, 0);
+    const KeyT *wk = win + lead;
+    const uint32_t wlen = (uint32_t)(staged ? len : 0);
+
+#pragma unroll 2
+    for (int r = 0; r < RJ_IPT; ++r) {
+        const uint64_t i = i0 + (uint64_t)r * RJ_THREADS + threadIdx.x;
+        bool emit_src = false;
+        KeyT fwd = WT::zero();
+        if (i < m) {
+            const KeyT x = reals[i];
+            const KeyT node = w_shr(x, L);
+            const bool node_head = i == 0 || !w_eq(w_shr(reals[i - 1], L), node);
+            if (node_head) {
+                uint64_t p;
+                bool found;
+                if (staged) {
+                    uint32_t base = 0, n = wlen;   // branch-free lower bound
+                    while (n > 1) {
+                        const uint32_t half = n >> 1;
+                        if (w_lt(wk[base + half - 1], node)) base += half;
+                        n -= half;
+                    }
+                    if (n == 1 && w_lt(wk[base], node)) ++base;
+                    p = lo + base;
+                    found = base < wlen ? w_eq(wk[base], node) : (p < nt && w_eq(targets[p], node));
+                } else {
+                    p = lower_bound_dev(targets, nt, node);
+                    found = p < nt && w_eq(targets[p], node);
+                }
+                if (found) {
+                    atomicOr(&hits[p >> 5], 1u << (p & 31));   // target p is a source node: no sink
+                } else {
+                    emit_src = true;
+                    for (uint32_t c = 1; c < K; ++c) {
+                        KeyT ch = w_and(w_shr(x, L * c), maskL);
+                        fwd = w_or(fwd, w_shl(ch, L * (K - 1 - c)));
+                    }
                 }
             }
         }
+        warp_append(emit_src, fwd, src_fwd, src_cap, d_num_src);
     }
-    warp_append(emit_sink, sink, sink_keys, sink_cap, d_num_sink);
-    warp_append(emit_src, fwd, src_fwd, src_cap, d_num_src);
+}
+
+// targets without a hit -> dummy sinks  t$  (node t, W = '$')
+template <typename KeyT>
+__global__ void __launch_bounds__(256)
+rj_sinks_kernel(const KeyT *__restrict__ targets, uint64_t nt, uint32_t L, const uint32_t *__restrict__ hits,
+                KeyT *sink_keys, uint64_t sink_cap, unsigned long long *d_num_sink) {
+    const uint64_t wi = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t nwords = (nt + 31) / 32;
+    uint32_t cand = 0;
+    if (wi < nwords) {
+        cand = ~hits[wi];
+        const uint64_t left = nt - wi * 32;
+        if (left < 32) cand &= (1u << left) - 1;
+    }
+    while (__any_sync(0xffffffffu, cand != 0)) {
+        const bool emit = cand != 0;
+        KeyT sink = WordTraits<KeyT>::zero();
+        if (emit) {
+            const uint32_t b = __ffs(cand) - 1;
+            cand &= cand - 1;
+            sink = w_shl(targets[wi * 32 + b], L);
+        }
+        warp_append(emit, sink, sink_keys, sink_cap, d_num_sink);
+    }
 }
 
 // keep the (key, info) pairs whose key lies in [lo, hi) (hi ignored when !has_hi); order is
@@ -616,20 +696,41 @@ void target_nodes(const KeyT *reals, uint64_t m, Alpha al, KeyT *out, cudaStream
     *launches += 1;
 }
 
+size_t ranged_scratch_bytes(uint64_t m, uint64_t nt) {
+    return 8 * (div_up(m, (size_t)RJ_TILE) + 2) + 4 * (nt / 32 + 2);
+}
+
 template <typename KeyT>
 void ranged_dummy_candidates(const KeyT *reals, uint64_t m, const KeyT *targets, uint64_t nt, Alpha al,
-                             const uint64_t *bucket_idx, KeyT *sink_keys, uint64_t sink_cap,
+                             void *scratch, KeyT *sink_keys, uint64_t sink_cap,
                              unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
                              unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches) {
     MTG_CUDA(cudaMemsetAsync(d_num_sink, 0, sizeof(unsigned long long), stream));
     MTG_CUDA(cudaMemsetAsync(d_num_src, 0, sizeof(unsigned long long), stream));
-    uint64_t n = m > nt ? m : nt;
-    if (n == 0) return;
-    ranged_candidates_kernel<KeyT><<<(unsigned)div_up(n, (size_t)256), 256, 0, stream>>>(
-        reals, m, targets, nt, al, make_bi(al, bucket_idx), sink_keys, sink_cap, d_num_sink, src_fwd, src_cap,
-        d_num_src);
+    const uint64_t tiles = div_up(m, (size_t)RJ_TILE);
+    uint64_t *part = reinterpret_cast<uint64_t *>(scratch);
+    uint32_t *hits = reinterpret_cast<uint32_t *>(part + tiles + 2);
+    MTG_CUDA(cudaMemsetAsync(hits, 0, 4 * (nt / 32 + 2), stream));
+    if (m) {
+        rj_partition_kernel<KeyT><<<(unsigned)div_up(tiles + 1, (size_t)256), 256, 0, stream>>>(
+            reals, m, targets, nt, al.L, tiles, part);
+        const size_t smem = sizeof(KeyT) * (RJ_POOL + 2);
+        auto kern = rj_join_kernel<KeyT>;
+        static bool attr_set = false;
+        if (!attr_set) {
+            MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            attr_set = true;
+        }
+        kern<<<(unsigned)tiles, RJ_THREADS, smem, stream>>>(reals, m, targets, nt, al, part, hits, src_fwd, src_cap,
+                                                           d_num_src);
+        *launches += 2;
+    }
+    if (nt) {
+        rj_sinks_kernel<KeyT><<<(unsigned)div_up(div_up(nt, (size_t)32), (size_t)256), 256, 0, stream>>>(
+            targets, nt, al.L, hits, sink_keys, sink_cap, d_num_sink);
+        *launches += 1;
+    }
     MTG_CUDA(cudaGetLastError());
-    *launches += 1;
 }
 
 template <typename KeyT>
@@ -673,7 +774,7 @@ void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, u
                                    uint8_t *, uint32_t *, cudaStream_t, unsigned *, uint32_t);     \
     template void target_nodes<KeyT>(const KeyT *, uint64_t, Alpha, KeyT *, cudaStream_t, unsigned *); \
     template void ranged_dummy_candidates<KeyT>(const KeyT *, uint64_t, const KeyT *, uint64_t, Alpha, \
-                                                const uint64_t *, KeyT *, uint64_t,               \
+                                                void *, KeyT *, uint64_t,               \
                                                 unsigned long long *, KeyT *, uint64_t,            \
                                                 unsigned long long *, cudaStream_t, unsigned *);   \
     template void filter_key_range<KeyT>(const KeyT *, const uint32_t *, uint64_t, KeyT, KeyT, int, \

@@ -127,9 +127,11 @@ template <typename KeyT>
 void target_nodes(const KeyT *reals, uint64_t m, Alpha al, KeyT *out, cudaStream_t stream,
                   unsigned *launches);
 // sinks = targets \ source nodes of `reals`; sources-1 = source nodes \ targets (forward-lex)
+// scratch: ranged_scratch_bytes(m, nt) bytes (window bounds + target hit bitmap)
+size_t ranged_scratch_bytes(uint64_t m, uint64_t nt);
 template <typename KeyT>
 void ranged_dummy_candidates(const KeyT *reals, uint64_t m, const KeyT *targets, uint64_t nt, Alpha al,
-                             const uint64_t *bucket_idx, KeyT *sink_keys, uint64_t sink_cap,
+                             void *scratch, KeyT *sink_keys, uint64_t sink_cap,
                              unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
                              unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches);
 template <typename KeyT>

@@ -235,6 +235,7 @@ class DistBuild:
         self.canonical = canonical
         self.a2a_bytes = 0
         self.a2a_ms = 0.0
+        self.phase_events = None
 
     def _exchange(self, send, send_sizes):
         """all_to_all of a bucket-grouped tensor; send_sizes[d] elements go to rank d."""
@@ -258,17 +259,39 @@ class DistBuild:
         self.a2a_bytes += (int(sum(send_sizes)) - own) * per_elem
         return recv
 
+    def _mark(self, name):
+        """phase timing (CUDA events on the current stream, which the library shares in bench.py)"""
+        if getattr(self, "phase_events", None) is not None:
+            ev = self.torch.cuda.Event(enable_timing=True)
+            ev.record()
+            self.phase_events.append((name, ev))
+
+    def phase_ms(self):
+        evs = self.phase_events or []
+        out = {}
+        for (_, a), (name, b) in zip(evs, evs[1:]):
+            b.synchronize()
+            out[name] = out.get(name, 0.0) + a.elapsed_time(b)
+        return out
+
     def build(self, device_output=False):
         torch, dist = self.torch, self.dist
         dev = self.rank.device
+        self._mark("start")
         counts, keys = self.rank.extract()
+        self._mark("extract+group")
         hist = torch.from_numpy(counts.astype(np.int64)).to(dev)
         dist.all_reduce(hist, group=self.group)
         self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
-        self.rank.collect(self._exchange(keys, split_sizes(counts, self.ranges)))
+        recv = self._exchange(keys, split_sizes(counts, self.ranges))
+        self._mark("exchange kmers")
+        self.rank.collect(recv)
+        del recv
+        self._mark("collect (sort+fold)")
         if self.canonical:
             # second strand from the distinct canonical k-mers, routed by the FINAL ranges
             xc, rc, X, Xc, R, Rc = self.rank.strands()
+            self._mark("strands")
             hist = torch.from_numpy((xc + rc).astype(np.int64)).to(dev)
             dist.all_reduce(hist, group=self.group)
             self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
@@ -277,10 +300,16 @@ class DistBuild:
             rR = self._exchange(R, rs)
             rXc = self._exchange(Xc, xs) if Xc is not None else None
             rRc = self._exchange(Rc, rs) if Rc is not None else None
+            self._mark("exchange strands")
             self.rank.merge(rX, rXc, rR, rRc)
+            del rX, rR, rXc, rRc
+            self._mark("merge strands")
         tcounts, tg = self.rank.targets()
+        self._mark("targets")
         tin = self._exchange(tg, split_sizes(tcounts, self.ranges))
+        self._mark("exchange targets")
         src = self.rank.dummies(tin, self.last_recv_sizes)   # one sorted run per source rank
+        self._mark("dummies")
         n_src = torch.tensor([src.shape[0]], dtype=torch.int64, device=dev)
         all_n = torch.empty(self.world, dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(all_n, n_src, group=self.group)
@@ -289,7 +318,10 @@ class DistBuild:
         self._all_gather_ragged(parts, src, all_n)
         all_src = torch.cat(parts)
         lo, hi = self.ranges[self.rank_id]
-        return self.rank.build(all_src, lo, hi, self.rank_id == 0, device_output)
+        self._mark("gather sources")
+        out = self.rank.build(all_src, lo, hi, self.rank_id == 0, device_output)
+        self._mark("build (expand+merge+emit)")
+        return out
 
     def _all_gather_ragged(self, parts, src, all_n):
         dist = self.dist
@@ -352,6 +384,7 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
     if rank == 0:
         sampler.start()
     db.a2a_bytes, db.a2a_ms = 0, 0.0
+    db.phase_events = []
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
     dist.barrier()
@@ -362,6 +395,10 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
     dist.barrier()
     ms = torch.tensor([ev0.elapsed_time(ev1)], dtype=torch.float64, device=dev)
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    phases = {k: round(v / args.steps, 3) for k, v in db.phase_ms().items() if k != "start"}
+    db.phase_events = None
+    all_phases = [None] * world
+    dist.all_gather_object(all_phases, phases)
     counters = torch.tensor([stats[-1]["n_input_kmers"], stats[-1]["n_real"], stats[-1]["n_rows"] - 1,
                              db.a2a_bytes, sum(s["n_kernel_launches"] for s in stats)],
                             dtype=torch.int64, device=dev)
@@ -431,7 +468,8 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                      "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None,
                      "alltoall": {"bytes_sent_per_gpu_per_step": int(counters[3]) / world / args.steps,
                                   "ms_per_step": float(a2a) / args.steps, "achieved_GBps": a2a_gbs,
-                                  "peak_GBps": 900.0, "frac": a2a_gbs / 900.0}},
+                                  "peak_GBps": 900.0, "frac": a2a_gbs / 900.0},
+                     "phases_ms_per_rank": all_phases},
         "cpu_baseline": None,
     }
     print(json.dumps(line))
