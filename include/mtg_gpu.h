@@ -158,15 +158,17 @@ int mtg_mg_collect(mtg_ctx *ctx, const void *d_keys, uint64_t n, uint64_t *n_rea
  * k-mers; the second strand is produced from the distinct ones, as add_reverse_complements does
  * (boss_chunk_construct.cpp:179-222). mtg_mg_strands returns X = the canonical k-mers of this
  * rank's stage-1 range (sorted, [x_bucket_counts] per routing bucket) and R = the reverse
- * complements of the non-palindromes grouped by bucket ([r_bucket_counts]); d_xc / d_rc are their
+ * complements of the non-palindromes, sorted as well ([r_bucket_counts]); d_xc / d_rc are their
  * uint32 counts (NULL without --count-kmers; palindrome counts already doubled). The caller plans
  * the FINAL ranges on x + r counts, exchanges X (keeping rank order) and R, and hands the received
- * arrays to mtg_mg_merge, which sorts R and merges: the real k-mers of the final range. Library
- * memory stays valid until mtg_mg_merge returns. */
+ * arrays to mtg_mg_merge with the lengths of the sorted runs R consists of (one per source rank;
+ * NULL = unsorted, R is radix sorted); it merges the runs and X: the real k-mers of the final
+ * range. Library memory stays valid until mtg_mg_merge returns. */
 int mtg_mg_strands(mtg_ctx *ctx, uint64_t *x_bucket_counts, uint64_t *r_bucket_counts, void **d_x, void **d_xc,
                    uint64_t *n_x, void **d_r, void **d_rc, uint64_t *n_r);
 int mtg_mg_merge(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t n_x, const void *d_r,
-                 const uint32_t *d_rc, uint64_t n_r, uint64_t *n_real);
+                 const uint32_t *d_rc, uint64_t n_r, const uint64_t *r_run_lengths, uint32_t n_runs,
+                 uint64_t *n_real);
 /* Sorted distinct target nodes (k-mer minus first char) of this range's k-mers, with the
  * per-bucket counts for routing them to the owner of the node. */
 int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint64_t *n);

@@ -291,10 +291,13 @@ class BOSSChunkConstructor:
                                              ctypes.byref(pr), ctypes.byref(prc), ctypes.byref(nr)))
         return xc, rc, (px.value or 0, pxc.value or 0, nx.value), (pr.value or 0, prc.value or 0, nr.value)
 
-    def mg_merge(self, x_ptr, xc_ptr, n_x, r_ptr, rc_ptr, n_r):
+    def mg_merge(self, x_ptr, xc_ptr, n_x, r_ptr, rc_ptr, n_r, r_runs=None):
         m = ctypes.c_uint64()
+        rl = np.ascontiguousarray(r_runs if r_runs is not None else [], dtype=np.uint64)
         self._check(self._lib.mtg_mg_merge(self._ctx, ctypes.c_void_p(x_ptr), ctypes.c_void_p(xc_ptr), n_x,
-                                           ctypes.c_void_p(r_ptr), ctypes.c_void_p(rc_ptr), n_r, ctypes.byref(m)))
+                                           ctypes.c_void_p(r_ptr), ctypes.c_void_p(rc_ptr), n_r,
+                                           rl.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)) if len(rl) else None,
+                                           len(rl), ctypes.byref(m)))
         return m.value
 
     def mg_targets(self):

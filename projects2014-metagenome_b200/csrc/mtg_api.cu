@@ -1386,7 +1386,8 @@ void mg_targets_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **
 // `a` holds consecutive sorted runs: pairwise merge-path rounds (ceil(log2(#runs)) passes over the
 // data instead of a full radix sort). On return `a` holds the sorted array.
 template <typename KeyT>
-void merge_runs(mtg_ctx *ctx, DevBuf &a, DevBuf &b, std::vector<uint64_t> runs) {
+void merge_runs(mtg_ctx *ctx, DevBuf &a, DevBuf &b, std::vector<uint64_t> runs, DevBuf *ca = nullptr,
+                DevBuf *cb = nullptr) {
     cudaStream_t s = ctx->stream;
     uint64_t total = 0;
     for (uint64_t r : runs) total += r;
@@ -1399,14 +1400,20 @@ void merge_runs(mtg_ctx *ctx, DevBuf &a, DevBuf &b, std::vector<uint64_t> runs) 
             if (lb == 0 || la == 0) {
                 MTG_CUDA(cudaMemcpyAsync(b.as<KeyT>() + off, a.as<KeyT>() + off, sizeof(KeyT) * (la + lb),
                                          cudaMemcpyDeviceToDevice, s));
+                if (ca)
+                    MTG_CUDA(cudaMemcpyAsync(cb->as<uint32_t>() + off, ca->as<uint32_t>() + off, 4 * (la + lb),
+                                             cudaMemcpyDeviceToDevice, s));
             } else {
-                merge_sorted<KeyT>(a.as<KeyT>() + off, la, a.as<KeyT>() + off + la, lb, nullptr, nullptr,
-                                   b.as<KeyT>() + off, nullptr, part.as<uint64_t>(), s, &ctx->launches);
+                merge_sorted<KeyT>(a.as<KeyT>() + off, la, a.as<KeyT>() + off + la, lb,
+                                   ca ? ca->as<uint32_t>() + off : nullptr, ca ? ca->as<uint32_t>() + off + la : nullptr,
+                                   b.as<KeyT>() + off, ca ? cb->as<uint32_t>() + off : nullptr, part.as<uint64_t>(), s,
+                                   &ctx->launches);
             }
             next.push_back(la + lb);
             off += la + lb;
         }
         std::swap(a, b);
+        if (ca) std::swap(*ca, *cb);
         runs.swap(next);
     }
 }
@@ -1495,26 +1502,26 @@ void mg_strands_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *x_counts, uint64_t *r_
     if (pb == 0) {
         x_counts[0] = m;
         r_counts[0] = mb;
+        SortPlan plan;
+        plan.n = 0;
+        plan_add_key_bits(plan, 0, KL);
+        sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s, &ctx->launches);
     } else {
-        if (mb) {   // group R by bucket: one pass on the top pb bits, its digit offsets are the bounds
+        if (mb) {
+            // R is sorted HERE, where the work is balanced (every stage-1 owner holds about the
+            // same number of canonical k-mers); the reverse complements concentrate in the high
+            // final ranges, whose owners then only merge sorted runs
             SortPlan plan;
             plan.n = 0;
-            plan.p[plan.n++] = DigitPass{0, (int)(KL - pb), (int)pb};
-            SortWorkspace ws;
-            DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(mb), s);
-            DevBuf hist(sizeof(unsigned long long) * MAX_SORT_PASSES * RADIX, s);
-            DevBuf tc(sizeof(unsigned int) * MAX_SORT_PASSES, s);
-            ws.status = status.as<unsigned long long>();
-            ws.hist = hist.as<unsigned long long>();
-            ws.tile_counters = tc.as<unsigned int>();
-            KeyT *keys[2] = {rb0.as<KeyT>(), rb1.as<KeyT>()};
-            uint32_t *vals[2] = {cb0.as<uint32_t>(), cb1.as<uint32_t>()};
-            int cur = radix_sort<KeyT>(keys, counting ? vals : nullptr, mb, plan, ws, s, &ctx->launches);
-            std::vector<unsigned long long> off(RADIX);
-            MTG_CUDA(cudaMemcpyAsync(off.data(), ws.hist, 8 * RADIX, cudaMemcpyDeviceToHost, s));
+            plan_add_key_bits(plan, 0, KL);
+            sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s,
+                            &ctx->launches);
+            std::vector<uint64_t> rbounds(nb + 1, 0);
+            DevBuf rdb(8 * (nb + 1), s);
+            bucket_bounds<KeyT>(rb0.as<KeyT>(), mb, pb, KL - pb, rdb.as<uint64_t>(), s, &ctx->launches);
+            MTG_CUDA(cudaMemcpyAsync(rbounds.data(), rdb.p, 8 * (nb + 1), cudaMemcpyDeviceToHost, s));
             MTG_CUDA(cudaStreamSynchronize(s));
-            for (uint32_t i = 0; i < nb; ++i) r_counts[i] = (i + 1 < nb ? off[i + 1] : mb) - off[i];
-            if (cur == 1) { std::swap(rb0, rb1); std::swap(cb0, cb1); }
+            for (uint32_t i = 0; i < nb; ++i) r_counts[i] = rbounds[i + 1] - rbounds[i];
         }
         std::vector<uint64_t> bounds(nb + 1, 0);
         DevBuf db(8 * (nb + 1), s);
@@ -1538,7 +1545,7 @@ void mg_strands_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *x_counts, uint64_t *r_
 // real k-mers of this range, both strands (what add_reverse_complements leaves behind).
 template <typename KeyT>
 void mg_merge_impl(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t nx, const void *d_r,
-                   const uint32_t *d_rc, uint64_t nr, uint64_t *n_real) {
+                   const uint32_t *d_rc, uint64_t nr, const uint64_t *r_runs, uint32_t n_runs, uint64_t *n_real) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const bool counting = ctx->prm.bits_per_count > 0;
@@ -1550,10 +1557,17 @@ void mg_merge_impl(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t
         cb1.alloc(4 * std::max<uint64_t>(nr, 1), s);
         MTG_CUDA(cudaMemcpyAsync(cb0.p, d_rc, 4 * nr, cudaMemcpyDeviceToDevice, s));
     }
-    SortPlan plan;
-    plan.n = 0;
-    plan_add_key_bits(plan, 0, al.K * al.L);
-    sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, nr, plan, s, &ctx->launches);
+    uint64_t run_total = 0;
+    for (uint32_t i = 0; i < n_runs; ++i) run_total += r_runs[i];
+    if (r_runs && n_runs && run_total == nr) {   // one sorted run per source rank
+        merge_runs<KeyT>(ctx, rb0, rb1, std::vector<uint64_t>(r_runs, r_runs + n_runs), counting ? &cb0 : nullptr,
+                         counting ? &cb1 : nullptr);
+    } else {
+        SortPlan plan;
+        plan.n = 0;
+        plan_add_key_bits(plan, 0, al.K * al.L);
+        sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, nr, plan, s, &ctx->launches);
+    }
     rb1.release(); cb1.release();
     const uint64_t m2 = nx + nr;
     DevBuf merged(sizeof(KeyT) * std::max<uint64_t>(m2, 1) + 16, s), merged_counts;
@@ -1677,10 +1691,11 @@ int mtg_mg_strands(mtg_ctx *ctx, uint64_t *x_bucket_counts, uint64_t *r_bucket_c
 }
 
 int mtg_mg_merge(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t n_x, const void *d_r,
-                 const uint32_t *d_rc, uint64_t n_r, uint64_t *n_real) {
+                 const uint32_t *d_rc, uint64_t n_r, const uint64_t *r_run_lengths, uint32_t n_runs,
+                 uint64_t *n_real) {
     MG_GUARD(ctx, {
-        if (wide) mg_merge_impl<u128>(ctx, d_x, d_xc, n_x, d_r, d_rc, n_r, n_real);
-        else mg_merge_impl<uint64_t>(ctx, d_x, d_xc, n_x, d_r, d_rc, n_r, n_real);
+        if (wide) mg_merge_impl<u128>(ctx, d_x, d_xc, n_x, d_r, d_rc, n_r, r_run_lengths, n_runs, n_real);
+        else mg_merge_impl<uint64_t>(ctx, d_x, d_xc, n_x, d_r, d_rc, n_r, r_run_lengths, n_runs, n_real);
     })
 }
 

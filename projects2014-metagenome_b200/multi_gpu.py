@@ -24,6 +24,8 @@ and are covered by world_size-2 gloo tests on CPU; `VirtualBuild` runs the same 
 virtual ranks on ONE GPU (exchange = tensor slicing), which is how the single-GPU parity tests
 check the partitioned path against the oracle.
 """
+import sys
+
 import numpy as np
 
 from .constructor import BOSSChunkConstructor, Chunk
@@ -128,11 +130,12 @@ class RangedRank:
         return (xc, rc, as_tensor(px, nx, self.words, self.device), as_counts(pxc, nx, self.device),
                 as_tensor(pr, nr, self.words, self.device), as_counts(prc, nr, self.device))
 
-    def merge(self, X, Xc, R, Rc):
+    def merge(self, X, Xc, R, Rc, r_runs=None):
         self._keep = (X, Xc, R, Rc)
         nx, nr = X.shape[0], R.shape[0]
         self.n_real = self.ctor.mg_merge(X.data_ptr() if nx else 0, Xc.data_ptr() if (Xc is not None and nx) else 0, nx,
-                                         R.data_ptr() if nr else 0, Rc.data_ptr() if (Rc is not None and nr) else 0, nr)
+                                         R.data_ptr() if nr else 0, Rc.data_ptr() if (Rc is not None and nr) else 0, nr,
+                                         r_runs)
         self._keep = None
         return self.n_real
 
@@ -198,7 +201,7 @@ class VirtualBuild:
                      route(4, ro, d), route(5, ro, d) if counting else None) for d in range(g)]
             torch.cuda.synchronize()
             for d, r in enumerate(self.ranks):
-                r.merge(*recv[d])
+                r.merge(*recv[d], r_runs=[ro[s][d][1] - ro[s][d][0] for s in range(g)])
             del recv, st
         tg = [r.targets() for r in self.ranks]
         toffs = [_bucket_offsets(c, self.ranges) for c, _ in tg]
@@ -233,30 +236,88 @@ class DistBuild:
         self.rank_id = dist.get_rank(group)
         self.rank = RangedRank(K, canonical, bits_per_count, alphabet, device)
         self.canonical = canonical
+        # MTG_A2A=nccl forces the NCCL all-to-all; default: peer stores over NVLink (symmetric memory)
+        import os
+        self.use_symm = (os.environ.get("MTG_A2A", "peer") != "nccl" and dist.get_backend(group) == "nccl"
+                         and self.world > 1)
+        self._slots = {}
+        self._streams = [torch.cuda.Stream(device=self.rank.device) for _ in range(self.world)] if self.use_symm else []
+        if self.use_symm:
+            try:
+                self._symm_slot(0, 1 << 20)
+            except Exception as e:   # no peer mapping on this system: NCCL
+                print("mtg_b200: symmetric memory unavailable (%s), using NCCL all_to_all" % e, file=sys.stderr)
+                self.use_symm = False
         self.a2a_bytes = 0
         self.a2a_ms = 0.0
         self.phase_events = None
 
-    def _exchange(self, send, send_sizes):
-        """all_to_all of a bucket-grouped tensor; send_sizes[d] elements go to rank d."""
+    # ---- exchange: NVLink peer stores into symmetric memory, NCCL all_to_all as the fallback ----
+    def _symm_slot(self, slot, need_bytes):
+        """Symmetric (peer-mapped) receive buffer `slot` of at least need_bytes on EVERY rank; the
+        decision to (re)allocate is taken from numbers all ranks share, so the rendezvous is collective."""
+        import torch.distributed._symmetric_memory as symm
+        cur = self._slots.get(slot)
+        if cur is None or cur[0].numel() < need_bytes:
+            cap = (int(need_bytes * 1.25) + (1 << 20)) & ~0xFFF
+            self._slots.pop(slot, None)
+            buf = symm.empty(cap, dtype=self.torch.uint8, device=self.rank.device)
+            name = self.group.group_name if self.group is not None else self.dist.group.WORLD.group_name
+            hdl = symm.rendezvous(buf, name)
+            cur = (buf, hdl)
+            self._slots[slot] = cur
+        return cur
+
+    def _exchange(self, send, send_sizes, slot=0):
+        """all-to-all of a bucket-grouped tensor; send_sizes[d] rows go to rank d. Returns the rows
+        received, ordered by source rank."""
         torch, dist = self.torch, self.dist
         dev = self.rank.device
         sizes = torch.tensor(send_sizes, dtype=torch.int64, device=dev)
         all_sizes = torch.empty((self.world, self.world), dtype=torch.int64, device=dev)
-        dist.all_gather_into_tensor(all_sizes, sizes, group=self.group)
-        recv_sizes = all_sizes[:, self.rank_id].tolist()
-        shape = (int(sum(recv_sizes)),) + tuple(send.shape[1:])
-        recv = torch.empty(shape, dtype=send.dtype, device=dev)
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-        dist.all_to_all_single(recv, send.contiguous(), recv_sizes, list(send_sizes), group=self.group)
-        ev1.record()
-        ev1.synchronize()
-        self.a2a_ms += ev0.elapsed_time(ev1)
+        dist.all_gather_into_tensor(all_sizes, sizes, group=self.group)   # also orders the ranks: every
+        all_sizes = all_sizes.cpu().numpy()                               # peer has consumed its slot
+        recv_sizes = [int(x) for x in all_sizes[:, self.rank_id]]
         self.last_recv_sizes = recv_sizes
+        tail = tuple(send.shape[1:])
+        row = 1
+        for t in tail:
+            row *= int(t)
         own = send_sizes[self.rank_id]
-        per_elem = send.element_size() * (send.shape[1] if send.dim() > 1 else 1)
-        self.a2a_bytes += (int(sum(send_sizes)) - own) * per_elem
+        self.a2a_bytes += (int(sum(send_sizes)) - own) * send.element_size() * row
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        total = int(sum(recv_sizes))
+        if self.use_symm:
+            need = int(all_sizes.sum(axis=0).max()) * send.element_size() * row
+            buf, hdl = self._symm_slot(slot, max(need, 16))
+            send = send.contiguous()
+            cur = torch.cuda.current_stream()
+            ev0.record()
+            so = np.concatenate([[0], np.cumsum(send_sizes)])
+            for k in range(self.world):
+                d = (self.rank_id + k) % self.world          # staggered: no peer is hit by all at once
+                n_d = int(send_sizes[d])
+                if n_d == 0:
+                    continue
+                off = int(all_sizes[:self.rank_id, d].sum()) * row     # my rows' place in d's buffer
+                dst = hdl.get_buffer(d, (n_d,) + tail, send.dtype, off)
+                st = self._streams[k]
+                st.wait_stream(cur)
+                with torch.cuda.stream(st):
+                    dst.copy_(send[int(so[d]):int(so[d + 1])], non_blocking=True)
+            for st in self._streams:
+                cur.wait_stream(st)
+            hdl.barrier()
+            ev1.record()
+            ev1.synchronize()
+            recv = hdl.get_buffer(self.rank_id, (total,) + tail, send.dtype, 0)
+        else:
+            recv = torch.empty((total,) + tail, dtype=send.dtype, device=dev)
+            ev0.record()
+            dist.all_to_all_single(recv, send.contiguous(), recv_sizes, list(send_sizes), group=self.group)
+            ev1.record()
+            ev1.synchronize()
+        self.a2a_ms += ev0.elapsed_time(ev1)
         return recv
 
     def _mark(self, name):
@@ -296,12 +357,13 @@ class DistBuild:
             dist.all_reduce(hist, group=self.group)
             self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
             xs, rs = split_sizes(xc, self.ranges), split_sizes(rc, self.ranges)
-            rX = self._exchange(X, xs)      # received in rank order = increasing stage-1 key ranges
-            rR = self._exchange(R, rs)
-            rXc = self._exchange(Xc, xs) if Xc is not None else None
-            rRc = self._exchange(Rc, rs) if Rc is not None else None
+            rX = self._exchange(X, xs, 1)   # received in rank order = increasing stage-1 key ranges
+            rR = self._exchange(R, rs, 2)   # one sorted run per source rank
+            r_runs = self.last_recv_sizes
+            rXc = self._exchange(Xc, xs, 3) if Xc is not None else None
+            rRc = self._exchange(Rc, rs, 4) if Rc is not None else None
             self._mark("exchange strands")
-            self.rank.merge(rX, rXc, rR, rRc)
+            self.rank.merge(rX, rXc, rR, rRc, r_runs)
             del rX, rR, rXc, rRc
             self._mark("merge strands")
         tcounts, tg = self.rank.targets()
@@ -333,6 +395,7 @@ class DistBuild:
             parts[r] = buf
 
     def close(self):
+        self._slots.clear()
         self.rank.close()
 
 
@@ -435,7 +498,8 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
         e2e = {"value": int(counters[0]) * e_steps / float(dt), "unit": UNIT,
                "h2d_bytes_per_step": int(n_total * (L + 1)), "d2h_bytes_per_step": int(d2h),
                "ms_per_step": 1e3 * float(dt) / e_steps, "steps": e_steps,
-               "api": "per rank: mtg_push_reads(host) + mtg_mg_* phases + NCCL all-to-all, chunk to host"}
+               "api": "per rank: mtg_push_reads(host) + mtg_mg_* phases + all-to-all, chunk to host"}
+    db_use_symm = db.use_symm
     db.close()
     if rank != 0:
         return
@@ -459,8 +523,11 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                    "n_reads_per_gpu": n_local, "read_len": L, "k": K,
                    "mode": "canonical" if wl["canonical"] else "basic", "count_width": wl["bpc"],
                    "input_kmers": N, "real_kmers": int(counters[1]), "rows": int(counters[2]) + 1,
-                   "partitioning": "key range (top 8 bits of the k-mer word), NCCL all-to-all of k-mers "
-                                   "and target nodes, all-gather of source nodes",
+                   "partitioning": "key range (top 8 bits of the k-mer word); all-to-all of canonical k-mers, "
+                                   "of both strands of the distinct k-mers and of target nodes (%s); "
+                                   "all-gather of source nodes"
+                                   % ("NVLink peer stores into symmetric memory" if db_use_symm
+                                      else "NCCL all_to_all_single"),
                    "l2_policy": "inputs larger than L2 (%.2f GB of keys per GPU and step)"
                                 % (n_windows * 8 * (2 if wl["canonical"] else 1) / 1e9)},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(counters[4]),
