@@ -732,7 +732,8 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
 // [n_sink dummy sinks | d_src dummy sources] with their info bytes. d_ctr + 8 = level histogram.
 template <typename KeyT>
 void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64_t n_sink,
-                    unsigned long long *d_ctr, DevBuf &dk0, DevBuf &di0, uint64_t *d_out) {
+                    unsigned long long *d_ctr, DevBuf &dk0, DevBuf &di0, uint64_t *d_out,
+                    const KeyT *lo = nullptr, const KeyT *hi = nullptr) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const uint32_t K = al.K, L = al.L;
@@ -747,7 +748,7 @@ void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64
     }
     srcB.release();
     DevBuf per_entry(4 * std::max<uint64_t>(d1, 1), s), offsets(8 * (d1 + 1), s);
-    source_prefix_counts<KeyT>(src.as<KeyT>(), d1, al, per_entry.as<uint32_t>(), s, &ctx->launches);
+    source_prefix_counts<KeyT>(src.as<KeyT>(), d1, al, lo, hi, per_entry.as<uint32_t>(), s, &ctx->launches);
     {
         DevBuf status(8 * (d1 / 2048 + 2), s), tctr(4, s);
         exclusive_scan_u32(per_entry.as<uint32_t>(), d1, offsets.as<uint64_t>(),
@@ -759,7 +760,7 @@ void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64
     di0.alloc(4 * std::max<uint64_t>(d, 1), s);
     MTG_CUDA(cudaMemcpyAsync(dk0.p, sink.p, sizeof(KeyT) * n_sink, cudaMemcpyDeviceToDevice, s));
     fill_u32(di0.as<uint32_t>(), INFO_W_DOLLAR, n_sink, s, &ctx->launches);
-    generate_source_dummies<KeyT>(src.as<KeyT>(), per_entry.as<uint32_t>(), offsets.as<uint64_t>(), d1, al,
+    generate_source_dummies<KeyT>(src.as<KeyT>(), offsets.as<uint64_t>(), d1, al, lo, hi,
                                   dk0.as<KeyT>() + n_sink, di0.as<uint32_t>() + n_sink, d_ctr + 8, s,
                                   &ctx->launches);
     sink.release(); src.release(); per_entry.release(); offsets.release();
@@ -1606,21 +1607,17 @@ void mg_build_impl(mtg_ctx *ctx, const void *d_all_src, uint64_t n_all, uint64_t
     DevBuf src(sizeof(KeyT) * std::max<uint64_t>(n_all, 1), s);
     MTG_CUDA(cudaMemcpyAsync(src.p, d_all_src, sizeof(KeyT) * n_all, cudaMemcpyDeviceToDevice, s));
     const uint64_t n_sink = ctx->mg.n_sink;
-    uint64_t d_all = 0;
-    DevBuf ak, ai;
-    expand_sources<KeyT>(ctx, src, n_all, ctx->mg.sinks, n_sink, d_ctr, ak, ai, &d_all);
-    const uint64_t n_srcd = d_all - n_sink;
-    DevBuf dk0(sizeof(KeyT) * std::max<uint64_t>(d_all, 1), s), di0(4 * std::max<uint64_t>(d_all, 1), s);
-    MTG_CUDA(cudaMemcpyAsync(dk0.p, ak.p, sizeof(KeyT) * n_sink, cudaMemcpyDeviceToDevice, s));
-    MTG_CUDA(cudaMemcpyAsync(di0.p, ai.p, 4 * n_sink, cudaMemcpyDeviceToDevice, s));
+    // every range expands the (small, global) list of source-1 nodes but materialises only the
+    // dummy sources of its own key range
     const uint64_t nb = 1ull << pb;
     const bool has_hi = pb > 0 && hi_bucket < nb;
     KeyT lo = pb ? w_shl(WordTraits<KeyT>::from_u64(lo_bucket), KL - pb) : WordTraits<KeyT>::zero();
     KeyT hi = has_hi ? w_shl(WordTraits<KeyT>::from_u64(hi_bucket), KL - pb) : WordTraits<KeyT>::zero();
-    filter_key_range<KeyT>(ak.as<KeyT>() + n_sink, ai.as<uint32_t>() + n_sink, n_srcd, lo, hi, has_hi ? 1 : 0,
-                           dk0.as<KeyT>() + n_sink, di0.as<uint32_t>() + n_sink, d_ctr + 2, s, &ctx->launches);
-    const uint64_t kept = read_counter(d_ctr + 2, s);
-    ak.release(); ai.release();
+    uint64_t d_mine = 0;
+    DevBuf dk0, di0;
+    expand_sources<KeyT>(ctx, src, n_all, ctx->mg.sinks, n_sink, d_ctr, dk0, di0, &d_mine, &lo,
+                         has_hi ? &hi : nullptr);
+    const uint64_t kept = d_mine - n_sink;
     DevBuf bidx;
     const bool use_index = rs.m >= (1u << 16);
     if (use_index) {

@@ -254,66 +254,85 @@ template <> __device__ __forceinline__ int w_clz<u128>(u128 x) {
     return x.hi ? __clzll(x.hi) : 64 + __clzll(x.lo);
 }
 
+// Key range of the chunk being built: dummies outside [lo, hi) belong to another range
+// (multi-GPU) and are neither counted for the layout nor written.
 template <typename KeyT>
-__global__ void source_prefix_counts_kernel(const KeyT *__restrict__ fwd, uint64_t d1, Alpha al,
-                                            uint32_t *__restrict__ per_entry) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= d1) return;
-    const uint32_t nchars = al.K - 1, bits = nchars * al.L;
-    uint32_t lcp = 0;
-    if (i > 0) {
-        KeyT d = w_xor(fwd[i], fwd[i - 1]);
-        bool same = w_eq(d, WordTraits<KeyT>::zero());
-        if (same) lcp = nchars;   // cannot happen for distinct nodes
-        else {
-            int lead = w_clz<KeyT>(d) - (WordTraits<KeyT>::BITS - (int)bits);   // equal leading bits
-            lcp = (uint32_t)lead / al.L;
-        }
+struct KeyRange {
+    KeyT lo, hi;
+    int has_lo, has_hi;
+    __device__ __forceinline__ bool holds(KeyT k) const {
+        return !(has_lo && w_lt(k, lo)) && !(has_hi && !w_lt(k, hi));
     }
-    per_entry[i] = nchars - lcp;
+};
+
+// Node i (forward-lex packing f, sorted) contributes the prefixes of length j = lcp+1 .. K-1, i.e.
+// the dummy sources with c = K - j leading '$': tight word x_{c+t} = s_t (t = 1..j-1), W = s_j.
+// Calls fn(key, c) for each of them, built incrementally: from j to j+1 every node char moves one
+// slot down and s_j enters at slot K-1.
+template <typename KeyT, typename F>
+__device__ __forceinline__ void for_each_new_prefix(KeyT f, uint32_t lcp, Alpha al, F fn) {
+    using WT = WordTraits<KeyT>;
+    const uint32_t L = al.L, K = al.K, nchars = K - 1;
+    const KeyT maskL = WT::low_mask(L);
+    const uint32_t j0 = lcp + 1;
+    KeyT node = WT::zero();
+    for (uint32_t t = 1; t < j0; ++t) {
+        KeyT ch = w_and(w_shr(f, L * (nchars - t)), maskL);
+        node = w_or(node, w_shl(ch, L * (K - j0 + t)));
+    }
+    for (uint32_t j = j0; j <= nchars; ++j) {
+        const uint32_t c = K - j;
+        KeyT sj = w_and(w_shr(f, L * (nchars - j)), maskL);   // W = s_j
+        fn(w_or(node, sj), c);
+        node = w_or(w_shr(node, L), w_shl(sj, L * (K - 1)));
+        node = w_and(node, w_not(maskL));
+    }
 }
 
-// Node i contributes prefixes of length j = lcp+1 .. K-1, i.e. dummy sources with
-// c = K - j leading '$': tight word has x_{c+t} = s_t (t = 1..j-1) and W = s_j.
+template <typename KeyT>
+__device__ __forceinline__ uint32_t fwd_lcp(const KeyT *fwd, uint64_t i, Alpha al) {
+    const uint32_t nchars = al.K - 1, bits = nchars * al.L;
+    if (i == 0) return 0;
+    KeyT d = w_xor(fwd[i], fwd[i - 1]);
+    if (w_eq(d, WordTraits<KeyT>::zero())) return nchars;   // cannot happen for distinct nodes
+    int lead = w_clz<KeyT>(d) - (WordTraits<KeyT>::BITS - (int)bits);   // equal leading bits
+    return (uint32_t)lead / al.L;
+}
+
+template <typename KeyT>
+__global__ void source_prefix_counts_kernel(const KeyT *__restrict__ fwd, uint64_t d1, Alpha al,
+                                            KeyRange<KeyT> range, uint32_t *__restrict__ per_entry) {
+    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= d1) return;
+    const uint32_t lcp = fwd_lcp(fwd, i, al);
+    uint32_t cnt = al.K - 1 - lcp;
+    if (range.has_lo || range.has_hi) {
+        cnt = 0;
+        for_each_new_prefix(fwd[i], lcp, al, [&](KeyT key, uint32_t) { cnt += range.holds(key) ? 1u : 0u; });
+    }
+    per_entry[i] = cnt;
+}
+
 template <typename KeyT>
 __global__ void generate_source_dummies_kernel(const KeyT *__restrict__ fwd,
-                                               const uint32_t *__restrict__ per_entry,
                                                const uint64_t *__restrict__ offsets, uint64_t d1,
-                                               Alpha al, KeyT *__restrict__ out_keys,
+                                               Alpha al, KeyRange<KeyT> range, KeyT *__restrict__ out_keys,
                                                uint32_t *__restrict__ out_info,
                                                unsigned long long *level_hist) {
-    using WT = WordTraits<KeyT>;
-    __shared__ unsigned int sh_levels[MTG_MAX_LEVELS];   // per-block level histogram
+    __shared__ unsigned int sh_levels[MTG_MAX_LEVELS];   // per-block level histogram (ALL ranges)
     for (int c = threadIdx.x; c < MTG_MAX_LEVELS; c += blockDim.x) sh_levels[c] = 0;
     __syncthreads();
     uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    const uint32_t L = al.L, K = al.K, nchars = K - 1;
     if (i < d1) {
-        const KeyT maskL = WT::low_mask(L);
-        KeyT f = fwd[i];
-        uint32_t cnt = per_entry[i];
         uint64_t dst = offsets[i];
-        // char s_t (t = 1..K-1) sits at bit L*(nchars - t) of f. The dummy with c = K - j leading
-        // '$' is  [s_{j-1} .. s_1 at slots c+j-1 .. c+1 | W = s_j]; going from j to j+1 the node
-        // part moves down one slot and s_j enters at the top: built incrementally.
-        const uint32_t j0 = nchars - cnt + 1;
-        // node part for j0: chars s_1..s_{j0-1}
-        KeyT node = WT::zero();
-        for (uint32_t t = 1; t < j0; ++t) {
-            KeyT ch = w_and(w_shr(f, L * (nchars - t)), maskL);
-            node = w_or(node, w_shl(ch, L * (K - j0 + t)));
-        }
-        for (uint32_t j = j0; j <= nchars; ++j) {
-            uint32_t c = K - j;
-            KeyT sj = w_and(w_shr(f, L * (nchars - j)), maskL);   // W = s_j
-            out_keys[dst] = w_or(node, sj);
-            out_info[dst] = c;
-            ++dst;
+        for_each_new_prefix(fwd[i], fwd_lcp(fwd, i, al), al, [&](KeyT key, uint32_t c) {
             atomicAdd(&sh_levels[c - 1], 1u);
-            // next j: every node char moves one slot down (c shrinks by 1), s_j joins at slot K-1
-            node = w_or(w_shr(node, L), w_shl(sj, L * (K - 1)));
-            node = w_and(node, w_not(maskL));
-        }
+            if (range.holds(key)) {
+                out_keys[dst] = key;
+                out_info[dst] = c;
+                ++dst;
+            }
+        });
     }
     __syncthreads();
     for (int c = threadIdx.x; c < MTG_MAX_LEVELS; c += blockDim.x)
@@ -551,33 +570,6 @@ rj_sinks_kernel(const KeyT *__restrict__ targets, uint64_t nt, uint32_t L, const
     }
 }
 
-// keep the (key, info) pairs whose key lies in [lo, hi) (hi ignored when !has_hi); order is
-// irrelevant (the dummies are sorted afterwards)
-template <typename KeyT>
-__global__ void filter_key_range_kernel(const KeyT *__restrict__ keys, const uint32_t *__restrict__ info,
-                                        uint64_t n, KeyT lo, KeyT hi, int has_hi, KeyT *out_keys,
-                                        uint32_t *out_info, unsigned long long *d_num) {
-    uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    bool keep = false;
-    KeyT k = WordTraits<KeyT>::zero();
-    uint32_t v = 0;
-    if (i < n) {
-        k = keys[i];
-        v = info[i];
-        keep = !w_lt(k, lo) && (!has_hi || w_lt(k, hi));
-    }
-    unsigned bal = __ballot_sync(0xffffffffu, keep);
-    if (bal == 0) return;
-    unsigned long long base = 0;
-    if ((threadIdx.x & 31) == 0) base = atomicAdd(d_num, (unsigned long long)__popc(bal));
-    base = __shfl_sync(0xffffffffu, base, 0);
-    if (keep) {
-        uint64_t dst = base + __popc(bal & lanemask_lt());
-        out_keys[dst] = k;
-        out_info[dst] = v;
-    }
-}
-
 }  // namespace
 
 size_t bucket_index_words(Alpha al) {
@@ -640,23 +632,33 @@ void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64
 }
 
 template <typename KeyT>
-void source_prefix_counts(const KeyT *src_fwd, uint64_t d1, Alpha al, uint32_t *per_entry,
-                          cudaStream_t stream, unsigned *launches) {
+static KeyRange<KeyT> make_range(const KeyT *lo, const KeyT *hi) {
+    KeyRange<KeyT> r;
+    r.lo = lo ? *lo : WordTraits<KeyT>::zero();
+    r.hi = hi ? *hi : WordTraits<KeyT>::zero();
+    r.has_lo = lo ? 1 : 0;
+    r.has_hi = hi ? 1 : 0;
+    return r;
+}
+
+template <typename KeyT>
+void source_prefix_counts(const KeyT *src_fwd, uint64_t d1, Alpha al, const KeyT *lo, const KeyT *hi,
+                          uint32_t *per_entry, cudaStream_t stream, unsigned *launches) {
     if (d1 == 0) return;
     source_prefix_counts_kernel<KeyT><<<(unsigned)div_up(d1, (size_t)256), 256, 0, stream>>>(
-        src_fwd, d1, al, per_entry);
+        src_fwd, d1, al, make_range(lo, hi), per_entry);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }
 
 template <typename KeyT>
-void generate_source_dummies(const KeyT *src_fwd, const uint32_t *per_entry, const uint64_t *offsets,
-                             uint64_t d1, Alpha al, KeyT *out_keys, uint32_t *out_info,
+void generate_source_dummies(const KeyT *src_fwd, const uint64_t *offsets, uint64_t d1, Alpha al,
+                             const KeyT *lo, const KeyT *hi, KeyT *out_keys, uint32_t *out_info,
                              unsigned long long *level_hist, cudaStream_t stream,
                              unsigned *launches) {
     if (d1 == 0) return;
     generate_source_dummies_kernel<KeyT><<<(unsigned)div_up(d1, (size_t)128), 128, 0, stream>>>(
-        src_fwd, per_entry, offsets, d1, al, out_keys, out_info, level_hist);
+        src_fwd, offsets, d1, al, make_range(lo, hi), out_keys, out_info, level_hist);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }
@@ -733,18 +735,6 @@ void ranged_dummy_candidates(const KeyT *reals, uint64_t m, const KeyT *targets,
     MTG_CUDA(cudaGetLastError());
 }
 
-template <typename KeyT>
-void filter_key_range(const KeyT *keys, const uint32_t *info, uint64_t n, KeyT lo, KeyT hi, int has_hi,
-                      KeyT *out_keys, uint32_t *out_info, unsigned long long *d_num, cudaStream_t stream,
-                      unsigned *launches) {
-    MTG_CUDA(cudaMemsetAsync(d_num, 0, sizeof(unsigned long long), stream));
-    if (n == 0) return;
-    filter_key_range_kernel<KeyT><<<(unsigned)div_up(n, (size_t)256), 256, 0, stream>>>(
-        keys, info, n, lo, hi, has_hi, out_keys, out_info, d_num);
-    MTG_CUDA(cudaGetLastError());
-    *launches += 1;
-}
-
 // bounds[b] = first position of the sorted array whose value >> shift is >= b, b = 0..2^B
 template <typename KeyT>
 void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, uint64_t *bounds,
@@ -762,10 +752,10 @@ void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, u
     template void find_dummy_candidates<KeyT>(const KeyT *, uint64_t, Alpha, const uint64_t *, void *, KeyT *, uint64_t, \
                                               unsigned long long *, KeyT *, uint64_t,              \
                                               unsigned long long *, cudaStream_t, unsigned *);     \
-    template void source_prefix_counts<KeyT>(const KeyT *, uint64_t, Alpha, uint32_t *,            \
-                                             cudaStream_t, unsigned *);                            \
-    template void generate_source_dummies<KeyT>(const KeyT *, const uint32_t *, const uint64_t *,  \
-                                                uint64_t, Alpha, KeyT *, uint32_t *,               \
+    template void source_prefix_counts<KeyT>(const KeyT *, uint64_t, Alpha, const KeyT *, const KeyT *, \
+                                             uint32_t *, cudaStream_t, unsigned *);                \
+    template void generate_source_dummies<KeyT>(const KeyT *, const uint64_t *, uint64_t, Alpha,   \
+                                                const KeyT *, const KeyT *, KeyT *, uint32_t *,    \
                                                 unsigned long long *, cudaStream_t, unsigned *);   \
     template void dummy_ranks<KeyT>(const KeyT *, uint64_t, const KeyT *, uint64_t, Alpha,         \
                                     const uint64_t *, uint64_t *, cudaStream_t, unsigned *);                         \
@@ -777,9 +767,6 @@ void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, u
                                                 void *, KeyT *, uint64_t,               \
                                                 unsigned long long *, KeyT *, uint64_t,            \
                                                 unsigned long long *, cudaStream_t, unsigned *);   \
-    template void filter_key_range<KeyT>(const KeyT *, const uint32_t *, uint64_t, KeyT, KeyT, int, \
-                                         KeyT *, uint32_t *, unsigned long long *, cudaStream_t,   \
-                                         unsigned *);                                              \
     template void bucket_bounds<KeyT>(const KeyT *, uint64_t, uint32_t, uint32_t, uint64_t *,      \
                                       cudaStream_t, unsigned *);
 INSTANTIATE(uint64_t)

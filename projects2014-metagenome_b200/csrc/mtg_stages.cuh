@@ -89,20 +89,22 @@ void find_dummy_candidates(const KeyT *reals, uint64_t m, Alpha al, const uint64
                            KeyT *src_fwd, uint64_t src_cap, unsigned long long *d_num_src,
                            cudaStream_t stream, unsigned *launches);
 
-// src_fwd sorted ascending (forward-lex). per_entry[i] = K-1-lcp(i, i-1) = number of
-// new distinct prefixes contributed by node i.
+// src_fwd sorted ascending (forward-lex). Node i contributes K-1-lcp(i, i-1) new distinct prefixes =
+// dummy k-mers $^c s_1..s_{K-1-c} -> s_{K-c} (tight word, '$' slots zero, info = c). lo / hi
+// (nullable) restrict them to the key range [lo, hi) of the chunk being built (multi-GPU):
+// per_entry[i] = number of new prefixes of node i inside the range.
 template <typename KeyT>
-void source_prefix_counts(const KeyT *src_fwd, uint64_t d1, Alpha al, uint32_t *per_entry,
-                          cudaStream_t stream, unsigned *launches);
+void source_prefix_counts(const KeyT *src_fwd, uint64_t d1, Alpha al, const KeyT *lo, const KeyT *hi,
+                          uint32_t *per_entry, cudaStream_t stream, unsigned *launches);
 // exclusive scan of uint32 -> uint64 offsets[n+1] (offsets[n] = total)
 void exclusive_scan_u32(const uint32_t *in, uint64_t n, uint64_t *out,
                         unsigned long long *scan_status, unsigned int *tile_counter,
                         cudaStream_t stream, unsigned *launches);
-// Expand every node into its new prefixes: dummy k-mers $^c s_1..s_{K-1-c} -> s_{K-c}
-// (tight word, '$' slots zero) with info = c; level_hist[c-1] += 1.
+// Writes the in-range dummies of node i from offsets[i] on; level_hist[c-1] counts ALL new
+// prefixes (the log line of boss_chunk_construct.cpp:296-302 is global).
 template <typename KeyT>
-void generate_source_dummies(const KeyT *src_fwd, const uint32_t *per_entry, const uint64_t *offsets,
-                             uint64_t d1, Alpha al, KeyT *out_keys, uint32_t *out_info,
+void generate_source_dummies(const KeyT *src_fwd, const uint64_t *offsets, uint64_t d1, Alpha al,
+                             const KeyT *lo, const KeyT *hi, KeyT *out_keys, uint32_t *out_info,
                              unsigned long long *level_hist, cudaStream_t stream,
                              unsigned *launches);
 void fill_u32(uint32_t *p, uint32_t v, uint64_t n, cudaStream_t stream, unsigned *launches);
@@ -134,10 +136,6 @@ void ranged_dummy_candidates(const KeyT *reals, uint64_t m, const KeyT *targets,
                              void *scratch, KeyT *sink_keys, uint64_t sink_cap,
                              unsigned long long *d_num_sink, KeyT *src_fwd, uint64_t src_cap,
                              unsigned long long *d_num_src, cudaStream_t stream, unsigned *launches);
-template <typename KeyT>
-void filter_key_range(const KeyT *keys, const uint32_t *info, uint64_t n, KeyT lo, KeyT hi, int has_hi,
-                      KeyT *out_keys, uint32_t *out_info, unsigned long long *d_num, cudaStream_t stream,
-                      unsigned *launches);
 template <typename KeyT>
 void bucket_bounds(const KeyT *sorted, uint64_t n, uint32_t B, uint32_t shift, uint64_t *bounds,
                    cudaStream_t stream, unsigned *launches);
