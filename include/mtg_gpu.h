@@ -182,6 +182,11 @@ int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, const 
  * [lo_bucket, hi_bucket); first_range adds the all-'$' row (boss_chunk_construct.cpp:310-315). */
 int mtg_mg_build(mtg_ctx *ctx, const void *d_all_src_nodes, uint64_t n_all, uint64_t lo_bucket,
                  uint64_t hi_bucket, int first_range, int device_output, mtg_chunk *out);
+/* The exchange step as one kernel of NVLink peer stores: pushes n_dest byte ranges of this GPU's
+ * memory into peer-mapped destinations (the symmetric receive buffers of the other ranks; the host
+ * side maps them and orders the ranks, multi_gpu.py). Enqueued on cuda_stream of the current device. */
+int mtg_peer_push(void *cuda_stream, uint32_t n_dest, void *const *dst_ptrs, const void *const *src_ptrs,
+                  const uint64_t *nbytes);
 
 /* Device-resident timing of the radix sort alone on n pseudo-random keys of key_bits bits
  * (tuning aid): ms_out[0] = digit-histogram kernel, [1] = mean onesweep pass, [2] = whole sort. */

@@ -240,6 +240,9 @@ class DistBuild:
         import os
         self.use_symm = (os.environ.get("MTG_A2A", "peer") != "nccl" and dist.get_backend(group) == "nccl"
                          and self.world > 1)
+        # MTG_A2A=kernel: the pushes as ONE kernel of peer stores (csrc/mtg_peer.cu) instead of one
+        # copy-engine peer copy per destination (measured at 2 GPUs: 470 vs 661 GB/s, so not the default)
+        self.push_kernel = os.environ.get("MTG_A2A", "peer") == "kernel"
         self._slots = {}
         self._streams = [torch.cuda.Stream(device=self.rank.device) for _ in range(self.world)] if self.use_symm else []
         if self.use_symm:
@@ -294,19 +297,41 @@ class DistBuild:
             cur = torch.cuda.current_stream()
             ev0.record()
             so = np.concatenate([[0], np.cumsum(send_sizes)])
-            for k in range(self.world):
-                d = (self.rank_id + k) % self.world          # staggered: no peer is hit by all at once
-                n_d = int(send_sizes[d])
-                if n_d == 0:
-                    continue
-                off = int(all_sizes[:self.rank_id, d].sum()) * row     # my rows' place in d's buffer
-                dst = hdl.get_buffer(d, (n_d,) + tail, send.dtype, off)
-                st = self._streams[k]
-                st.wait_stream(cur)
-                with torch.cuda.stream(st):
-                    dst.copy_(send[int(so[d]):int(so[d + 1])], non_blocking=True)
-            for st in self._streams:
-                cur.wait_stream(st)
+            esz = send.element_size() * row
+            if self.push_kernel:
+                # one kernel of peer stores (csrc/mtg_peer.cu), every destination served concurrently
+                import ctypes
+                dsts, srcs, nby = [], [], []
+                for k in range(self.world):
+                    d = (self.rank_id + k) % self.world
+                    n_d = int(send_sizes[d])
+                    if n_d == 0:
+                        continue
+                    off = int(all_sizes[:self.rank_id, d].sum()) * esz     # my rows' place in d's buffer
+                    dsts.append(int(hdl.buffer_ptrs[d]) + off)
+                    srcs.append(send.data_ptr() + int(so[d]) * esz)
+                    nby.append(n_d * esz)
+                if dsts:
+                    n = len(dsts)
+                    rc = self.rank.ctor._lib.mtg_peer_push(
+                        ctypes.c_void_p(cur.cuda_stream), n, (ctypes.c_void_p * n)(*dsts),
+                        (ctypes.c_void_p * n)(*srcs), (ctypes.c_uint64 * n)(*nby))
+                    if rc != 0:
+                        raise RuntimeError("mtg_peer_push failed (%d)" % rc)
+            else:
+                for k in range(self.world):
+                    d = (self.rank_id + k) % self.world          # staggered: no peer is hit by all at once
+                    n_d = int(send_sizes[d])
+                    if n_d == 0:
+                        continue
+                    off = int(all_sizes[:self.rank_id, d].sum()) * row     # my rows' place in d's buffer
+                    dst = hdl.get_buffer(d, (n_d,) + tail, send.dtype, off)
+                    st = self._streams[k]
+                    st.wait_stream(cur)
+                    with torch.cuda.stream(st):
+                        dst.copy_(send[int(so[d]):int(so[d + 1])], non_blocking=True)
+                for st in self._streams:
+                    cur.wait_stream(st)
             hdl.barrier()
             ev1.record()
             ev1.synchronize()
@@ -526,7 +551,7 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                    "partitioning": "key range (top 8 bits of the k-mer word); all-to-all of canonical k-mers, "
                                    "of both strands of the distinct k-mers and of target nodes (%s); "
                                    "all-gather of source nodes"
-                                   % ("NVLink peer stores into symmetric memory" if db_use_symm
+                                   % ("NVLink peer copies into symmetric memory" if db_use_symm
                                       else "NCCL all_to_all_single"),
                    "l2_policy": "inputs larger than L2 (%.2f GB of keys per GPU and step)"
                                 % (n_windows * 8 * (2 if wl["canonical"] else 1) / 1e9)},
