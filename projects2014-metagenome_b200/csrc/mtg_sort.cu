@@ -118,288 +118,6 @@ __device__ __forceinline__ unsigned long long lookback_digit(const unsigned long
 }
 
 // ---------------------------------------------------------------------------
-// Kernel S3: one onesweep pass. Tile = THREADS*IPT keys, warp-striped so that
-// (warp, item, lane) order == memory order (stability).
-// ---------------------------------------------------------------------------
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int LB = 1, int MINB = 1, int MODE = 0>
-__global__ void __launch_bounds__(THREADS, MINB)
-onesweep_pass_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out_keys,
-                     const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
-                     uint64_t n, DigitPass dp, const unsigned long long *__restrict__ digit_offsets,
-                     unsigned long long *__restrict__ status, unsigned int *tile_counter,
-                     unsigned epoch) {
-    constexpr int WARPS = THREADS / 32;
-    constexpr int TILE = THREADS * IPT;
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    KeyT *sh_keys = reinterpret_cast<KeyT *>(smem_raw);                       // [TILE]
-    uint32_t *sh_vals = reinterpret_cast<uint32_t *>(sh_keys + TILE);        // [HAS_VAL ? TILE : 0]
-    uint32_t *whist = sh_vals + (HAS_VAL ? TILE : 0);                        // [WARPS][RADIX]
-    long long *goff = reinterpret_cast<long long *>(whist + WARPS * RADIX);  // [RADIX]
-    uint32_t *warp_tot = reinterpret_cast<uint32_t *>(goff + RADIX);         // [WARPS + 1]
-    __shared__ unsigned int sh_tile;
-
-    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) sh_tile = atomicAdd(tile_counter, 1u);
-    for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;
-    __syncthreads();
-    const unsigned tile = sh_tile;
-    const uint64_t tile_base = (uint64_t)tile * TILE;
-    const uint32_t tile_valid = (uint32_t)(n - tile_base < (uint64_t)TILE ? n - tile_base : TILE);
-
-    // ---- load (coalesced, warp-striped) ----
-    KeyT key[IPT];
-    uint32_t val[IPT];
-    uint32_t dig[IPT];
-    const uint32_t warp_base = warp * (IPT * 32);
-#pragma unroll
-    for (int r = 0; r < IPT; ++r) {
-        uint32_t idx = warp_base + r * 32 + lane;
-        if (idx < tile_valid) {
-            key[r] = in_keys[tile_base + idx];
-            val[r] = HAS_VAL ? in_vals[tile_base + idx] : 0;
-            dig[r] = digit_of(key[r], val[r], dp);
-        } else {
-            key[r] = WordTraits<KeyT>::low_mask(WordTraits<KeyT>::BITS);
-            val[r] = 0xffffffffu;
-            dig[r] = RADIX - 1;   // padding sorts to the very end of the tile
-        }
-    }
-
-    // ---- rank inside the warp, running per-warp digit counters ----
-    uint32_t rank[IPT];
-    uint32_t *my_hist = whist + warp * RADIX;
-    if (MODE & 1) {
-        // all MATCH.ANY issued back to back (their ~30-cycle latency overlaps), then the serial
-        // counter chain; rank[] first holds the peer mask
-#pragma unroll
-        for (int r = 0; r < IPT; ++r) rank[r] = __match_any_sync(0xffffffffu, dig[r]);
-#pragma unroll
-        for (int r = 0; r < IPT; ++r) {
-            unsigned peers = rank[r];
-            uint32_t before = my_hist[dig[r]];
-            __syncwarp();
-            if ((peers & lanemask_lt()) == 0) my_hist[dig[r]] = before + __popc(peers);
-            __syncwarp();
-            rank[r] = before + __popc(peers & lanemask_lt());
-        }
-    } else {
-#pragma unroll
-        for (int r = 0; r < IPT; ++r) {
-            unsigned peers = __match_any_sync(0xffffffffu, dig[r]);
-            uint32_t before = my_hist[dig[r]];
-            __syncwarp();
-            if ((peers & lanemask_lt()) == 0) my_hist[dig[r]] = before + __popc(peers);
-            __syncwarp();
-            rank[r] = before + __popc(peers & lanemask_lt());
-        }
-    }
-    __syncthreads();
-
-    // ---- per digit: exclusive prefix over warps, tile count ----
-    uint32_t count = 0;
-    if (tid < RADIX) {
-#pragma unroll
-        for (int w = 0; w < WARPS; ++w) {
-            uint32_t t = whist[w * RADIX + tid];
-            whist[w * RADIX + tid] = count;
-            count += t;
-        }
-        if (tid == RADIX - 1) count -= (TILE - tile_valid);   // drop the padding
-        // publish the tile aggregate early so successors can start looking back
-        if (tile > 0)
-            st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(1, epoch, count));
-    }
-    // exclusive scan of the digit counts inside the tile (first RADIX threads carry data)
-    uint32_t inc = count;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= (unsigned)o) inc += t;
-    }
-    if (lane == 31) warp_tot[warp] = inc;
-    __syncthreads();
-    uint32_t local_base = 0;
-    if (tid < RADIX) {
-        for (unsigned w = 0; w < warp; ++w) local_base += warp_tot[w];
-        local_base += inc - count;
-        goff[tid] = local_base;   // temporarily: local start of the digit
-    }
-    __syncthreads();
-
-    // ---- scatter into shared memory in tile-sorted order ----
-#pragma unroll
-    for (int r = 0; r < IPT; ++r) {
-        uint32_t pos = (uint32_t)goff[dig[r]] + my_hist[dig[r]] + rank[r];
-        sh_keys[pos] = key[r];
-        if (HAS_VAL) sh_vals[pos] = val[r];
-    }
-    __syncthreads();
-
-    // ---- decoupled look-back per digit ----
-    if (tid < RADIX) {
-        // MODE & 2: timing probe without the look-back (wrong output, never dispatched by default)
-        unsigned long long excl = 0;
-        if (MODE & 2) {
-        } else if (LB == 0) {
-            if (tile > 0) {
-                long long t = (long long)tile - 1;
-                while (true) {
-                    unsigned long long s = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
-                    unsigned flag = (unsigned)(s >> 62);
-                    if (flag == 0 || ((s >> 56) & 63) != epoch) continue;   // not published yet
-                    excl += s & OS_VALUE_MASK;
-                    if (flag == 2) break;
-                    --t;
-                }
-            }
-        } else {
-            excl = lookback_digit<(LB > 0 ? LB : 1)>(status, tile, tid, epoch);
-        }
-        st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(2, epoch, excl + count));
-        goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
-    }
-    __syncthreads();
-
-    // ---- coalesced write-out ----
-    for (uint32_t p = tid; p < tile_valid; p += THREADS) {
-        KeyT k = sh_keys[p];
-        uint32_t v = HAS_VAL ? sh_vals[p] : 0;
-        uint32_t d = digit_of(k, v, dp);
-        size_t dst = (size_t)(goff[d] + (long long)p);
-        out_keys[dst] = k;
-        if (HAS_VAL) out_vals[dst] = v;
-    }
-}
-
-// ---------------------------------------------------------------------------
-// Kernel S3 (v2): same contract as onesweep_pass_kernel, restructured after the ncu capture
-// profiles/r01_onesweep_full_v0.txt (27 % of the stall samples in the look-back spin, 37 %
-// occupancy at 80 registers):
-//   * "early counts": the tile's digit histogram is built with shared-memory atomics right
-//     after the load, so the tile aggregate is published before the (expensive) ranking and
-//     successors find it as soon as they look back;
-//   * ranking and the scatter into shared memory are fused (no rank[]/dig[] register arrays);
-//   * the look-back reads a window of LB status words per step (independent loads in flight)
-//     instead of one dependent L2 round trip per predecessor tile.
-// ---------------------------------------------------------------------------
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
-__global__ void __launch_bounds__(THREADS, MINB)
-onesweep_pass_v2_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out_keys,
-                        const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
-                        uint64_t n, DigitPass dp, const unsigned long long *__restrict__ digit_offsets,
-                        unsigned long long *__restrict__ status, unsigned int *tile_counter,
-                        unsigned epoch) {
-    constexpr int WARPS = THREADS / 32;
-    constexpr int TILE = THREADS * IPT;
-    constexpr int DPT = (RADIX + THREADS - 1) / THREADS;   // digits handled per thread (1 if THREADS >= 256)
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    KeyT *sh_keys = reinterpret_cast<KeyT *>(smem_raw);                       // [TILE]
-    uint32_t *sh_vals = reinterpret_cast<uint32_t *>(sh_keys + TILE);        // [HAS_VAL ? TILE : 0]
-    uint32_t *whist = sh_vals + (HAS_VAL ? TILE : 0);                        // [WARPS][RADIX]
-    long long *goff = reinterpret_cast<long long *>(whist + WARPS * RADIX);  // [RADIX]
-    uint32_t *lbase = reinterpret_cast<uint32_t *>(goff + RADIX);            // [RADIX] local digit start
-    uint32_t *warp_tot = lbase + RADIX;                                      // [WARPS + 1]
-    __shared__ unsigned int sh_tile;
-    static_assert(DPT == 1, "v2 assumes THREADS >= RADIX");
-
-    const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    if (tid == 0) sh_tile = atomicAdd(tile_counter, 1u);
-    for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;
-    __syncthreads();
-    const unsigned tile = sh_tile;
-    const uint64_t tile_base = (uint64_t)tile * TILE;
-    const uint32_t tile_valid = (uint32_t)(n - tile_base < (uint64_t)TILE ? n - tile_base : TILE);
-
-    // ---- load (coalesced, warp-striped) + early per-warp digit counts ----
-    KeyT key[IPT];
-    uint32_t val[IPT];
-    uint32_t *my_hist = whist + warp * RADIX;
-    const uint32_t warp_base = warp * (IPT * 32);
-#pragma unroll
-    for (int r = 0; r < IPT; ++r) {
-        uint32_t idx = warp_base + r * 32 + lane;
-        if (idx < tile_valid) {
-            key[r] = in_keys[tile_base + idx];
-            val[r] = HAS_VAL ? in_vals[tile_base + idx] : 0;
-        } else {
-            key[r] = WordTraits<KeyT>::low_mask(WordTraits<KeyT>::BITS);
-            val[r] = 0xffffffffu;
-        }
-    }
-#pragma unroll
-    for (int r = 0; r < IPT; ++r) {
-        uint32_t idx = warp_base + r * 32 + lane;
-        if (idx < tile_valid) atomicAdd(&my_hist[digit_of(key[r], val[r], dp)], 1u);
-    }
-    __syncthreads();
-
-    // ---- per digit: exclusive prefix over warps, tile count, early publish ----
-    uint32_t count = 0;
-    if (tid < RADIX) {
-#pragma unroll
-        for (int w = 0; w < WARPS; ++w) {
-            uint32_t t = whist[w * RADIX + tid];
-            whist[w * RADIX + tid] = count;
-            count += t;
-        }
-        if (tile > 0)
-            st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(1, epoch, count));
-    }
-    uint32_t inc = count;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        uint32_t t = __shfl_up_sync(0xffffffffu, inc, o);
-        if (lane >= (unsigned)o) inc += t;
-    }
-    if (lane == 31) warp_tot[warp] = inc;
-    __syncthreads();
-    uint32_t local_base = 0;
-    if (tid < RADIX) {
-        for (unsigned w = 0; w < warp; ++w) local_base += warp_tot[w];
-        local_base += inc - count;
-        lbase[tid] = local_base;
-    }
-    __syncthreads();
-
-    // ---- rank inside the warp and scatter into shared memory (tile-sorted order) ----
-#pragma unroll
-    for (int r = 0; r < IPT; ++r) {
-        uint32_t idx = warp_base + r * 32 + lane;
-        bool valid = idx < tile_valid;
-        uint32_t d = valid ? digit_of(key[r], val[r], dp) : RADIX;   // padding never matches a digit
-        unsigned peers = __match_any_sync(0xffffffffu, d);
-        if (valid) {
-            uint32_t before = my_hist[d];
-            uint32_t pos = lbase[d] + before + __popc(peers & lanemask_lt());
-            __syncwarp(peers);
-            if ((peers & lanemask_lt()) == 0) my_hist[d] = before + __popc(peers);
-            sh_keys[pos] = key[r];
-            if (HAS_VAL) sh_vals[pos] = val[r];
-        }
-        __syncwarp();
-    }
-
-    // ---- decoupled look-back per digit, LB predecessors per step ----
-    if (tid < RADIX) {
-        unsigned long long excl = lookback_digit<LB>(status, tile, tid, epoch);
-        st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(2, epoch, excl + count));
-        goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
-    }
-    __syncthreads();
-
-    // ---- coalesced write-out ----
-#pragma unroll 4
-    for (uint32_t p = tid; p < tile_valid; p += THREADS) {
-        KeyT k = sh_keys[p];
-        uint32_t v = HAS_VAL ? sh_vals[p] : 0;
-        uint32_t d = digit_of(k, v, dp);
-        size_t dst = (size_t)(goff[d] + (long long)p);
-        out_keys[dst] = k;
-        if (HAS_VAL) out_vals[dst] = v;
-    }
-}
-
-// ---------------------------------------------------------------------------
 // Kernel S3 (v3): MATCH-free onesweep pass.
 // Measured on B200 (scripts/micro/match_bench.cu): MATCH.ANY sustains one warp-instruction per
 // ~62 cycles per SM, 8 ballots ~28 cycles, a shared-memory atomic (random bank, with or without
@@ -746,7 +464,7 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
                                                                       dp, offs, status, ctr, epoch);
 }
 
-// variant selection (experiments): MTG_SORT_VARIANT = 0 (v1), 1.. (v2 configurations)
+// variant selection (experiments): MTG_SORT_VARIANT, see the switch in radix_sort_impl
 static int sort_variant() {
     static int v = -1;
     if (v < 0) {
@@ -756,31 +474,12 @@ static int sort_variant() {
     return v;
 }
 
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
-void launch_v2(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
-               uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
-               unsigned int *ctr, unsigned epoch, cudaStream_t stream) {
-    constexpr int TILE = THREADS * IPT;
-    size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
-                  + sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
-                  + sizeof(uint32_t) * RADIX + sizeof(uint32_t) * (THREADS / 32 + 1);
-    auto kern = onesweep_pass_v2_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB, LB>;
-    static bool attr_set = false;
-    if (!attr_set) {
-        MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
-    }
-    kern<<<(unsigned)div_up(n, (size_t)TILE), THREADS, smem, stream>>>(in_keys, out_keys, in_vals, out_vals, n,
-                                                                      dp, offs, status, ctr, epoch);
-}
-
 // (THREADS, IPT) per variant; tile = THREADS * IPT keys
 template <typename KeyT>
 static int variant_tile(int v) {
     constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;   // u128 tiles hold half the keys
     switch (v) {
-        case 5: case 22: case 31: case 33: return 8192 / S;
-        case 6: return 2048 / S;
+        case 22: case 31: case 33: return 8192 / S;
         default: return 4096 / S;
     }
 }
@@ -788,7 +487,6 @@ static int variant_tile(int v) {
 template <typename KeyT, bool HAS_VAL>
 int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan &plan,
                     SortWorkspace &ws, cudaStream_t stream, unsigned *launches) {
-    constexpr int THREADS = SortTile<KeyT>::THREADS, IPT = SortTile<KeyT>::IPT;
     constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;
     if (n == 0 || plan.n == 0) return 0;
     const int variant = sort_variant();
@@ -813,9 +511,6 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         sort_scan_hist_kernel<<<plan.n, RADIX, 0, stream>>>(ws.hist);
         *launches += 2;
     }
-    size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
-                  + sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
-                  + sizeof(uint32_t) * (THREADS / 32 + 1);
     int cur = 0;
     for (int p = 0; p < plan.n; ++p) {
         if (ws.events) cudaEventRecord(ws.events[2 * p], stream);
@@ -826,52 +521,20 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         const unsigned long long *offs = ws.hist + (size_t)p * RADIX;
         unsigned int *ctr = ws.tile_counters + p;
         const unsigned ep = (unsigned)(p + 1);
-#define V1(LBW, B, ...)                                                                              \
-    do {                                                                                             \
-        auto k1 = onesweep_pass_kernel<KeyT, HAS_VAL, THREADS, IPT, LBW, B, ##__VA_ARGS__>;          \
-        static bool attr_done = false;                                                               \
-        if (!attr_done) {                                                                            \
-            MTG_CUDA(cudaFuncSetAttribute(k1, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
-            attr_done = true;                                                                        \
-        }                                                                                            \
-        k1<<<(unsigned)tiles, THREADS, smem, stream>>>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, \
-                                                      ctr, ep);                                      \
-    } while (0)
 #define V3(T, I, B, LBW) launch_v3<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
 #define V4(T, I, B, LBW) launch_v4<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
-#define V2(T, I, B, LBW) launch_v2<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
-        switch (variant) {
-            case 1: V1(4, 1); break;
-            case 20: V3(256, 16, 3, 0); break;
-            case 30: V4(256, 16, 3, 0); break;
-            case 31: V4(512, 16, 2, 0); break;
-            case 32: V4(256, 16, 3, 4); break;
-            case 33: V4(512, 16, 2, 4); break;
-            case 34: V4(256, 16, 4, 0); break;
-            case 21: V3(256, 16, 4, 0); break;
-            case 22: V3(512, 16, 2, 0); break;
-            case 25: V3(256, 16, 3, 4); break;
+        switch (variant) {   // measured alternatives (scripts/sort_bench.py); 20 is the default
+            case 21: V3(256, 16, 4, 0); break;    // 4 blocks per SM
+            case 22: V3(512, 16, 2, 0); break;    // 8192-key tiles
+            case 25: V3(256, 16, 3, 4); break;    // look-back windows of 4 / 8 / 16 / 2 predecessors
             case 26: V3(256, 16, 3, 8); break;
             case 27: V3(256, 16, 3, 16); break;
             case 28: V3(256, 16, 3, 2); break;
-            case 8: V1(1, 3); break;
-            case 14: V1(0, 3); break;
-            case 15: V1(0, 3, 1); break;
-            case 9: V1(4, 3); break;
-            case 10: V1(1, 3, 2); break;
-            case 11: V1(1, 3, 1); break;
-            case 12: V1(1, 3, 3); break;
-            case 13: V1(1, 4, 1); break;
-            case 2: V1(4, 4); break;
-            case 3: V1(1, 4); break;
-            case 4: V2(256, 16, 3, 1); break;
-            case 7: V2(256, 16, 3, 4); break;
-            case 5: V2(512, 16, 2, 4); break;
-            case 6: V2(256, 8, 6, 4); break;
-            default: V1(1, 1); break;
+            case 30: V4(256, 16, 3, 0); break;    // ballot-ranked
+            case 31: V4(512, 16, 2, 0); break;
+            case 33: V4(512, 16, 2, 4); break;
+            default: V3(256, 16, 3, 0); break;
         }
-#undef V1
-#undef V2
 #undef V3
 #undef V4
         if (ws.events) cudaEventRecord(ws.events[2 * p + 1], stream);

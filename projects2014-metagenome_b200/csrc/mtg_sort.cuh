@@ -40,10 +40,6 @@ struct SortWorkspace {
     cudaEvent_t *events = nullptr;
 };
 
-template <typename KeyT> struct SortTile;
-template <> struct SortTile<uint64_t> { static constexpr int THREADS = 256, IPT = 16; };
-template <> struct SortTile<u128> { static constexpr int THREADS = 256, IPT = 8; };
-
 size_t sort_tile_keys(bool wide);
 // test/bench helper: pseudo-random words (top word of every key masked with hi_mask)
 void fill_random_words(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask, bool wide,

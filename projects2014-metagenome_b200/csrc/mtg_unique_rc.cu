@@ -102,7 +102,7 @@ constexpr int UB_THREADS = 256;
 
 // Tiles are numbered by blockIdx.x (blocks of a 1-D grid are dispatched in index order, which is
 // what the look-back needs), so the bulk load is issued by the first instruction of the block.
-template <typename KeyT, int UB_TILE_BYTES, int PROBE = 0>   // PROBE: timing experiments only (wrong output)
+template <typename KeyT, int UB_TILE_BYTES>
 __global__ void __launch_bounds__(UB_THREADS)
 unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_keys,
                    uint64_t *__restrict__ out_starts, unsigned long long *d_num_out,
@@ -147,10 +147,9 @@ unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__
     }
     __syncthreads();
     const uint32_t tile_total = warp_cnt[WARPS];
-    const uint64_t tile_excl = PROBE == 1 ? (uint64_t)tile * (TILE / 4) : lookback_exclusive(status, tile, tile_total, &slot);
+    const uint64_t tile_excl = lookback_exclusive(status, tile, tile_total, &slot);
     uint64_t pos = tile_excl + warp_cnt[warp];
     const unsigned lt = lanemask_lt();
-    if (PROBE == 2) return;
 #pragma unroll 8
     for (int r = 0; r < ROWS; ++r) {
         const uint32_t idx = wbase + r * 32 + lane;
@@ -328,8 +327,6 @@ void unique_keys(const KeyT *keys, uint64_t n, KeyT *out_keys, uint64_t *out_sta
                 keys, n, out_keys, out_starts, d_num_out, scan_status, tile_counter);
         };
         if (tile_kb >= 64) launch(unique_bulk_kernel<KeyT, 64 * 1024>, 64 * 1024);
-        else if (getenv("MTG_UQ_PROBE") && atoi(getenv("MTG_UQ_PROBE")) == 1) launch(unique_bulk_kernel<KeyT, 32 * 1024, 1>, 32 * 1024);
-        else if (getenv("MTG_UQ_PROBE") && atoi(getenv("MTG_UQ_PROBE")) == 2) launch(unique_bulk_kernel<KeyT, 32 * 1024, 2>, 32 * 1024);
         else if (tile_kb >= 32) launch(unique_bulk_kernel<KeyT, 32 * 1024>, 32 * 1024);
         else launch(unique_bulk_kernel<KeyT, 16 * 1024>, 16 * 1024);
         MTG_CUDA(cudaGetLastError());
