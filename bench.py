@@ -317,7 +317,7 @@ def run_ours(args, wl):
 
         def step_host():
             ctor2.add_packed(bases, offsets)
-            return ctor2.build_chunk()
+            return ctor2.build_chunk(copy=False)   # W / last / F in the pinned host buffer of the C ABI
 
         chunk = step_host()   # warm-up (pinned staging, pools)
         torch.cuda.synchronize()

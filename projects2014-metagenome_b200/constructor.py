@@ -10,6 +10,7 @@ Names, argument meaning and error behaviour follow the reference (errors that th
 reference reports with logger->error + exit(1) are raised as MtgError).
 """
 import ctypes
+import weakref
 
 import numpy as np
 
@@ -243,24 +244,21 @@ class BOSSChunkConstructor:
         finally:
             self._lib.mtg_free_chunk(ctypes.byref(c))
 
-    def build_chunk(self):
+    def build_chunk(self, copy=True):
+        """BOSS::Chunk of everything pushed so far. copy=False leaves W / last / weights in the
+        library's pinned result buffer (what the C ABI hands out): the arrays are views that stay
+        valid as long as the returned Chunk object is alive."""
         c = MtgChunk()
         self._check(self._lib.mtg_build_chunk(self._ctx, ctypes.byref(c)))
-        try:
-            n = c.n_rows
-            nW = (n * c.W_width + 63) // 64
-            nl = (n + 63) // 64
-            W = np.ctypeslib.as_array(c.W, (nW,)).copy()
-            last = np.ctypeslib.as_array(c.last, (nl,)).copy()
-            wts = None
-            if c.weights_width:
-                nw = (n * c.weights_width + 63) // 64
-                wts = np.ctypeslib.as_array(c.weights, (nw,)).copy()
-            F = np.array(c.F[: c.sigma], dtype=np.uint64)
-            stats = self._stats(c)
-            return Chunk(c.sigma, c.k, n, W, last, F, c.W_width, wts, c.weights_width, stats)
-        finally:
-            self._lib.mtg_free_chunk(ctypes.byref(c))
+        if copy:
+            try:
+                return self._chunk_from(c)
+            finally:
+                self._lib.mtg_free_chunk(ctypes.byref(c))
+        chunk = self._chunk_from(c, copy=False)
+        lib = self._lib
+        weakref.finalize(chunk, lambda: lib.mtg_free_chunk(ctypes.byref(c)))
+        return chunk
 
     # ---- range-partitioned (multi-GPU) phases, include/mtg_gpu.h mtg_mg_* ----------------
     def mg_part_bits(self):
@@ -330,16 +328,17 @@ class BOSSChunkConstructor:
         finally:
             self._lib.mtg_free_chunk(ctypes.byref(c))
 
-    def _chunk_from(self, c):
+    def _chunk_from(self, c, copy=True):
         n = c.n_rows
         nW = (n * c.W_width + 63) // 64
         nl = (n + 63) // 64
-        W = np.ctypeslib.as_array(c.W, (nW,)).copy()
-        last = np.ctypeslib.as_array(c.last, (nl,)).copy()
+        take = (lambda a: a.copy()) if copy else (lambda a: a)
+        W = take(np.ctypeslib.as_array(c.W, (nW,)))
+        last = take(np.ctypeslib.as_array(c.last, (nl,)))
         wts = None
         if c.weights_width:
             nw = (n * c.weights_width + 63) // 64
-            wts = np.ctypeslib.as_array(c.weights, (nw,)).copy()
+            wts = take(np.ctypeslib.as_array(c.weights, (nw,)))
         F = np.array(c.F[: c.sigma], dtype=np.uint64)
         return Chunk(c.sigma, c.k, n, W, last, F, c.W_width, wts, c.weights_width, self._stats(c))
 

@@ -296,6 +296,21 @@ void pack_parallel(const char *bases, const uint64_t *offsets, size_t r0, size_t
     for (auto &t : th) t.join();
 }
 
+// multi-threaded memcpy (staging of pageable caller memory)
+void copy_parallel(char *dst, const char *src, size_t bytes) {
+    unsigned nt = (unsigned)std::min<size_t>(std::max<size_t>(bytes >> 22, 1),
+                                             std::min(16u, std::max(1u, std::thread::hardware_concurrency())));
+    if (nt <= 1) { memcpy(dst, src, bytes); return; }
+    std::vector<std::thread> th;
+    size_t per = ((bytes + nt - 1) / nt + 63) & ~(size_t)63;
+    for (unsigned t = 0; t < nt; ++t) {
+        size_t a = (size_t)t * per, b = std::min(bytes, a + per);
+        if (a >= b) break;
+        th.emplace_back([=]() { memcpy(dst + a, src + a, b - a); });
+    }
+    for (auto &t : th) t.join();
+}
+
 }  // namespace
 
 extern "C" {
@@ -405,8 +420,14 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
     try {
         MTG_CUDA(cudaSetDevice(ctx->device));
         t_arena = ctx->arena;
-        // split very large pushes so that packing and H2D overlap
-        const size_t CHUNK = (size_t)64 << 20;
+        // The reads go up raw (as the caller holds them: concatenated bases + offsets) and are
+        // brought into the packed layout by a kernel. Pinned caller memory is copied from directly
+        // (the call returns after the copies: the caller's buffers are free again); pageable memory
+        // is staged through pinned buffers in <= 64 MB pieces so that staging and H2D overlap.
+        cudaPointerAttributes attr;
+        const bool pinned_src = cudaPointerGetAttributes(&attr, bases) == cudaSuccess && attr.type == cudaMemoryTypeHost;
+        cudaGetLastError();
+        const size_t CHUNK = pinned_src ? (size_t)1 << 30 : (size_t)64 << 20;
         size_t r0 = 0;
         while (r0 < n_reads) {
             size_t r1 = r0;
@@ -418,10 +439,12 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
                 if (len >= K) nwin += len - K + 1;
                 ++r1;
             }
-            size_t padded = (bytes + 15) & ~(size_t)15;
+            const size_t nr = r1 - r0;
+            const size_t raw_bytes = offsets[r1] - offsets[r0];
+            const size_t padded = (bytes + 15) & ~(size_t)15;
             const bool want_starts = ctx->prm.bits_per_count > 0;
-            size_t nr = r1 - r0;
-            size_t stage_bytes = padded + (want_starts ? nr * 8 + 16 : 0) + (counts ? nr * 4 + 16 : 0);
+            const size_t off_bytes = (nr + 1) * 8, cnt_bytes = counts ? nr * 4 : 0;
+            const size_t stage_bytes = (pinned_src ? 0 : ((raw_bytes + 15) & ~(size_t)15)) + off_bytes + cnt_bytes + 16;
             PinnedBuf *pb;
             ReadSegment seg;
             {
@@ -429,44 +452,49 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
                 pb = get_pinned(ctx, stage_bytes);
             }
             char *h = (char *)pb->p;
-            pack_parallel(bases, offsets, r0, r1, h);
-            memset(h + bytes, 0, padded - bytes);
-            uint64_t *h_starts = (uint64_t *)(h + padded);
-            uint32_t *h_counts = (uint32_t *)(h + padded + (want_starts ? nr * 8 + 16 : 0));
-            if (want_starts) {
-                uint64_t pos = 0;
-                for (size_t r = r0; r < r1; ++r) {
-                    h_starts[r - r0] = pos;
-                    pos += offsets[r + 1] - offsets[r] + 1;
-                }
+            char *h_raw = h;
+            if (!pinned_src) {
+                copy_parallel(h, bases + offsets[r0], raw_bytes);
+                h += (raw_bytes + 15) & ~(size_t)15;
             }
+            uint64_t *h_off = (uint64_t *)h;
+            memcpy(h_off, offsets + r0, off_bytes);
+            uint32_t *h_counts = (uint32_t *)(h + off_bytes);
             if (counts)
                 for (size_t r = r0; r < r1; ++r)   // kmer_collector.cpp:92
                     h_counts[r - r0] = (uint32_t)std::min<uint64_t>(counts[r], ctx->cmax);
             {
                 std::lock_guard<std::mutex> lk(ctx->mu);
-                seg.own_packed.alloc(padded, ctx->stream);
-                MTG_CUDA(cudaMemcpyAsync(seg.own_packed.p, h, padded, cudaMemcpyHostToDevice, ctx->stream));
+                cudaStream_t s = ctx->stream;
+                DevBuf d_raw(std::max<size_t>(raw_bytes, 16), s), d_off(off_bytes, s);
+                seg.own_packed.alloc(padded, s);
+                MTG_CUDA(cudaMemcpyAsync(d_raw.p, pinned_src ? bases + offsets[r0] : h_raw, raw_bytes,
+                                         cudaMemcpyHostToDevice, s));
+                MTG_CUDA(cudaMemcpyAsync(d_off.p, h_off, off_bytes, cudaMemcpyHostToDevice, s));
                 if (want_starts) {
-                    seg.starts.alloc(nr * 8, ctx->stream);
-                    MTG_CUDA(cudaMemcpyAsync(seg.starts.p, h_starts, nr * 8, cudaMemcpyHostToDevice, ctx->stream));
+                    seg.starts.alloc(nr * 8, s);
                     seg.has_starts = true;
                 }
                 if (counts) {
-                    seg.counts.alloc(nr * 4, ctx->stream);
-                    MTG_CUDA(cudaMemcpyAsync(seg.counts.p, h_counts, nr * 4, cudaMemcpyHostToDevice, ctx->stream));
+                    seg.counts.alloc(nr * 4, s);
+                    MTG_CUDA(cudaMemcpyAsync(seg.counts.p, h_counts, nr * 4, cudaMemcpyHostToDevice, s));
                     seg.has_counts = true;
                     ctx->any_explicit_counts = true;
                 }
-                MTG_CUDA(cudaEventRecord(pb->ev, ctx->stream));
+                pack_reads_device(d_raw.as<uint8_t>(), d_off.as<uint64_t>(), nr, seg.own_packed.as<uint8_t>(), padded,
+                                  want_starts ? seg.starts.as<uint64_t>() : nullptr, s);
+                ctx->launches += 1;
+                MTG_CUDA(cudaEventRecord(pb->ev, s));
                 seg.d_packed = seg.own_packed.as<uint8_t>();
                 seg.nbytes = padded;
                 seg.n_windows_max = nwin;
                 seg.n_reads = nr;
                 ctx->segs.push_back(std::move(seg));
+                // d_raw / d_off go back to the arena here: all work of the context is ordered on s
             }
             r0 = r1;
         }
+        if (pinned_src) MTG_CUDA(cudaStreamSynchronize(ctx->stream));   // the caller's memory is free again
     } catch (const CudaError &e) {
         return fail_cuda(ctx, e);
     }

@@ -213,6 +213,42 @@ void launch_extract(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream) {
 
 }  // namespace
 
+namespace {
+// Raw concatenated reads + offsets -> packed layout (read r at raw offset o_r - o_0 moves to
+// o_r - o_0 + r, followed by its 0x00 separator). One warp per read, 32 consecutive bytes per step.
+__global__ void __launch_bounds__(256)
+pack_reads_kernel(const uint8_t *__restrict__ raw, const uint64_t *__restrict__ offsets, uint64_t n_reads,
+                  uint8_t *__restrict__ packed, uint64_t packed_bytes, uint64_t *__restrict__ starts) {
+    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const unsigned lane = threadIdx.x & 31;
+    const uint64_t nwarps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+    const uint64_t o0 = offsets[0];
+    for (uint64_t r = warp; r < n_reads; r += nwarps) {
+        const uint64_t a = offsets[r] - o0, b = offsets[r + 1] - o0;
+        uint8_t *dst = packed + a + r;
+        for (uint64_t i = a + lane; i < b; i += 32) dst[i - a] = raw[i];
+        if (lane == 0) {
+            dst[b - a] = 0;
+            if (starts) starts[r] = a + r;
+        }
+    }
+    // zero the alignment tail
+    if (blockIdx.x == 0 && threadIdx.x < 16) {
+        const uint64_t end = offsets[n_reads] - o0 + n_reads;
+        if (end + threadIdx.x < packed_bytes) packed[end + threadIdx.x] = 0;
+    }
+}
+}  // namespace
+
+void pack_reads_device(const uint8_t *raw, const uint64_t *offsets, uint64_t n_reads, uint8_t *packed,
+                       uint64_t packed_bytes, uint64_t *starts, cudaStream_t stream) {
+    if (n_reads == 0) return;
+    const uint64_t want = div_up(n_reads * 32, (size_t)256);
+    const unsigned grid = (unsigned)(want < 148 * 32 ? want : 148 * 32);
+    pack_reads_kernel<<<grid, 256, 0, stream>>>(raw, offsets, n_reads, packed, packed_bytes, starts);
+    MTG_CUDA(cudaGetLastError());
+}
+
 template <typename KeyT>
 void extract_kmers(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream) {
     if (a.nbytes == 0) return;

@@ -26,6 +26,10 @@ struct ExtractArgs {
 };
 template <typename KeyT>
 void extract_kmers(const ExtractArgs &a, KeyT *out_keys, cudaStream_t stream);
+// raw concatenated reads + offsets[n_reads + 1] (device) -> packed layout; starts (nullable) = packed
+// start of each read
+void pack_reads_device(const uint8_t *raw, const uint64_t *offsets, uint64_t n_reads, uint8_t *packed,
+                       uint64_t packed_bytes, uint64_t *starts, cudaStream_t stream);
 
 // Row descriptor byte for dummy k-mers / merged rows:
 //   bits 0..6  number of leading '$' in the node (dummy prefix length), 0 for real
