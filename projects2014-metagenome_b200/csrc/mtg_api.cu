@@ -296,6 +296,33 @@ void pack_parallel(const char *bases, const uint64_t *offsets, size_t r0, size_t
     for (auto &t : th) t.join();
 }
 
+// number of K-windows of reads [r0, r1): sum of max(0, len - K + 1), multi-threaded for big pushes
+uint64_t count_windows(const uint64_t *offsets, size_t r0, size_t r1, uint32_t K) {
+    auto part = [&](size_t a, size_t b) {
+        uint64_t n = 0;
+        for (size_t r = a; r < b; ++r) {
+            const uint64_t len = offsets[r + 1] - offsets[r];
+            if (len >= K) n += len - K + 1;
+        }
+        return n;
+    };
+    const size_t nr = r1 - r0;
+    unsigned nt = (unsigned)std::min<size_t>(nr >> 18, std::min(16u, std::max(1u, std::thread::hardware_concurrency())));
+    if (nt <= 1) return part(r0, r1);
+    std::vector<uint64_t> sums(nt, 0);
+    std::vector<std::thread> th;
+    const size_t per = (nr + nt - 1) / nt;
+    for (unsigned t = 0; t < nt; ++t) {
+        const size_t a = r0 + t * per, b = std::min(r1, a + per);
+        if (a >= b) break;
+        th.emplace_back([&, t, a, b]() { sums[t] = part(a, b); });
+    }
+    for (auto &x : th) x.join();
+    uint64_t n = 0;
+    for (uint64_t v : sums) n += v;
+    return n;
+}
+
 // multi-threaded memcpy (staging of pageable caller memory)
 void copy_parallel(char *dst, const char *src, size_t bytes) {
     unsigned nt = (unsigned)std::min<size_t>(std::max<size_t>(bytes >> 22, 1),
@@ -430,15 +457,15 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
         const size_t CHUNK = pinned_src ? (size_t)1 << 30 : (size_t)64 << 20;
         size_t r0 = 0;
         while (r0 < n_reads) {
-            size_t r1 = r0;
-            size_t bytes = 0;
-            uint64_t nwin = 0;
-            while (r1 < n_reads && (bytes < CHUNK)) {
-                size_t len = offsets[r1 + 1] - offsets[r1];
-                bytes += len + 1;
-                if (len >= K) nwin += len - K + 1;
-                ++r1;
+            // segment end: first r1 with packed size (raw bytes + one separator per read) >= CHUNK
+            size_t lo = r0 + 1, hi = n_reads;
+            while (lo < hi) {
+                size_t mid = (lo + hi) >> 1;
+                if ((offsets[mid] - offsets[r0]) + (mid - r0) >= CHUNK) hi = mid; else lo = mid + 1;
             }
+            const size_t r1 = lo;
+            const size_t bytes = (offsets[r1] - offsets[r0]) + (r1 - r0);
+            const uint64_t nwin = count_windows(offsets, r0, r1, K);
             const size_t nr = r1 - r0;
             const size_t raw_bytes = offsets[r1] - offsets[r0];
             const size_t padded = (bytes + 15) & ~(size_t)15;
@@ -458,7 +485,7 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
                 h += (raw_bytes + 15) & ~(size_t)15;
             }
             uint64_t *h_off = (uint64_t *)h;
-            memcpy(h_off, offsets + r0, off_bytes);
+            copy_parallel((char *)h_off, (const char *)(offsets + r0), off_bytes);
             uint32_t *h_counts = (uint32_t *)(h + off_bytes);
             if (counts)
                 for (size_t r = r0; r < r1; ++r)   // kmer_collector.cpp:92

@@ -272,3 +272,33 @@ def test_suffix_rejects_bad_arguments():
         mtg_b200.BOSSChunkConstructor.initialize(4, filter_suffix="ACGTA")   # not shorter than k + 1
     with pytest.raises(mtg_b200.MtgError):
         mtg_b200.BOSSChunkConstructor.initialize(10, filter_suffix="AN")     # outside the alphabet
+
+
+# ---- the reference binary itself, at a size well above the golden fixtures -----------------
+
+@pytest.mark.parametrize("n_reads,K,canonical,bpc", [(200_000, 31, True, 8), (60_000, 31, False, 0),
+                                                     (40_000, 63, True, 0)])
+def test_chunk_files_equal_reference_binary(n_reads, K, canonical, bpc, tmp_path):
+    """Files written from the GPU chunk == files the reference's own code writes for the same
+    reads (oracle/_ref/ref_driver_DNA: the unmodified BOSSChunkConstructor + Chunk::serialize,
+    compiled by oracle/build_ref.sh; it travels to the GPU box prebuilt)."""
+    import subprocess
+    drv = oracle_lib.ref_driver("DNA")
+    if not drv:
+        pytest.skip("oracle/_ref not built")
+    packed = synth.dna_reads_packed_np(1234 + K, n_reads, 150, 2_000_000, 0.01)
+    reads = synth.packed_to_strings(packed)
+    src = tmp_path / "reads.txt"
+    src.write_text("\n".join(reads) + "\n")
+    cmd = [drv, "-k", str(K), "-p", "8", "-o", str(tmp_path / "ref"), str(src)]
+    if canonical:
+        cmd.append("--canonical")
+    if bpc:
+        cmd += ["--count-width", str(bpc)]
+    subprocess.check_call(cmd, stdout=subprocess.DEVNULL)
+    chunk = gpu_build(reads, K, "DNA", canonical, bpc)
+    chunk.serialize(str(tmp_path / "gpu"))
+    for ext in ("", ".W", ".last", ".weights"):
+        a = (tmp_path / ("ref.dbg.chunk" + ext)).read_bytes()
+        b = (tmp_path / ("gpu.dbg.chunk" + ext)).read_bytes()
+        assert a == b, "chunk file %r differs from the reference's" % ext
