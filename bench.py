@@ -315,13 +315,22 @@ def run_ours(args, wl):
         offsets = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(L)
         ctor2 = mtg_b200.BOSSChunkConstructor.initialize(K - 1, wl["canonical"], wl["bpc"], device=local)
 
+        host_ms = {"push": 0.0, "build": 0.0}
+
         def step_host():
+            ta = time.perf_counter()
             ctor2.add_packed(bases, offsets)
-            return ctor2.build_chunk(copy=False)   # W / last / F in the pinned host buffer of the C ABI
+            tb = time.perf_counter()
+            c = ctor2.build_chunk(copy=False)   # W / last / F in the pinned host buffer of the C ABI
+            host_ms["push"] += 1e3 * (tb - ta)
+            host_ms["build"] += 1e3 * (time.perf_counter() - tb)
+            return c
 
         chunk = step_host()   # warm-up (pinned staging, pools)
+        chunk = step_host()   # second result buffer: the previous chunk is alive while the next is built
         torch.cuda.synchronize()
         e_steps = max(1, min(args.steps, 3))
+        host_ms["push"] = host_ms["build"] = 0.0
         t0 = time.perf_counter()
         for _ in range(e_steps):
             chunk = step_host()
@@ -331,6 +340,8 @@ def run_ours(args, wl):
                "h2d_bytes_per_step": int(n_reads * (L + 1)),
                "d2h_bytes_per_step": int(chunk.stats["chunk_bytes"]),
                "ms_per_step": 1e3 * dt / e_steps, "steps": e_steps,
+               "push_ms": host_ms["push"] / e_steps, "build_ms": host_ms["build"] / e_steps,
+               "build_device_ms": float(chunk.stats["ms_total"]) if "ms_total" in chunk.stats else None,
                "api": "mtg_push_reads(host bases+offsets) + mtg_build_chunk (host W/last/F)"}
         ctor2.close()
         del host
