@@ -8,6 +8,7 @@
 #include <deque>
 #include <map>
 #include <memory>
+#include <functional>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -823,8 +824,11 @@ void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64
 }
 
 // rows -> W / last / F / weights (K6) -> mtg_chunk (pinned host copy or device-resident)
+// launches the kernels that write W / last / weights / F (device pointers) of an E-row chunk
+using EmitFn = std::function<void(uint64_t *, uint64_t *, uint64_t *, unsigned long long *)>;
+
 template <typename KeyT>
-void emit_deliver(mtg_ctx *ctx, DevBuf &row_keys, DevBuf &row_info, DevBuf *row_counts, uint64_t E,
+void emit_deliver(mtg_ctx *ctx, const EmitFn &emit, uint64_t E,
                   const unsigned long long *d_levels, Timer &tm, SortProfile &prof, mtg_chunk *out,
                   bool device_output, uint64_t n_input, uint64_t n_real, uint64_t n_sink) {
     cudaStream_t s = ctx->stream;
@@ -837,9 +841,7 @@ void emit_deliver(mtg_ctx *ctx, DevBuf &row_keys, DevBuf &row_info, DevBuf *row_
     DevBuf outbuf(8 * (W_words + last_words + wt_words + MTG_MAX_SIGMA), s);
     uint64_t *dW = outbuf.as<uint64_t>(), *dLast = dW + W_words, *dWt = dLast + last_words;
     unsigned long long *dF = (unsigned long long *)(dWt + wt_words);
-    emit_chunk<KeyT>(row_keys.as<KeyT>(), row_info.as<uint8_t>(),
-                     row_counts ? row_counts->as<uint32_t>() : nullptr, E, al, ww, dW, dLast,
-                     counting ? dWt : nullptr, dF, s, &ctx->launches);
+    emit(dW, dLast, counting ? dWt : nullptr, dF);
     tm.mark();   // 6: emit done
 
     // ---- results to pinned host memory ----
@@ -936,6 +938,17 @@ void finish_chunk(mtg_ctx *ctx, RealSet &rs, DevBuf &dk0, DevBuf &di0, uint64_t 
 
     // ---- merge + emit ----
     const uint64_t E = m + d + row_off;
+    const uint32_t ww = ctx->prm.bits_per_count;
+    if (L == 2 && al.W_width == 4 && !getenv("MTG_EMIT_UNFUSED")) {
+        // DNA: one kernel merges and emits out of shared memory, the rows are never written to HBM
+        DevBuf part(8 * emit_merged_scratch_words(E), s);
+        const uint32_t *rc = counting ? rs.counts.as<uint32_t>() : nullptr;
+        emit_deliver<KeyT>(ctx, [&](uint64_t *dW, uint64_t *dLast, uint64_t *dWt, unsigned long long *dF) {
+            emit_merged<KeyT>(reals, rc, m, dk0.as<KeyT>(), di0.as<uint32_t>(), rank.as<uint64_t>(), d, row_off,
+                              al, ww, part.as<uint64_t>(), dW, dLast, dWt, dF, s, &ctx->launches);
+        }, E, d_ctr + 8, tm, prof, out, device_output, rs.n_input, m, n_sink);
+        return;
+    }
     DevBuf row_keys(sizeof(KeyT) * E, s), row_info(E, s), row_counts;
     if (counting) row_counts.alloc(4 * E, s);
     merge_rows<KeyT>(reals, counting ? rs.counts.as<uint32_t>() : nullptr, m, dk0.as<KeyT>(),
@@ -943,8 +956,10 @@ void finish_chunk(mtg_ctx *ctx, RealSet &rs, DevBuf &dk0, DevBuf &di0, uint64_t 
                      row_info.as<uint8_t>(), counting ? row_counts.as<uint32_t>() : nullptr, s,
                      &ctx->launches, row_off);
     rs.keys.release(); rs.counts.release(); dk0.release(); di0.release(); rank.release();
-    emit_deliver<KeyT>(ctx, row_keys, row_info, counting ? &row_counts : nullptr, E, d_ctr + 8, tm, prof, out,
-                       device_output, rs.n_input, m, n_sink);
+    emit_deliver<KeyT>(ctx, [&](uint64_t *dW, uint64_t *dLast, uint64_t *dWt, unsigned long long *dF) {
+        emit_chunk<KeyT>(row_keys.as<KeyT>(), row_info.as<uint8_t>(), counting ? row_counts.as<uint32_t>() : nullptr,
+                         E, al, ww, dW, dLast, dWt, dF, s, &ctx->launches);
+    }, E, d_ctr + 8, tm, prof, out, device_output, rs.n_input, m, n_sink);
 }
 
 template <typename KeyT>
@@ -1112,8 +1127,11 @@ void build_suffix_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
                       counting ? row_counts.as<uint32_t>() : nullptr, s, &ctx->launches);
     keysB.release(); counts.release(); keep.release(); offs.release();
     tm.mark();   // 5: rows
-    emit_deliver<KeyT>(ctx, row_keys, row_info, counting ? &row_counts : nullptr, E, d_ctr + 8, tm, prof, out,
-                       device_output, n_input, m, 0);
+    const uint32_t ww = ctx->prm.bits_per_count;
+    emit_deliver<KeyT>(ctx, [&](uint64_t *dW, uint64_t *dLast, uint64_t *dWt, unsigned long long *dF) {
+        emit_chunk<KeyT>(row_keys.as<KeyT>(), row_info.as<uint8_t>(), counting ? row_counts.as<uint32_t>() : nullptr,
+                         E, al, ww, dW, dLast, dWt, dF, s, &ctx->launches);
+    }, E, d_ctr + 8, tm, prof, out, device_output, n_input, m, 0);
 }
 
 void clear_ctx(mtg_ctx *ctx) {

@@ -171,4 +171,15 @@ void emit_chunk(const KeyT *row_keys, const uint8_t *row_info, const uint32_t *r
                 uint64_t n_rows, Alpha al, uint32_t weights_width, uint64_t *W, uint64_t *last,
                 uint64_t *weights, unsigned long long *F, cudaStream_t stream, unsigned *launches);
 
+
+// Fused merge + emit for L = 2 (DNA): W / last / F / weights straight from the sorted reals and the
+// sorted dummies with their ranks; the merged rows never exist in HBM (mtg_emit.cu). `part` is
+// scratch of emit_merged_scratch_words(m + d + row_off) words.
+size_t emit_merged_scratch_words(uint64_t n_rows);
+template <typename KeyT>
+void emit_merged(const KeyT *reals, const uint32_t *real_counts, uint64_t m, const KeyT *dummy_keys,
+                 const uint32_t *dummy_info, const uint64_t *rank, uint64_t d, uint32_t row_off, Alpha al,
+                 uint32_t weights_width, uint64_t *part, uint64_t *W, uint64_t *last, uint64_t *weights,
+                 unsigned long long *F, cudaStream_t stream, unsigned *launches);
+
 }  // namespace mtg

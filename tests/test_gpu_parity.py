@@ -302,3 +302,14 @@ def test_chunk_files_equal_reference_binary(n_reads, K, canonical, bpc, tmp_path
         a = (tmp_path / ("ref.dbg.chunk" + ext)).read_bytes()
         b = (tmp_path / ("gpu.dbg.chunk" + ext)).read_bytes()
         assert a == b, "chunk file %r differs from the reference's" % ext
+
+
+@pytest.mark.parametrize("K,canonical,bpc", [(31, True, 8), (12, False, 0), (40, True, 12)])
+def test_unfused_merge_emit_path(K, canonical, bpc, monkeypatch):
+    """DNA chunks come from the fused merge + emit kernel; the row-materialising kernels (what
+    Protein uses) must give the same chunk."""
+    reads = dna_reads(77, 3000, 100, 20_000)
+    fused = check(reads, K, canonical=canonical, bits_per_count=bpc)
+    monkeypatch.setenv("MTG_EMIT_UNFUSED", "1")
+    plain = check(reads, K, canonical=canonical, bits_per_count=bpc)
+    assert np.array_equal(fused.W_words, plain.W_words) and np.array_equal(fused.last_words, plain.last_words)
