@@ -83,7 +83,7 @@ __device__ __forceinline__ void warp_append(bool emit, KeyT v, KeyT *out, uint64
 constexpr int DC_THREADS = 256;
 constexpr int DC_IPT = 8;
 constexpr int DC_TILE = DC_THREADS * DC_IPT;
-constexpr int DC_POOL = 2 * DC_TILE + 64;     // window keys staged per tile (all labels together)
+constexpr int DC_POOL = DC_TILE + DC_TILE / 2 + 64;    // window keys staged per tile (all labels together)
 constexpr int DC_MAX_CH = 32;
 
 template <typename KeyT>

@@ -5,7 +5,7 @@
 set -u
 TAG=${1:-cur}
 mkdir -p gpurun_out
-OURS='extract|sort_|onesweep|unique|run_counts|append_rc|merge|dummy|dc_|source_prefix|scan_u32|fill_u32|flip_info|bucket_index|emit|target_nodes|ranged|filter_key'
+OURS='extract|sort_|onesweep|unique|run_counts|append_rc|merge|dummy|dc_|source_prefix|scan_u32|fill_u32|flip_info|bucket_index|emit|fe_partition|pack_reads|suffix|rj_|target_nodes|ranged|filter_key'
 CMD="python bench.py --steps 1 --warmup 1 --no-e2e --no-cpu-baseline"
 $CMD > gpurun_out/plain_$TAG.json 2> gpurun_out/plain_$TAG.err || { echo "plain run failed"; tail -5 gpurun_out/plain_$TAG.err; exit 1; }
 cat gpurun_out/plain_$TAG.json
@@ -17,8 +17,8 @@ if [ "${2:-}" != "nofull" ]; then
 NPS=${NCU_PASSES_PER_STEP:-34}
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:onesweep_pass -s $NPS -c 1 \
    -o gpurun_out/onesweep_full_$TAG -f $CMD > gpurun_out/ncu_full_$TAG.log 2>&1
-HEAVY=${NCU_HEAVY:-'extract_kernel|unique_bulk|dc_sinks|merge_tiles|merge_reals|emit_kernel'}
-timeout 1200 ncu --set full --clock-control none --import-source on -k "regex:$HEAVY" -s ${NCU_HEAVY_SKIP:-15} -c ${NCU_HEAVY_COUNT:-15} \
+HEAVY=${NCU_HEAVY:-'extract_kernel|unique_bulk|dc_sinks|merge_tiles|emit_merged|sort_histogram'}
+timeout 1200 ncu --set full --clock-control none --import-source on -k "regex:$HEAVY" -s ${NCU_HEAVY_SKIP:-11} -c ${NCU_HEAVY_COUNT:-11} \
    -o gpurun_out/heavy_full_$TAG -f $CMD > gpurun_out/ncu_heavy_$TAG.log 2>&1
 ls -la gpurun_out/*.ncu-rep
 fi
