@@ -313,3 +313,21 @@ def test_unfused_merge_emit_path(K, canonical, bpc, monkeypatch):
     monkeypatch.setenv("MTG_EMIT_UNFUSED", "1")
     plain = check(reads, K, canonical=canonical, bits_per_count=bpc)
     assert np.array_equal(fused.W_words, plain.W_words) and np.array_equal(fused.last_words, plain.last_words)
+
+
+def test_dna_character_classes():
+    """Arithmetic DNA encoding (4 characters per word) against the table semantics: either case,
+    U as T, every other byte (N, '@', '`', 'V', digits ...) ends the window."""
+    rng = np.random.default_rng(5)
+    base = dna_reads(9, 400, 120, 5000)
+    odd = "NnUu@`VvTt0-*ZKk"
+    reads = []
+    for r in base:
+        b = list(r)
+        for p in rng.integers(0, len(b), 6):
+            b[p] = odd[int(rng.integers(0, len(odd)))]
+        if rng.random() < 0.5:
+            b = [ch.lower() if rng.random() < 0.5 else ch for ch in b]
+        reads.append("".join(b))
+    check(reads, 9, canonical=True, bits_per_count=8)
+    check(reads, 33, canonical=False)
