@@ -42,8 +42,14 @@ merge_tiles_kernel(const KeyT *__restrict__ A, uint64_t na, const KeyT *__restri
                    uint32_t *__restrict__ outc) {
     constexpr int MG_IPT = MergeTile<KeyT>::IPT;
     constexpr int TILE = MG_THREADS * MG_IPT;
-    __shared__ KeyT s_in[TILE + 2];
-    __shared__ KeyT s_out[TILE];
+    // Shared-memory indices are padded (PI: one slot every 4, PO: one every MG_IPT): thread t walks
+    // the inputs around index IPT/2 * t and writes outputs IPT * t .. IPT * t + IPT - 1, and without
+    // the padding those strides put 8 to 16 lanes of a warp on the same banks (the ncu capture of
+    // the unpadded kernel: L1TEX 98 %, 64 % of the shared wavefronts were conflicts).
+    auto PI = [](uint32_t i) { return i + (i >> 2); };
+    auto PO = [](uint32_t i) { return i + i / MG_IPT; };
+    __shared__ KeyT s_in[TILE + 2 + (TILE + 2) / 4 + 1];
+    __shared__ KeyT s_out[TILE + TILE / MG_IPT];
     __shared__ uint32_t s_src[HAS_VAL ? TILE : 1];
     const uint64_t a0 = part[blockIdx.x], a1 = part[blockIdx.x + 1];
     const uint64_t d0 = (uint64_t)blockIdx.x * TILE;
@@ -52,26 +58,42 @@ merge_tiles_kernel(const KeyT *__restrict__ A, uint64_t na, const KeyT *__restri
     const uint64_t b0 = d0 - a0, b1 = d1 - a1;
     const uint32_t la = (uint32_t)(a1 - a0), lb = (uint32_t)(b1 - b0), total = la + lb;
     for (uint32_t i = threadIdx.x; i < total; i += MG_THREADS)
-        s_in[i] = i < la ? A[a0 + i] : B[b0 + (i - la)];
+        s_in[PI(i)] = i < la ? A[a0 + i] : B[b0 + (i - la)];
     __syncthreads();
-    const KeyT *sA = s_in, *sB = s_in + la;
     uint32_t diag = threadIdx.x * MG_IPT;
     if (diag > total) diag = total;
-    uint32_t ia = merge_path<KeyT, uint32_t>(sA, la, sB, lb, diag);
+    uint32_t ia;
+    {   // merge-path split of the thread's diagonal (A first on ties), on the padded layout
+        uint32_t lo = diag > lb ? diag - lb : 0, hi = diag < la ? diag : la;
+        while (lo < hi) {
+            const uint32_t mid = (lo + hi) >> 1;
+            if (!w_lt(s_in[PI(la + diag - 1 - mid)], s_in[PI(mid)])) lo = mid + 1; else hi = mid;
+        }
+        ia = lo;
+    }
     uint32_t ib = diag - ia;
+    // the two current heads live in registers: one shared-memory read per output
+    KeyT ka = ia < la ? s_in[PI(ia)] : WordTraits<KeyT>::zero();
+    KeyT kb = ib < lb ? s_in[PI(la + ib)] : WordTraits<KeyT>::zero();
 #pragma unroll
     for (int i = 0; i < MG_IPT; ++i) {
-        uint32_t o = diag + i;
+        const uint32_t o = diag + i;
         if (o < total) {
-            bool takeA = ib >= lb || (ia < la && !w_lt(sB[ib], sA[ia]));
-            s_out[o] = takeA ? sA[ia] : sB[ib];
+            const bool takeA = ib >= lb || (ia < la && !w_lt(kb, ka));
+            s_out[PO(o)] = takeA ? ka : kb;
             if (HAS_VAL) s_src[o] = takeA ? ia : (0x80000000u | ib);
-            if (takeA) ++ia; else ++ib;
+            if (takeA) {
+                ++ia;
+                if (ia < la) ka = s_in[PI(ia)];
+            } else {
+                ++ib;
+                if (ib < lb) kb = s_in[PI(la + ib)];
+            }
         }
     }
     __syncthreads();
     for (uint32_t i = threadIdx.x; i < total; i += MG_THREADS) {
-        out[d0 + i] = s_out[i];
+        out[d0 + i] = s_out[PO(i)];
         if (HAS_VAL) {
             uint32_t src = s_src[i];
             outc[d0 + i] = (src & 0x80000000u) ? Bc[b0 + (src & 0x7fffffffu)] : Ac[a0 + src];
