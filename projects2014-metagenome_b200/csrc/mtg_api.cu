@@ -579,8 +579,10 @@ struct SortProfile {   // CUDA events around every kernel of the main sort
 
 template <typename KeyT>
 void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const SortPlan &plan,
-               cudaStream_t s, unsigned *launches, cudaEvent_t *events = nullptr) {
-    // sorts; on return `a` (and *va) hold the sorted data
+               cudaStream_t s, unsigned *launches, cudaEvent_t *events = nullptr,
+               const void *first_src = nullptr) {
+    // sorts; on return `a` (and *va) hold the sorted data. first_src: the unsorted keys are read
+    // from there (first pass and histogram) instead of `a`
     SortWorkspace ws;
     DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
     DevBuf hist(sizeof(unsigned long long) * MAX_SORT_PASSES * RADIX, s);
@@ -589,6 +591,9 @@ void sort_keys(DevBuf &a, DevBuf &b, DevBuf *va, DevBuf *vb, uint64_t n, const S
     ws.hist = hist.as<unsigned long long>();
     ws.tile_counters = ctr.as<unsigned int>();
     ws.events = events;
+    ws.first_src = plan.n ? first_src : nullptr;
+    if (first_src && !plan.n && n)
+        MTG_CUDA(cudaMemcpyAsync(a.p, first_src, sizeof(KeyT) * n, cudaMemcpyDeviceToDevice, s));
     KeyT *keys[2] = {a.as<KeyT>(), b.as<KeyT>()};
     uint32_t *vals[2] = {va ? va->as<uint32_t>() : nullptr, vb ? vb->as<uint32_t>() : nullptr};
     int cur = radix_sort<KeyT>(keys, va ? vals : nullptr, n, plan, ws, s, launches);
@@ -660,8 +665,7 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
     if (payload) { valsA.alloc(4 * n_ub, s); valsB.alloc(4 * n_ub, s); }
 
     if (tm) tm->mark();
-    if (ext_keys) {
-        MTG_CUDA(cudaMemcpyAsync(keysA.p, ext_keys, sizeof(KeyT) * ext_n, cudaMemcpyDeviceToDevice, s));
+    if (ext_keys) {   // sorted straight out of the caller's (receive) buffer, no staging copy
         unsigned long long hn = ext_n;
         MTG_CUDA(cudaMemcpyAsync(d_ctr, &hn, 8, cudaMemcpyHostToDevice, s));
     } else {
@@ -700,7 +704,7 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
         prof->bytes_per_key = 2 * (sizeof(KeyT) + (payload ? 4 : 0));
     }
     sort_keys<KeyT>(keysA, keysB, payload ? &valsA : nullptr, payload ? &valsB : nullptr, n, plan_lo, s,
-                    &ctx->launches, prof && n ? prof->ev : nullptr);
+                    &ctx->launches, prof && n ? prof->ev : nullptr, ext_keys);
 
     auto fold = [&](DevBuf &src, uint64_t cnt, DevBuf &dst, const uint32_t *src_vals, DevBuf *dst_counts,
                     uint64_t counts_cap) -> uint64_t {
@@ -1460,34 +1464,45 @@ void mg_targets_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **
 // `a` holds consecutive sorted runs: pairwise merge-path rounds (ceil(log2(#runs)) passes over the
 // data instead of a full radix sort). On return `a` holds the sorted array.
 template <typename KeyT>
+// The runs start in `a` (or, with ext_a, in the caller's receive buffer: the first level of the
+// merge tree then reads them from there and no staging copy is made); the result ends in `a`.
 void merge_runs(mtg_ctx *ctx, DevBuf &a, DevBuf &b, std::vector<uint64_t> runs, DevBuf *ca = nullptr,
-                DevBuf *cb = nullptr) {
+                DevBuf *cb = nullptr, const void *ext_a = nullptr, const uint32_t *ext_ca = nullptr) {
     cudaStream_t s = ctx->stream;
     uint64_t total = 0;
     for (uint64_t r : runs) total += r;
+    if (ext_a && runs.size() <= 1) {
+        MTG_CUDA(cudaMemcpyAsync(a.p, ext_a, sizeof(KeyT) * total, cudaMemcpyDeviceToDevice, s));
+        if (ca) MTG_CUDA(cudaMemcpyAsync(ca->p, ext_ca, 4 * total, cudaMemcpyDeviceToDevice, s));
+        return;
+    }
     DevBuf part(8 * merge_partition_words(total), s);
+    bool from_ext = ext_a != nullptr;
     while (runs.size() > 1) {
         std::vector<uint64_t> next;
         uint64_t off = 0;
+        const KeyT *ik = from_ext ? static_cast<const KeyT *>(ext_a) : a.as<KeyT>();
+        const uint32_t *ic = !ca ? nullptr : from_ext ? ext_ca : ca->as<uint32_t>();
+        KeyT *ok = from_ext ? a.as<KeyT>() : b.as<KeyT>();
+        uint32_t *oc = !ca ? nullptr : from_ext ? ca->as<uint32_t>() : cb->as<uint32_t>();
         for (size_t i = 0; i < runs.size(); i += 2) {
             const uint64_t la = runs[i], lb = i + 1 < runs.size() ? runs[i + 1] : 0;
             if (lb == 0 || la == 0) {
-                MTG_CUDA(cudaMemcpyAsync(b.as<KeyT>() + off, a.as<KeyT>() + off, sizeof(KeyT) * (la + lb),
-                                         cudaMemcpyDeviceToDevice, s));
-                if (ca)
-                    MTG_CUDA(cudaMemcpyAsync(cb->as<uint32_t>() + off, ca->as<uint32_t>() + off, 4 * (la + lb),
-                                             cudaMemcpyDeviceToDevice, s));
+                MTG_CUDA(cudaMemcpyAsync(ok + off, ik + off, sizeof(KeyT) * (la + lb), cudaMemcpyDeviceToDevice, s));
+                if (ca) MTG_CUDA(cudaMemcpyAsync(oc + off, ic + off, 4 * (la + lb), cudaMemcpyDeviceToDevice, s));
             } else {
-                merge_sorted<KeyT>(a.as<KeyT>() + off, la, a.as<KeyT>() + off + la, lb,
-                                   ca ? ca->as<uint32_t>() + off : nullptr, ca ? ca->as<uint32_t>() + off + la : nullptr,
-                                   b.as<KeyT>() + off, ca ? cb->as<uint32_t>() + off : nullptr, part.as<uint64_t>(), s,
-                                   &ctx->launches);
+                merge_sorted<KeyT>(ik + off, la, ik + off + la, lb, ca ? ic + off : nullptr,
+                                   ca ? ic + off + la : nullptr, ok + off, ca ? oc + off : nullptr,
+                                   part.as<uint64_t>(), s, &ctx->launches);
             }
             next.push_back(la + lb);
             off += la + lb;
         }
-        std::swap(a, b);
-        if (ca) std::swap(*ca, *cb);
+        if (!from_ext) {
+            std::swap(a, b);
+            if (ca) std::swap(*ca, *cb);
+        }
+        from_ext = false;
         runs.swap(next);
     }
 }
@@ -1505,18 +1520,18 @@ void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, const uint64
     unsigned long long *d_ctr = ctr.as<unsigned long long>();
     // targets received from every range: sort, fold -> T_i
     DevBuf t0(sizeof(KeyT) * std::max<uint64_t>(n_in, 1), s), t1(sizeof(KeyT) * std::max<uint64_t>(n_in, 1), s);
-    MTG_CUDA(cudaMemcpyAsync(t0.p, d_in, sizeof(KeyT) * n_in, cudaMemcpyDeviceToDevice, s));
     {
         uint64_t run_total = 0;
         for (uint32_t i = 0; i < n_runs; ++i) run_total += run_lengths[i];
         if (run_lengths && n_runs && run_total == n_in) {
-            // every source sends its targets sorted: merge the runs
-            merge_runs<KeyT>(ctx, t0, t1, std::vector<uint64_t>(run_lengths, run_lengths + n_runs));
+            // every source sends its targets sorted: merge the runs (read from the receive buffer)
+            merge_runs<KeyT>(ctx, t0, t1, std::vector<uint64_t>(run_lengths, run_lengths + n_runs), nullptr, nullptr,
+                             d_in);
         } else {
             SortPlan plan;
             plan.n = 0;
             plan_add_key_bits(plan, 0, (K - 1) * L);
-            sort_keys<KeyT>(t0, t1, nullptr, nullptr, n_in, plan, s, &ctx->launches);
+            sort_keys<KeyT>(t0, t1, nullptr, nullptr, n_in, plan, s, &ctx->launches, nullptr, d_in);
         }
         DevBuf status(sizeof(unsigned long long) * unique_status_words(n_in), s), tctr(sizeof(unsigned int), s);
         unique_keys<KeyT>(t0.as<KeyT>(), n_in, t1.as<KeyT>(), nullptr, d_ctr, status.as<unsigned long long>(),
@@ -1625,18 +1640,18 @@ void mg_merge_impl(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t
     const bool counting = ctx->prm.bits_per_count > 0;
     DevBuf rb0(sizeof(KeyT) * std::max<uint64_t>(nr, 1), s), rb1(sizeof(KeyT) * std::max<uint64_t>(nr, 1), s);
     DevBuf cb0, cb1;
-    MTG_CUDA(cudaMemcpyAsync(rb0.p, d_r, sizeof(KeyT) * nr, cudaMemcpyDeviceToDevice, s));
     if (counting) {
         cb0.alloc(4 * std::max<uint64_t>(nr, 1), s);
         cb1.alloc(4 * std::max<uint64_t>(nr, 1), s);
-        MTG_CUDA(cudaMemcpyAsync(cb0.p, d_rc, 4 * nr, cudaMemcpyDeviceToDevice, s));
     }
     uint64_t run_total = 0;
     for (uint32_t i = 0; i < n_runs; ++i) run_total += r_runs[i];
-    if (r_runs && n_runs && run_total == nr) {   // one sorted run per source rank
+    if (r_runs && n_runs && run_total == nr) {   // one sorted run per source rank, read from the receive buffer
         merge_runs<KeyT>(ctx, rb0, rb1, std::vector<uint64_t>(r_runs, r_runs + n_runs), counting ? &cb0 : nullptr,
-                         counting ? &cb1 : nullptr);
+                         counting ? &cb1 : nullptr, d_r, d_rc);
     } else {
+        MTG_CUDA(cudaMemcpyAsync(rb0.p, d_r, sizeof(KeyT) * nr, cudaMemcpyDeviceToDevice, s));
+        if (counting) MTG_CUDA(cudaMemcpyAsync(cb0.p, d_rc, 4 * nr, cudaMemcpyDeviceToDevice, s));
         SortPlan plan;
         plan.n = 0;
         plan_add_key_bits(plan, 0, al.K * al.L);

@@ -524,7 +524,8 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         size_t sh = sizeof(unsigned int) * plan.n * RADIX;
         if (ws.events) cudaEventRecord(ws.events[2 * MAX_SORT_PASSES], stream);
         const uint32_t *v0 = vals ? vals[0] : nullptr;
-#define HIST(NP) launch_histogram<KeyT, HAS_VAL, NP>(grid, sh, keys[0], v0, n, plan, ws.hist, stream)
+        const KeyT *k0 = ws.first_src ? static_cast<const KeyT *>(ws.first_src) : keys[0];
+#define HIST(NP) launch_histogram<KeyT, HAS_VAL, NP>(grid, sh, k0, v0, n, plan, ws.hist, stream)
         switch (plan.n) {
             case 1: HIST(1); break;
             case 2: HIST(2); break;
@@ -545,7 +546,7 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
     int cur = 0;
     for (int p = 0; p < plan.n; ++p) {
         if (ws.events) cudaEventRecord(ws.events[2 * p], stream);
-        const KeyT *ik = keys[cur];
+        const KeyT *ik = p == 0 && ws.first_src ? static_cast<const KeyT *>(ws.first_src) : keys[cur];
         KeyT *ok = keys[cur ^ 1];
         const uint32_t *iv = HAS_VAL ? vals[cur] : nullptr;
         uint32_t *ov = HAS_VAL ? vals[cur ^ 1] : nullptr;

@@ -38,6 +38,9 @@ struct SortWorkspace {
     unsigned int *tile_counters = nullptr;  // [MAX_SORT_PASSES]
     // optional profiling: [2p], [2p+1] bracket pass p; [2*MAX], [2*MAX+1] the histogram
     cudaEvent_t *events = nullptr;
+    // optional: the unsorted keys live here (read-only, e.g. a receive buffer); the histogram and
+    // the first pass read them, the passes then alternate keys[1], keys[0], ... as usual
+    const void *first_src = nullptr;
 };
 
 size_t sort_tile_keys(bool wide);
