@@ -224,8 +224,11 @@ def run_ours(args, wl):
         import torch.distributed as dist
         # all-to-all over NVLink: 64 p2p channels measured 620 GB/s per GPU and direction at 2 GPUs
         # against 425 GB/s with NCCL's default (scripts/a2a_bench.py)
-        if os.environ.get("NCCL_DEBUG", "VERSION") == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"   # keep stdout to the one JSON line
+        # stdout carries exactly one JSON line: NCCL prints its version banner there (NCCL_DEBUG=VERSION
+        # or WARN), so fd 1 points at stderr until the line is printed (multi_gpu.bench restores it)
+        sys.stdout.flush()
+        os.environ["MTG_BENCH_STDOUT_FD"] = str(os.dup(1))
+        os.dup2(2, 1)
         os.environ.setdefault("NCCL_MIN_P2P_NCHANNELS", "64")
         os.environ.setdefault("NCCL_MAX_P2P_NCHANNELS", "64")
         dist.init_process_group("nccl", device_id=dev)

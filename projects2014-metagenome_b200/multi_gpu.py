@@ -564,4 +564,8 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                      "phases_ms_per_rank": all_phases},
         "cpu_baseline": None,
     }
-    print(json.dumps(line))
+    fd = os.environ.pop("MTG_BENCH_STDOUT_FD", None)
+    if fd is not None:   # bench.py parked the real stdout while NCCL could write to fd 1
+        sys.stdout.flush()
+        os.dup2(int(fd), 1)
+    print(json.dumps(line), flush=True)
