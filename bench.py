@@ -293,10 +293,22 @@ def run_ours(args, wl):
     P = (K * 2 + 7) // 8
     alg = algorithmic_bytes(st, n_bytes, w, c, P, wl["canonical"], 4, wl["bpc"])
     device_ms = sum(s["ms_total"] for s in stats) / len(stats)
+    # DRAM traffic of that kernel from the committed ncu --set full capture of this same workload
+    traffic, traffic_src = None, None
+    try:
+        with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
+            ent = json.load(f)["onesweep_pass_v3_kernel<u64>"]
+        if w == 8 and int(st["onesweep_keys"]) == int(ent["keys_per_launch"]):
+            traffic = float(ent["dram_bytes_read"] + ent["dram_bytes_write"])
+            traffic_src = ent["source"]
+    except Exception:
+        pass
     roofline = {
-        "bound": "hbm", "kernel": "onesweep_pass_kernel<u64> (main k-mer sort, 8 launches/step)",
+        "bound": "hbm",
+        "kernel": "onesweep_pass_v3_kernel<u64> (low passes of the main k-mer sort over all input k-mers, "
+                  "%d launches/step)" % (n_launch // max(len(stats), 1)),
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-        "traffic": None, "peak_source": peak_src,
+        "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": bytes_launch, "ms_per_launch": ms_kernel,
         "kernel_share_of_step": sum(s["ms_onesweep_sum"] for s in stats) / max(ms_total, 1e-9),
         "whole_path": {"algorithmic_bytes_per_step": alg, "bytes_per_input_kmer": alg / max(N, 1),
