@@ -144,7 +144,8 @@ int mtg_debug_sort_u128(int device, uint64_t *keys_lohi, uint32_t *vals /*nullab
  * its word; bucket ranges are assigned to contexts by the caller, which moves the data
  * between contexts (NCCL all-to-all / all-gather in multi_gpu.py). All buffers are device
  * memory; element size is 8 bytes if (k+1)*L <= 64, else 16. Sequence of calls per context:
- *   mtg_push_reads* -> mtg_mg_extract -> [all-to-all by bucket] -> mtg_mg_collect
+ *   mtg_push_reads* -> mtg_mg_extract -> [all-to-all by bucket]   (or: mtg_mg_count -> mtg_mg_route)
+ *   -> mtg_mg_collect
  *   [canonical: -> mtg_mg_strands -> [all-to-all of both strands by final range] -> mtg_mg_merge]
  *   -> mtg_mg_targets -> [all-to-all by bucket] -> mtg_mg_dummies -> [all-gather]
  *   -> mtg_mg_build  (chunk of this range; the host concatenates with Chunk::extend). */
@@ -152,6 +153,17 @@ uint32_t mtg_mg_part_bits(const mtg_ctx *ctx);
 /* Extracts the pushed reads (the canonical k-mers in canonical mode) and groups the k-mers by bucket:
  * bucket_counts[2^part_bits] (host), *d_keys library-owned until mtg_mg_collect. */
 int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_t *n);
+/* The same phase with the exchange fused into the grouping pass (what multi_gpu.py uses over NVLink):
+ * mtg_mg_count extracts and returns bucket_counts[2^part_bits] (the k-mers stay in the context,
+ * unordered); after the ranks have agreed on the bucket ranges, mtg_mg_route scatters the k-mers in
+ * ONE kernel, bucket b to the array at device address bucket_dst[b] -- normally a slice of the owner
+ * GPU's peer-mapped receive buffer, so the stores of the grouping pass are the all-to-all
+ * (csrc/mtg_sort.cu: onesweep_pass_v3_kernel<ROUTE>). Keys of a bucket arrive in extraction order
+ * (the pass is stable); the call returns when the kernel is done, the caller then synchronises the
+ * ranks. Replaces the routing of boss_chunk_construct.cpp:366-397 (split by F/W into per-bucket
+ * containers). */
+int mtg_mg_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n);
+int mtg_mg_route(mtg_ctx *ctx, const uint64_t *bucket_dst /* [2^part_bits] device addresses */);
 /* Sort + fold the k-mers routed to this context (d_keys NULL: the context's own extraction). */
 int mtg_mg_collect(mtg_ctx *ctx, const void *d_keys, uint64_t n, uint64_t *n_real);
 /* Canonical mode only (both_strands): mtg_mg_extract / mtg_mg_collect route and reduce the CANONICAL

@@ -272,6 +272,20 @@ class BOSSChunkConstructor:
                                              ctypes.byref(ptr), ctypes.byref(n)))
         return counts, ptr.value or 0, n.value
 
+    def mg_count(self):
+        """extraction + per-bucket counts; the k-mers stay in the context -> (bucket_counts, n)"""
+        counts = np.zeros(1 << self.mg_part_bits(), dtype=np.uint64)
+        n = ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_count(self._ctx, counts.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
+                                           ctypes.byref(n)))
+        return counts, n.value
+
+    def mg_route(self, bucket_dst):
+        """one scatter kernel: bucket b of the counted k-mers goes to device address bucket_dst[b]"""
+        dst = np.ascontiguousarray(bucket_dst, dtype=np.uint64)
+        assert dst.shape[0] == 1 << self.mg_part_bits()
+        self._check(self._lib.mtg_mg_route(self._ctx, dst.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
+
     def mg_collect(self, dptr, n):
         m = ctypes.c_uint64()
         self._check(self._lib.mtg_mg_collect(self._ctx, ctypes.c_void_p(dptr), n, ctypes.byref(m)))

@@ -211,7 +211,7 @@ struct mtg_ctx {
     struct Mg {
         DevBuf keys, targets, tset, sinks, src, rkeys, rcounts;
         RealSet reals;
-        uint64_t nt = 0, n_sink = 0, n_src = 0, n_input = 0;
+        uint64_t nt = 0, n_sink = 0, n_src = 0, n_input = 0, n_routed = 0;
     } mg;
 };
 
@@ -1423,6 +1423,65 @@ void mg_extract_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **
     ctx->segs.clear();
 }
 
+// Phase 1 split for the fused exchange: mg_count extracts and counts the k-mers per routing bucket
+// (they stay unordered in the context); mg_route then scatters them ONCE, each bucket straight to
+// the address the caller gives for it -- a slice of the owner GPU's peer-mapped receive buffer.
+template <typename KeyT>
+void mg_count_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, uint64_t *n_out) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    uint64_t n_ub = 0;
+    for (auto &seg : ctx->segs) n_ub += seg.n_windows_max;
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
+    DevBuf a(sizeof(KeyT) * std::max<uint64_t>(n_ub, 1), s);
+    ctx->launches = 0;
+    run_extraction<KeyT>(ctx, false, false, a.as<KeyT>(), nullptr, d_ctr);
+    const uint64_t n = read_counter(d_ctr, s);
+    const uint32_t nb = 1u << pb;
+    for (uint32_t i = 0; i < nb; ++i) bucket_counts[i] = 0;
+    if (pb == 0 || n == 0) {
+        bucket_counts[0] = n;
+    } else {
+        DevBuf hist(sizeof(unsigned long long) * RADIX, s);
+        digit_histogram<KeyT>(a.as<KeyT>(), n, DigitPass{0, (int)(al.K * al.L - pb), (int)pb},
+                              hist.as<unsigned long long>(), s, &ctx->launches);
+        std::vector<unsigned long long> h(RADIX);
+        MTG_CUDA(cudaMemcpyAsync(h.data(), hist.p, 8 * RADIX, cudaMemcpyDeviceToHost, s));
+        MTG_CUDA(cudaStreamSynchronize(s));
+        for (uint32_t i = 0; i < nb; ++i) bucket_counts[i] = h[i];
+    }
+    ctx->mg.keys = std::move(a);
+    ctx->mg.n_input = n;
+    ctx->mg.n_routed = n;
+    *n_out = n;
+    ctx->segs.clear();
+}
+
+template <typename KeyT>
+void mg_route_impl(mtg_ctx *ctx, uint32_t pb, const uint64_t *bucket_dst) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint64_t n = ctx->mg.n_routed;
+    if (n) {
+        const uint32_t nb = 1u << pb;
+        std::vector<unsigned long long> h(RADIX, 0ull);
+        for (uint32_t i = 0; i < nb; ++i) h[i] = bucket_dst[i];
+        DevBuf route(8 * RADIX, s), tc(sizeof(unsigned int), s);
+        DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
+        MTG_CUDA(cudaMemcpyAsync(route.p, h.data(), 8 * RADIX, cudaMemcpyHostToDevice, s));
+        // pb = 0: one bucket, a 1-bit digit above the key bits (always 0) keeps the pass generic
+        const DigitPass dp = pb ? DigitPass{0, (int)(al.K * al.L - pb), (int)pb}
+                                : DigitPass{0, (int)(8 * sizeof(KeyT) - 1), 1};
+        route_scatter<KeyT>(ctx->mg.keys.as<KeyT>(), n, dp, route.as<unsigned long long>(),
+                            status.as<unsigned long long>(), tc.as<unsigned int>(), s, &ctx->launches);
+        MTG_CUDA(cudaStreamSynchronize(s));   // `h` and the scratch outlive the kernel
+    }
+    ctx->mg.keys.release();
+    ctx->mg.n_routed = 0;
+}
+
 template <typename KeyT>
 void mg_targets_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **d_targets, uint64_t *n_out) {
     cudaStream_t s = ctx->stream;
@@ -1754,6 +1813,29 @@ int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_
             return fail(ctx, MTG_ERR_UNSUPPORTED, "a suffix-filtered chunk is built on one GPU (mtg_build_chunk)");
         if (wide) mg_extract_impl<u128>(ctx, mg_part_bits(ctx), bucket_counts, d_keys, n);
         else mg_extract_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_counts, d_keys, n);
+    })
+}
+
+int mtg_mg_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n) {
+    MG_GUARD(ctx, {
+        if (ctx->any_explicit_counts)
+            return fail(ctx, MTG_ERR_UNSUPPORTED, "per-read counts are not supported by the range-partitioned build");
+        if (!ctx->suffix.empty())
+            return fail(ctx, MTG_ERR_UNSUPPORTED, "a suffix-filtered chunk is built on one GPU (mtg_build_chunk)");
+        if (!bucket_counts || !n) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+        if (wide) mg_count_impl<u128>(ctx, mg_part_bits(ctx), bucket_counts, n);
+        else mg_count_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_counts, n);
+    })
+}
+
+int mtg_mg_route(mtg_ctx *ctx, const uint64_t *bucket_dst) {
+    MG_GUARD(ctx, {
+        if (!bucket_dst) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+        const uint32_t w = wide ? 16 : 8;
+        for (uint32_t i = 0; i < (1u << mg_part_bits(ctx)); ++i)
+            if (bucket_dst[i] % w) return fail(ctx, MTG_ERR_BAD_ARG, "bucket destinations must be key-aligned");
+        if (wide) mg_route_impl<u128>(ctx, mg_part_bits(ctx), bucket_dst);
+        else mg_route_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_dst);
     })
 }
 

@@ -149,7 +149,10 @@ __device__ __forceinline__ unsigned long long lookback_digit(const unsigned long
 //   * rank = running per-warp digit offset (already holding the tile position) + popc(peers
 //     below my lane): stable, deterministic, no dependence on atomic ordering.
 // ---------------------------------------------------------------------------
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
+// ROUTE: the keys of digit d go to the array at address route[d] (local or peer-mapped memory of
+// another GPU) instead of out_keys + digit_offsets[d]: the scatter of the pass IS the exchange
+// (grouping by routing bucket + all-to-all in one kernel; its stores leave over NVLink).
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB, bool ROUTE = false>
 __global__ void __launch_bounds__(THREADS, MINB)
 onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out_keys,
                         const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
@@ -276,7 +279,11 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
             excl = lookback_digit<(LB > 0 ? LB : 1)>(status, tile, tid, epoch);
         }
         st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(2, epoch, excl + count));
-        goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
+        if (ROUTE)   // digit_offsets = the 2^bits destination addresses; goff = byte address of tile slot 0
+            goff[tid] = (long long)digit_offsets[tid]
+                        + ((long long)excl - (long long)local_base) * (long long)sizeof(KeyT);
+        else
+            goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
     }
     __syncthreads();
 
@@ -286,9 +293,13 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
         KeyT k = sh_keys[p];
         uint32_t v = HAS_VAL ? sh_vals[p] : 0;
         uint32_t d = digit_of(k, v, dp);
-        size_t dst = (size_t)(goff[d] + (long long)p);
-        out_keys[dst] = k;
-        if (HAS_VAL) out_vals[dst] = v;
+        if (ROUTE) {
+            *reinterpret_cast<KeyT *>(goff[d] + (long long)p * (long long)sizeof(KeyT)) = k;
+        } else {
+            size_t dst = (size_t)(goff[d] + (long long)p);
+            out_keys[dst] = k;
+            if (HAS_VAL) out_vals[dst] = v;
+        }
     }
 }
 
@@ -465,7 +476,7 @@ void launch_v4(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
                                                                       dp, offs, status, ctr, epoch);
 }
 
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB, bool ROUTE = false>
 void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
                uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
                unsigned int *ctr, unsigned epoch, cudaStream_t stream) {
@@ -473,7 +484,7 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
     size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
                   + 2 * sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
                   + sizeof(uint32_t) * (THREADS / 32 + 1);
-    auto kern = onesweep_pass_v3_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB, LB>;
+    auto kern = onesweep_pass_v3_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB, LB, ROUTE>;
     static bool attr_set = false;
     if (!attr_set) {
         MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -585,6 +596,51 @@ int radix_sort(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan &pla
     if (vals && vals[0]) return radix_sort_impl<KeyT, true>(keys, vals, n, plan, ws, stream, launches);
     return radix_sort_impl<KeyT, false>(keys, nullptr, n, plan, ws, stream, launches);
 }
+
+// Counts of one digit (raw, not scanned): hist[0 .. 2^bits)
+template <typename KeyT>
+void digit_histogram(const KeyT *keys, uint64_t n, DigitPass dp, unsigned long long *hist, cudaStream_t stream,
+                     unsigned *launches) {
+    MTG_CUDA(cudaMemsetAsync(hist, 0, sizeof(unsigned long long) * RADIX, stream));
+    if (n == 0) return;
+    int dev, sms;
+    MTG_CUDA(cudaGetDevice(&dev));
+    MTG_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    SortPlan plan;
+    plan.n = 1;
+    plan.p[0] = dp;
+    size_t want = div_up(n, (size_t)512 * 8);
+    unsigned grid = (unsigned)(want < (size_t)sms * 4 ? (want ? want : 1) : (size_t)sms * 4);
+    launch_histogram<KeyT, false, 1>(grid, sizeof(unsigned int) * RADIX, keys, nullptr, n, plan, hist, stream);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+template void digit_histogram<uint64_t>(const uint64_t *, uint64_t, DigitPass, unsigned long long *,
+                                        cudaStream_t, unsigned *);
+template void digit_histogram<u128>(const u128 *, uint64_t, DigitPass, unsigned long long *, cudaStream_t,
+                                    unsigned *);
+
+// One stable scatter pass on digit dp whose digit-d keys are written to the array at address
+// route[d] (device array of 2^bits addresses; local or peer-mapped memory). status: tiles * RADIX
+// words, tile_counter: one word; both are cleared here.
+template <typename KeyT>
+void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned long long *route,
+                   unsigned long long *status, unsigned int *tile_counter, cudaStream_t stream,
+                   unsigned *launches) {
+    if (n == 0) return;
+    constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;
+    const size_t tiles = div_up(n, (size_t)4096 / S);
+    MTG_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream));
+    MTG_CUDA(cudaMemsetAsync(status, 0, sizeof(unsigned long long) * tiles * RADIX, stream));
+    launch_v3<KeyT, false, 256, 16 / S, 3, 0, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
+                                                    tile_counter, 1u, stream);
+    MTG_CUDA(cudaGetLastError());
+    *launches += 1;
+}
+template void route_scatter<uint64_t>(const uint64_t *, uint64_t, DigitPass, const unsigned long long *,
+                                      unsigned long long *, unsigned int *, cudaStream_t, unsigned *);
+template void route_scatter<u128>(const u128 *, uint64_t, DigitPass, const unsigned long long *,
+                                  unsigned long long *, unsigned int *, cudaStream_t, unsigned *);
 
 namespace {
 __global__ void fill_random_kernel(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask,

@@ -61,4 +61,17 @@ template <typename KeyT>
 int radix_sort(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan &plan,
                SortWorkspace &ws, cudaStream_t stream, unsigned *launches);
 
+// raw counts of one digit: hist[0 .. 2^bits) (device)
+template <typename KeyT>
+void digit_histogram(const KeyT *keys, uint64_t n, DigitPass dp, unsigned long long *hist, cudaStream_t stream,
+                     unsigned *launches);
+
+// Grouping + exchange in one kernel: a stable scatter pass on digit dp whose digit-d keys go to the
+// array at address route[d] (device array of 2^bits addresses, local or peer-mapped memory of another
+// GPU). status: sort_status_words(n) words, tile_counter: one word.
+template <typename KeyT>
+void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned long long *route,
+                   unsigned long long *status, unsigned int *tile_counter, cudaStream_t stream,
+                   unsigned *launches);
+
 }  // namespace mtg

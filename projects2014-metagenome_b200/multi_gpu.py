@@ -59,6 +59,22 @@ def split_sizes(bucket_counts, ranges):
     return [int(c[lo:hi].sum()) for lo, hi in ranges]
 
 
+def route_addresses(all_counts, ranges, me, base_ptrs, key_bytes):
+    """Where source rank `me` writes each of its routing buckets (mtg_mg_route). all_counts[s][b] =
+    k-mers of source s in bucket b; destination d's receive buffer (at base_ptrs[d]) holds the
+    sources in rank order, each source's slice its buckets lo_d..hi_d in order.
+    -> (bucket_dst uint64[nb], sizes int64[source][destination])"""
+    c = np.asarray(all_counts, dtype=np.int64)
+    sizes = np.array([[int(c[s, lo:hi].sum()) for lo, hi in ranges] for s in range(c.shape[0])], dtype=np.int64)
+    dst = np.zeros(c.shape[1], dtype=np.uint64)
+    for d, (lo, hi) in enumerate(ranges):
+        off = int(sizes[:me, d].sum())
+        for b in range(lo, hi):
+            dst[b] = int(base_ptrs[d]) + off * key_bytes
+            off += int(c[me, b])
+    return dst, sizes
+
+
 def concat_chunks(chunks):
     """Host concatenation, exactly BOSS::Chunk::extend in rank (= key range) order."""
     full = chunks[0]
@@ -117,6 +133,14 @@ class RangedRank:
         self.n_extracted = n
         return counts, as_tensor(ptr, n, self.words, self.device)
 
+    def count(self):
+        counts, n = self.ctor.mg_count()
+        self.n_extracted = n
+        return counts
+
+    def route(self, bucket_dst):
+        self.ctor.mg_route(bucket_dst)
+
     def collect(self, keys):
         self._keep = keys   # the library copies; keep the tensor alive until the call returns
         n = keys.shape[0]
@@ -165,9 +189,10 @@ def _bucket_offsets(counts, ranges):
 class VirtualBuild:
     """g virtual ranks on one GPU: the same phases, the exchanges done by slicing."""
 
-    def __init__(self, world, K, canonical=False, bits_per_count=0, alphabet="DNA", device=0):
+    def __init__(self, world, K, canonical=False, bits_per_count=0, alphabet="DNA", device=0, fused_route=True):
         self.world = world
         self.canonical = canonical
+        self.fused_route = fused_route
         self.ranks = [RangedRank(K, canonical, bits_per_count, alphabet, device) for _ in range(world)]
 
     def add_sequences(self, rank, sequences):
@@ -176,11 +201,25 @@ class VirtualBuild:
     def build_chunks(self):
         torch = self.ranks[0].torch
         g = self.world
-        ex = [r.extract() for r in self.ranks]
-        hist = np.sum([c for c, _ in ex], axis=0)
-        self.ranges = plan_ranges(hist, g)
-        offs = [_bucket_offsets(c, self.ranges) for c, _ in ex]
-        routed = [torch.cat([ex[s][1][offs[s][d][0]:offs[s][d][1]] for s in range(g)]) for d in range(g)]
+        if self.fused_route:
+            # grouping + exchange in one kernel per rank: buckets are scattered straight into the
+            # owners' receive buffers (here: plain device tensors, over NVLink: peer-mapped memory)
+            counts = np.stack([r.count() for r in self.ranks])
+            self.ranges = plan_ranges(counts.sum(axis=0), g)
+            words = self.ranks[0].words
+            _, sizes = route_addresses(counts, self.ranges, 0, [0] * g, 8 * words)
+            routed = [torch.empty((int(sizes[:, d].sum()), words) if words > 1 else (int(sizes[:, d].sum()),),
+                                  dtype=torch.int64, device=self.ranks[0].device) for d in range(g)]
+            torch.cuda.synchronize()
+            for s_, r in enumerate(self.ranks):
+                dst, _ = route_addresses(counts, self.ranges, s_, [t.data_ptr() for t in routed], 8 * words)
+                r.route(dst)
+        else:
+            ex = [r.extract() for r in self.ranks]
+            hist = np.sum([c for c, _ in ex], axis=0)
+            self.ranges = plan_ranges(hist, g)
+            offs = [_bucket_offsets(c, self.ranges) for c, _ in ex]
+            routed = [torch.cat([ex[s][1][offs[s][d][0]:offs[s][d][1]] for s in range(g)]) for d in range(g)]
         torch.cuda.synchronize()   # the library works on its own streams
         for d, r in enumerate(self.ranks):
             r.collect(routed[d])
@@ -243,6 +282,8 @@ class DistBuild:
         # MTG_A2A=kernel: the pushes as ONE kernel of peer stores (csrc/mtg_peer.cu) instead of one
         # copy-engine peer copy per destination (measured at 2 GPUs: 470 vs 661 GB/s, so not the default)
         self.push_kernel = os.environ.get("MTG_A2A", "peer") == "kernel"
+        # MTG_ROUTE=0: grouping pass, then a separate exchange (the first design)
+        self.fused_route = os.environ.get("MTG_ROUTE", "1") != "0"
         self._slots = {}
         self._streams = [torch.cuda.Stream(device=self.rank.device) for _ in range(self.world)] if self.use_symm else []
         if self.use_symm:
@@ -345,6 +386,39 @@ class DistBuild:
         self.a2a_ms += ev0.elapsed_time(ev1)
         return recv
 
+    def _route_kmers(self):
+        """Exchange #1 fused into the grouping pass: after the per-bucket counts of all ranks are
+        known, ONE scatter kernel per rank writes every bucket straight into its owner's symmetric
+        receive buffer over NVLink (mtg_mg_route). Returns the k-mers received, sources in rank order."""
+        torch, dist = self.torch, self.dist
+        dev = self.rank.device
+        counts = self.rank.count()
+        self._mark("extract+count")
+        mine = torch.from_numpy(counts.astype(np.int64)).to(dev)
+        allc = torch.empty((self.world, mine.numel()), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allc, mine, group=self.group)   # also: every peer is done with slot 0
+        allc = allc.cpu().numpy()
+        self.ranges = plan_ranges(allc.sum(axis=0), self.world)
+        kb = 8 * self.rank.words
+        _, sizes = route_addresses(allc, self.ranges, self.rank_id, [0] * self.world, kb)
+        need = int(sizes.sum(axis=0).max()) * kb
+        buf, hdl = self._symm_slot(0, max(need, 16))
+        dst, _ = route_addresses(allc, self.ranges, self.rank_id, [int(p) for p in hdl.buffer_ptrs], kb)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        self.rank.route(dst)
+        hdl.barrier()
+        ev1.record()
+        ev1.synchronize()
+        self.a2a_ms += ev0.elapsed_time(ev1)
+        self.a2a_bytes += int(sizes[self.rank_id].sum() - sizes[self.rank_id, self.rank_id]) * kb
+        self.last_recv_sizes = [int(x) for x in sizes[:, self.rank_id]]
+        total = int(sizes[:, self.rank_id].sum())
+        shape = (total, self.rank.words) if self.rank.words > 1 else (total,)
+        recv = hdl.get_buffer(self.rank_id, shape, torch.int64, 0)
+        self._mark("route (group + exchange)")
+        return recv
+
     def _mark(self, name):
         """phase timing (CUDA events on the current stream, which the library shares in bench.py)"""
         if getattr(self, "phase_events", None) is not None:
@@ -364,13 +438,16 @@ class DistBuild:
         torch, dist = self.torch, self.dist
         dev = self.rank.device
         self._mark("start")
-        counts, keys = self.rank.extract()
-        self._mark("extract+group")
-        hist = torch.from_numpy(counts.astype(np.int64)).to(dev)
-        dist.all_reduce(hist, group=self.group)
-        self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
-        recv = self._exchange(keys, split_sizes(counts, self.ranges))
-        self._mark("exchange kmers")
+        if self.use_symm and self.fused_route:
+            recv = self._route_kmers()
+        else:
+            counts, keys = self.rank.extract()
+            self._mark("extract+group")
+            hist = torch.from_numpy(counts.astype(np.int64)).to(dev)
+            dist.all_reduce(hist, group=self.group)
+            self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
+            recv = self._exchange(keys, split_sizes(counts, self.ranges))
+            self._mark("exchange kmers")
         self.rank.collect(recv)
         del recv
         self._mark("collect (sort+fold)")

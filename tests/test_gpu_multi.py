@@ -13,8 +13,8 @@ from test_gpu_parity import dna_reads
 pytestmark = pytest.mark.gpu
 
 
-def virtual_build(reads, K, world, alphabet="DNA", canonical=False, bpc=0):
-    vb = multi_gpu.VirtualBuild(world, K, canonical, bpc, alphabet)
+def virtual_build(reads, K, world, alphabet="DNA", canonical=False, bpc=0, fused_route=True):
+    vb = multi_gpu.VirtualBuild(world, K, canonical, bpc, alphabet, fused_route=fused_route)
     for r in range(world):
         vb.add_sequences(r, reads[r::world])
     chunks = vb.build_chunks()
@@ -23,8 +23,8 @@ def virtual_build(reads, K, world, alphabet="DNA", canonical=False, bpc=0):
     return chunks, ranges
 
 
-def check(reads, K, world, alphabet="DNA", canonical=False, bpc=0):
-    chunks, ranges = virtual_build(reads, K, world, alphabet, canonical, bpc)
+def check(reads, K, world, alphabet="DNA", canonical=False, bpc=0, fused_route=True):
+    chunks, ranges = virtual_build(reads, K, world, alphabet, canonical, bpc, fused_route)
     stats = [c.stats for c in chunks]
     full = multi_gpu.concat_chunks(chunks)
     ref = oracle_lib.oracle_build(reads, K, alphabet=alphabet, canonical=canonical, bits_per_count=bpc)
@@ -82,3 +82,14 @@ def test_partitioned_matches_reference_golden(name):
     full = multi_gpu.concat_chunks(chunks)
     res = {"W": full.W, "last": full.last, "F": full.F, "weights": full.weights}
     assert_chunk_equals_golden(res, load_golden(name), case.get("bpc", 0))
+
+
+@pytest.mark.parametrize("world", [2, 5])
+@pytest.mark.parametrize("K,canonical,bpc", [(31, True, 8), (40, False, 0), (3, True, 0)])
+def test_separate_group_and_exchange_path(world, K, canonical, bpc):
+    """mtg_mg_extract + slicing (what the NCCL fallback uses) against the default, where the
+    grouping pass scatters straight into the owners' buffers (mtg_mg_count + mtg_mg_route)."""
+    reads = dna_reads(3 * K + world, 900, 110, 7000, e=0.01, n_frac=0.002)
+    a, ra = check(reads, K, world, canonical=canonical, bpc=bpc, fused_route=False)
+    b, rb = check(reads, K, world, canonical=canonical, bpc=bpc, fused_route=True)
+    assert ra == rb and np.array_equal(a.W_words, b.W_words)
