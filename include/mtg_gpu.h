@@ -156,14 +156,17 @@ int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_
 /* The same phase with the exchange fused into the grouping pass (what multi_gpu.py uses over NVLink):
  * mtg_mg_count extracts and returns bucket_counts[2^part_bits] (the k-mers stay in the context,
  * unordered); after the ranks have agreed on the bucket ranges, mtg_mg_route scatters the k-mers in
- * ONE kernel, bucket b to the array at device address bucket_dst[b] -- normally a slice of the owner
- * GPU's peer-mapped receive buffer, so the stores of the grouping pass are the all-to-all
- * (csrc/mtg_sort.cu: onesweep_pass_v3_kernel<ROUTE>). Keys of a bucket arrive in extraction order
- * (the pass is stable); the call returns when the kernel is done, the caller then synchronises the
- * ranks. Replaces the routing of boss_chunk_construct.cpp:366-397 (split by F/W into per-bucket
- * containers). */
+ * ONE kernel: a k-mer of bucket b goes to owner bucket_owner[b] (< n_owners <= 256) and is stored
+ * into the array at device address owner_dst[owner] -- normally this context's slice of the owner
+ * GPU's peer-mapped receive buffer (room for the sum of this context's counts of the owner's
+ * buckets), so the stores of the grouping pass are the all-to-all (csrc/mtg_sort.cu:
+ * onesweep_pass_v3_kernel<ROUTE>). Within a slice the k-mers arrive in extraction order (not grouped
+ * by bucket: mtg_mg_collect sorts them anyway). The call returns when the kernel is done; the
+ * caller then synchronises the ranks. Replaces the routing of boss_chunk_construct.cpp:366-397
+ * (split by F/W into per-bucket containers). */
 int mtg_mg_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n);
-int mtg_mg_route(mtg_ctx *ctx, const uint64_t *bucket_dst /* [2^part_bits] device addresses */);
+int mtg_mg_route(mtg_ctx *ctx, const uint32_t *bucket_owner /* [2^part_bits] */, uint32_t n_owners,
+                 const uint64_t *owner_dst /* [n_owners] device addresses */);
 /* Sort + fold the k-mers routed to this context (d_keys NULL: the context's own extraction). */
 int mtg_mg_collect(mtg_ctx *ctx, const void *d_keys, uint64_t n, uint64_t *n_real);
 /* Canonical mode only (both_strands): mtg_mg_extract / mtg_mg_collect route and reduce the CANONICAL

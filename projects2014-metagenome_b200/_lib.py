@@ -108,7 +108,7 @@ def load():
     lib.mtg_mg_part_bits.restype = ctypes.c_uint32
     lib.mtg_mg_extract.argtypes = [ctypes.c_void_p, u64p, vpp, u64p]
     lib.mtg_mg_count.argtypes = [ctypes.c_void_p, u64p, u64p]
-    lib.mtg_mg_route.argtypes = [ctypes.c_void_p, u64p]
+    lib.mtg_mg_route.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, u64p]
     lib.mtg_mg_collect.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, u64p]
     lib.mtg_mg_targets.argtypes = [ctypes.c_void_p, u64p, vpp, u64p]
     lib.mtg_peer_push.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(ctypes.c_void_p),

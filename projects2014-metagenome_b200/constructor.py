@@ -280,11 +280,14 @@ class BOSSChunkConstructor:
                                            ctypes.byref(n)))
         return counts, n.value
 
-    def mg_route(self, bucket_dst):
-        """one scatter kernel: bucket b of the counted k-mers goes to device address bucket_dst[b]"""
-        dst = np.ascontiguousarray(bucket_dst, dtype=np.uint64)
-        assert dst.shape[0] == 1 << self.mg_part_bits()
-        self._check(self._lib.mtg_mg_route(self._ctx, dst.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
+    def mg_route(self, bucket_owner, owner_dst):
+        """one scatter kernel: a counted k-mer of bucket b is stored into the array at device address
+        owner_dst[bucket_owner[b]]"""
+        own = np.ascontiguousarray(bucket_owner, dtype=np.uint32)
+        dst = np.ascontiguousarray(owner_dst, dtype=np.uint64)
+        assert own.shape[0] == 1 << self.mg_part_bits()
+        self._check(self._lib.mtg_mg_route(self._ctx, own.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
+                                           dst.shape[0], dst.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
 
     def mg_collect(self, dptr, n):
         m = ctypes.c_uint64()

@@ -1460,22 +1460,28 @@ void mg_count_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, uint64_t 
 }
 
 template <typename KeyT>
-void mg_route_impl(mtg_ctx *ctx, uint32_t pb, const uint64_t *bucket_dst) {
+void mg_route_impl(mtg_ctx *ctx, uint32_t pb, const uint32_t *bucket_owner, uint32_t n_owners,
+                   const uint64_t *owner_dst) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const uint64_t n = ctx->mg.n_routed;
     if (n) {
         const uint32_t nb = 1u << pb;
-        std::vector<unsigned long long> h(RADIX, 0ull);
-        for (uint32_t i = 0; i < nb; ++i) h[i] = bucket_dst[i];
-        DevBuf route(8 * RADIX, s), tc(sizeof(unsigned int), s);
+        // one staging block: RADIX addresses followed by RADIX owner bytes
+        std::vector<unsigned long long> h(RADIX + RADIX / 8, 0ull);
+        unsigned char *ho = reinterpret_cast<unsigned char *>(h.data() + RADIX);
+        for (uint32_t i = 0; i < n_owners; ++i) h[i] = owner_dst[i];
+        for (uint32_t i = 0; i < nb; ++i) ho[i] = (unsigned char)bucket_owner[i];
+        DevBuf route(8 * (RADIX + RADIX / 8), s), tc(sizeof(unsigned int), s);
         DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
-        MTG_CUDA(cudaMemcpyAsync(route.p, h.data(), 8 * RADIX, cudaMemcpyHostToDevice, s));
+        MTG_CUDA(cudaMemcpyAsync(route.p, h.data(), 8 * (RADIX + RADIX / 8), cudaMemcpyHostToDevice, s));
         // pb = 0: one bucket, a 1-bit digit above the key bits (always 0) keeps the pass generic
         const DigitPass dp = pb ? DigitPass{0, (int)(al.K * al.L - pb), (int)pb}
                                 : DigitPass{0, (int)(8 * sizeof(KeyT) - 1), 1};
-        route_scatter<KeyT>(ctx->mg.keys.as<KeyT>(), n, dp, route.as<unsigned long long>(),
-                            status.as<unsigned long long>(), tc.as<unsigned int>(), s, &ctx->launches);
+        route_scatter<KeyT>(ctx->mg.keys.as<KeyT>(), n, dp,
+                            reinterpret_cast<const unsigned char *>(route.as<unsigned long long>() + RADIX),
+                            route.as<unsigned long long>(), status.as<unsigned long long>(), tc.as<unsigned int>(),
+                            s, &ctx->launches);
         MTG_CUDA(cudaStreamSynchronize(s));   // `h` and the scratch outlive the kernel
     }
     ctx->mg.keys.release();
@@ -1828,14 +1834,17 @@ int mtg_mg_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n) {
     })
 }
 
-int mtg_mg_route(mtg_ctx *ctx, const uint64_t *bucket_dst) {
+int mtg_mg_route(mtg_ctx *ctx, const uint32_t *bucket_owner, uint32_t n_owners, const uint64_t *owner_dst) {
     MG_GUARD(ctx, {
-        if (!bucket_dst) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+        if (!bucket_owner || !owner_dst || n_owners == 0 || n_owners > 256)
+            return fail(ctx, MTG_ERR_BAD_ARG, "bad owner table");
         const uint32_t w = wide ? 16 : 8;
+        for (uint32_t i = 0; i < n_owners; ++i)
+            if (owner_dst[i] % w) return fail(ctx, MTG_ERR_BAD_ARG, "destinations must be key-aligned");
         for (uint32_t i = 0; i < (1u << mg_part_bits(ctx)); ++i)
-            if (bucket_dst[i] % w) return fail(ctx, MTG_ERR_BAD_ARG, "bucket destinations must be key-aligned");
-        if (wide) mg_route_impl<u128>(ctx, mg_part_bits(ctx), bucket_dst);
-        else mg_route_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_dst);
+            if (bucket_owner[i] >= n_owners) return fail(ctx, MTG_ERR_BAD_ARG, "bucket owner out of range");
+        if (wide) mg_route_impl<u128>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
+        else mg_route_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
     })
 }
 

@@ -158,7 +158,7 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
                         const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
                         uint64_t n, DigitPass dp, const unsigned long long *__restrict__ digit_offsets,
                         unsigned long long *__restrict__ status, unsigned int *tile_counter,
-                        unsigned epoch) {
+                        unsigned epoch, const unsigned char *__restrict__ route_owner = nullptr) {
     constexpr int WARPS = THREADS / 32;
     constexpr int TILE = THREADS * IPT;
     static_assert(THREADS >= RADIX, "one digit per thread in the scan phases");
@@ -170,8 +170,16 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     long long *goff = reinterpret_cast<long long *>(wmask + WARPS * RADIX);  // [RADIX]
     uint32_t *warp_tot = reinterpret_cast<uint32_t *>(goff + RADIX);         // [WARPS + 1]
     __shared__ unsigned int sh_tile;
+    // ROUTE: the scatter digit is the OWNER of the key's routing bucket (a handful of values), so a
+    // tile leaves in a few long contiguous runs, which is what the NVLink stores need
+    __shared__ unsigned char sh_owner[ROUTE ? RADIX : 1];
+    auto dig = [&](KeyT k, uint32_t v) -> uint32_t {
+        const uint32_t d = digit_of(k, v, dp);
+        return ROUTE ? (uint32_t)sh_owner[d] : d;
+    };
 
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (ROUTE && tid < RADIX) sh_owner[tid] = route_owner[tid];
     if (tid == 0) sh_tile = atomicAdd(tile_counter, 1u);
     for (int i = tid; i < 2 * WARPS * RADIX; i += THREADS) whist[i] = 0;   // whist and wmask
     __syncthreads();
@@ -200,7 +208,7 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
 #pragma unroll
     for (int r = 0; r < IPT; ++r) {
         uint32_t idx = warp_base + r * 32 + lane;
-        if (full || idx < tile_valid) atomicAdd(&my_hist[digit_of(key[r], val[r], dp)], 1u);
+        if (full || idx < tile_valid) atomicAdd(&my_hist[dig(key[r], val[r])], 1u);
     }
     __syncthreads();
 
@@ -241,7 +249,7 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     for (int r = 0; r < IPT; ++r) {
         const uint32_t idx = warp_base + r * 32 + lane;
         const bool valid = full || idx < tile_valid;
-        const uint32_t d = digit_of(key[r], val[r], dp);
+        const uint32_t d = dig(key[r], val[r]);
         if (valid) atomicOr(&my_mask[d], 1u << lane);
         __syncwarp();
         unsigned peers = 0;
@@ -292,7 +300,7 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     for (uint32_t p = tid; p < tile_valid; p += THREADS) {
         KeyT k = sh_keys[p];
         uint32_t v = HAS_VAL ? sh_vals[p] : 0;
-        uint32_t d = digit_of(k, v, dp);
+        uint32_t d = dig(k, v);
         if (ROUTE) {
             *reinterpret_cast<KeyT *>(goff[d] + (long long)p * (long long)sizeof(KeyT)) = k;
         } else {
@@ -479,7 +487,7 @@ void launch_v4(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
 template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB, bool ROUTE = false>
 void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
                uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
-               unsigned int *ctr, unsigned epoch, cudaStream_t stream) {
+               unsigned int *ctr, unsigned epoch, cudaStream_t stream, const unsigned char *route_owner = nullptr) {
     constexpr int TILE = THREADS * IPT;
     size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
                   + 2 * sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
@@ -491,7 +499,7 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
         attr_set = true;
     }
     kern<<<(unsigned)div_up(n, (size_t)TILE), THREADS, smem, stream>>>(in_keys, out_keys, in_vals, out_vals, n,
-                                                                      dp, offs, status, ctr, epoch);
+                                                                      dp, offs, status, ctr, epoch, route_owner);
 }
 
 // variant selection (experiments): MTG_SORT_VARIANT, see the switch in radix_sort_impl
@@ -620,27 +628,29 @@ template void digit_histogram<uint64_t>(const uint64_t *, uint64_t, DigitPass, u
 template void digit_histogram<u128>(const u128 *, uint64_t, DigitPass, unsigned long long *, cudaStream_t,
                                     unsigned *);
 
-// One stable scatter pass on digit dp whose digit-d keys are written to the array at address
-// route[d] (device array of 2^bits addresses; local or peer-mapped memory). status: tiles * RADIX
-// words, tile_counter: one word; both are cleared here.
+// One stable scatter pass: a key whose digit dp is b goes to owner[b] (device array of RADIX bytes)
+// and is written to the array at address route[owner] (device array of RADIX addresses; local or
+// peer-mapped memory). status: tiles * RADIX words, tile_counter: one word; both are cleared here.
 template <typename KeyT>
-void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned long long *route,
-                   unsigned long long *status, unsigned int *tile_counter, cudaStream_t stream,
-                   unsigned *launches) {
+void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned char *owner,
+                   const unsigned long long *route, unsigned long long *status, unsigned int *tile_counter,
+                   cudaStream_t stream, unsigned *launches) {
     if (n == 0) return;
     constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;
     const size_t tiles = div_up(n, (size_t)4096 / S);
     MTG_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream));
     MTG_CUDA(cudaMemsetAsync(status, 0, sizeof(unsigned long long) * tiles * RADIX, stream));
     launch_v3<KeyT, false, 256, 16 / S, 3, 0, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
-                                                    tile_counter, 1u, stream);
+                                                    tile_counter, 1u, stream, owner);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }
-template void route_scatter<uint64_t>(const uint64_t *, uint64_t, DigitPass, const unsigned long long *,
-                                      unsigned long long *, unsigned int *, cudaStream_t, unsigned *);
-template void route_scatter<u128>(const u128 *, uint64_t, DigitPass, const unsigned long long *,
-                                  unsigned long long *, unsigned int *, cudaStream_t, unsigned *);
+template void route_scatter<uint64_t>(const uint64_t *, uint64_t, DigitPass, const unsigned char *,
+                                      const unsigned long long *, unsigned long long *, unsigned int *,
+                                      cudaStream_t, unsigned *);
+template void route_scatter<u128>(const u128 *, uint64_t, DigitPass, const unsigned char *,
+                                  const unsigned long long *, unsigned long long *, unsigned int *, cudaStream_t,
+                                  unsigned *);
 
 namespace {
 __global__ void fill_random_kernel(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask,

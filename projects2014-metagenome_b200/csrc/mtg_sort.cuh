@@ -66,12 +66,13 @@ template <typename KeyT>
 void digit_histogram(const KeyT *keys, uint64_t n, DigitPass dp, unsigned long long *hist, cudaStream_t stream,
                      unsigned *launches);
 
-// Grouping + exchange in one kernel: a stable scatter pass on digit dp whose digit-d keys go to the
-// array at address route[d] (device array of 2^bits addresses, local or peer-mapped memory of another
-// GPU). status: sort_status_words(n) words, tile_counter: one word.
+// Grouping + exchange in one kernel: a stable scatter pass in which a key whose digit dp is b goes
+// to owner[b] (device array of RADIX bytes) and is stored into the array at address route[owner]
+// (device array of RADIX addresses, local or peer-mapped memory of another GPU).
+// status: sort_status_words(n) words, tile_counter: one word.
 template <typename KeyT>
-void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned long long *route,
-                   unsigned long long *status, unsigned int *tile_counter, cudaStream_t stream,
-                   unsigned *launches);
+void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned char *owner,
+                   const unsigned long long *route, unsigned long long *status, unsigned int *tile_counter,
+                   cudaStream_t stream, unsigned *launches);
 
 }  // namespace mtg

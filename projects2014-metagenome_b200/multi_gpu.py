@@ -60,19 +60,18 @@ def split_sizes(bucket_counts, ranges):
 
 
 def route_addresses(all_counts, ranges, me, base_ptrs, key_bytes):
-    """Where source rank `me` writes each of its routing buckets (mtg_mg_route). all_counts[s][b] =
-    k-mers of source s in bucket b; destination d's receive buffer (at base_ptrs[d]) holds the
-    sources in rank order, each source's slice its buckets lo_d..hi_d in order.
-    -> (bucket_dst uint64[nb], sizes int64[source][destination])"""
+    """Where source rank `me` writes its k-mers (mtg_mg_route). all_counts[s][b] = k-mers of source s
+    in routing bucket b; destination d's receive buffer (at base_ptrs[d]) holds one slice per
+    source, in rank order. -> (bucket_owner uint32[nb], owner_dst uint64[world],
+    sizes int64[source][destination])"""
     c = np.asarray(all_counts, dtype=np.int64)
     sizes = np.array([[int(c[s, lo:hi].sum()) for lo, hi in ranges] for s in range(c.shape[0])], dtype=np.int64)
-    dst = np.zeros(c.shape[1], dtype=np.uint64)
+    owner = np.zeros(c.shape[1], dtype=np.uint32)
+    dst = np.zeros(len(ranges), dtype=np.uint64)
     for d, (lo, hi) in enumerate(ranges):
-        off = int(sizes[:me, d].sum())
-        for b in range(lo, hi):
-            dst[b] = int(base_ptrs[d]) + off * key_bytes
-            off += int(c[me, b])
-    return dst, sizes
+        owner[lo:hi] = d
+        dst[d] = int(base_ptrs[d]) + int(sizes[:me, d].sum()) * key_bytes
+    return owner, dst, sizes
 
 
 def concat_chunks(chunks):
@@ -138,8 +137,8 @@ class RangedRank:
         self.n_extracted = n
         return counts
 
-    def route(self, bucket_dst):
-        self.ctor.mg_route(bucket_dst)
+    def route(self, bucket_owner, owner_dst):
+        self.ctor.mg_route(bucket_owner, owner_dst)
 
     def collect(self, keys):
         self._keep = keys   # the library copies; keep the tensor alive until the call returns
@@ -207,13 +206,13 @@ class VirtualBuild:
             counts = np.stack([r.count() for r in self.ranks])
             self.ranges = plan_ranges(counts.sum(axis=0), g)
             words = self.ranks[0].words
-            _, sizes = route_addresses(counts, self.ranges, 0, [0] * g, 8 * words)
+            _, _, sizes = route_addresses(counts, self.ranges, 0, [0] * g, 8 * words)
             routed = [torch.empty((int(sizes[:, d].sum()), words) if words > 1 else (int(sizes[:, d].sum()),),
                                   dtype=torch.int64, device=self.ranks[0].device) for d in range(g)]
             torch.cuda.synchronize()
             for s_, r in enumerate(self.ranks):
-                dst, _ = route_addresses(counts, self.ranges, s_, [t.data_ptr() for t in routed], 8 * words)
-                r.route(dst)
+                owner, dst, _ = route_addresses(counts, self.ranges, s_, [t.data_ptr() for t in routed], 8 * words)
+                r.route(owner, dst)
         else:
             ex = [r.extract() for r in self.ranks]
             hist = np.sum([c for c, _ in ex], axis=0)
@@ -400,13 +399,13 @@ class DistBuild:
         allc = allc.cpu().numpy()
         self.ranges = plan_ranges(allc.sum(axis=0), self.world)
         kb = 8 * self.rank.words
-        _, sizes = route_addresses(allc, self.ranges, self.rank_id, [0] * self.world, kb)
+        _, _, sizes = route_addresses(allc, self.ranges, self.rank_id, [0] * self.world, kb)
         need = int(sizes.sum(axis=0).max()) * kb
         buf, hdl = self._symm_slot(0, max(need, 16))
-        dst, _ = route_addresses(allc, self.ranges, self.rank_id, [int(p) for p in hdl.buffer_ptrs], kb)
+        owner, dst, _ = route_addresses(allc, self.ranges, self.rank_id, [int(p) for p in hdl.buffer_ptrs], kb)
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
-        self.rank.route(dst)
+        self.rank.route(owner, dst)
         hdl.barrier()
         ev1.record()
         ev1.synchronize()

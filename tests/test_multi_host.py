@@ -102,25 +102,22 @@ def test_gloo_world2_routing_and_chunk_gather(world, tmp_path):
 
 
 def test_route_addresses_layout():
-    """mtg_mg_route destinations: every destination buffer is tiled exactly once, sources in rank
-    order, each source's buckets in bucket order."""
+    """mtg_mg_route destinations: every destination buffer is tiled exactly once by the sources'
+    slices, in rank order; every bucket is owned by the rank whose range holds it."""
     rng = np.random.default_rng(3)
     world, nb, kb = 4, 16, 8
     counts = rng.integers(0, 50, (world, nb))
     counts[:, 5] = 0
     ranges = multi_gpu.plan_ranges(counts.sum(axis=0), world)
     bases = [1 << 20, 2 << 20, 3 << 20, 4 << 20]
-    seen = {d: [] for d in range(world)}
+    ends = {d: 0 for d in range(world)}
     for me in range(world):
-        dst, sizes = multi_gpu.route_addresses(counts, ranges, me, bases, kb)
-        assert sizes.shape == (world, world)
+        owner, dst, sizes = multi_gpu.route_addresses(counts, ranges, me, bases, kb)
+        assert sizes.shape == (world, world) and owner.shape == (nb,) and dst.shape == (world,)
         for d, (lo, hi) in enumerate(ranges):
             assert sizes[me, d] == counts[me, lo:hi].sum()
-            for b in range(lo, hi):
-                seen[d].append((int(dst[b]) - bases[d], int(counts[me, b]) * kb, me, b))
-    for d in range(world):
-        off = 0
-        for start, nbytes, me, b in sorted(seen[d], key=lambda t: (t[2], t[3])):
-            assert start == off, (d, me, b)
-            off += nbytes
-        assert off == counts[:, ranges[d][0]:ranges[d][1]].sum() * kb
+            assert all(owner[b] == d for b in range(lo, hi))
+            assert int(dst[d]) - bases[d] == ends[d]     # slices follow each other in rank order
+            ends[d] += int(sizes[me, d]) * kb
+    for d, (lo, hi) in enumerate(ranges):
+        assert ends[d] == counts[:, lo:hi].sum() * kb
