@@ -331,3 +331,55 @@ def test_dna_character_classes():
         reads.append("".join(b))
     check(reads, 9, canonical=True, bits_per_count=8)
     check(reads, 33, canonical=False)
+
+
+# ---- BASELINE.json's full size (cfg #2): size-independent BOSS invariants ---------------------
+
+def _popcount_bits(words, a, b):
+    """number of set bits at positions [a, b) of a little-endian uint64 bit vector"""
+    if b <= a:
+        return 0
+    wa, wb = a >> 6, (b - 1) >> 6
+    w = words[wa:wb + 1].copy()
+    w[0] &= np.uint64(0xFFFFFFFFFFFFFFFF) << np.uint64(a & 63)
+    if b & 63:
+        w[-1] &= (np.uint64(1) << np.uint64(b & 63)) - np.uint64(1)
+    return int(np.bitwise_count(w).sum())
+
+
+def test_full_size_chunk_invariants():
+    """10 M x 150 bp reads, k = 31, canonical (the bench workload). The chunk must be a valid BOSS
+    table: every node except the all-'$' root is entered by exactly one unflagged edge, per last
+    character (the LF mapping the reference's BOSS::initialize relies on, boss.cpp:99-122):
+        #nodes whose last char is c  ==  #rows with W == c (no minus flag)          c = A..T
+    with the node ranges taken from F; plus F monotone and the row count = 1 + root + reals + dummies."""
+    import torch
+    n_reads, L, K, G = 10_000_000, 150, 31, 100_000_000
+    packed = synth.dna_reads_packed_torch(1, n_reads, L, G, 0.005, device="cuda")
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, True, 0)
+    ctor.add_packed_device(packed.data_ptr(), packed.numel(), n_reads * (L - K + 1))
+    torch.cuda.synchronize()
+    chunk = ctor.build_chunk(copy=False)
+    st = chunk.stats
+    n = chunk.n_rows
+    assert st["n_input_kmers"] == n_reads * (L - K + 1)
+    # rows = placeholder + all-'$' root + reals + sinks + sources (the root may be booked as a source level)
+    extra = n - (st["n_real"] + st["n_dummy_sink"] + sum(st["n_dummy_source"]))
+    assert extra in (1, 2)
+    F = [int(x) for x in chunk.F] + [n - 1]
+    assert F[0] == 0 and all(F[i] <= F[i + 1] for i in range(5))
+    last = np.asarray(chunk.last_words, dtype=np.uint64)
+    Ww = np.asarray(chunk.W_words, dtype=np.uint64)[: (n * 4 + 63) // 64]
+    counts = np.zeros(16, dtype=np.int64)
+    for s in range(16):   # 16 nibbles per word
+        counts += np.bincount(((Ww >> np.uint64(4 * s)) & np.uint64(15)).astype(np.uint8), minlength=16)
+    assert counts[5] == 0 and counts[10:].sum() == 0            # codes: 0 '$', 1..4, 6..9 flagged
+    nodes = _popcount_bits(last, 1, n)
+    assert _popcount_bits(last, 0, 1) == 0                      # placeholder row
+    assert nodes - 1 == int(counts[1:5].sum())
+    assert _popcount_bits(last, 1, F[1] + 1) == 1               # the all-'$' root is the only '$'-ending node
+    for c in range(1, 5):
+        assert _popcount_bits(last, F[c] + 1, F[c + 1] + 1) == int(counts[c]), "LF invariant, char %d" % c
+    # every real k-mer and every dummy source has an edge label; sinks and the root row carry '$'
+    assert int(counts[1:5].sum() + counts[6:10].sum()) == st["n_real"] + sum(st["n_dummy_source"]) - (2 - extra)
+    ctor.close()
