@@ -314,76 +314,95 @@ class DistBuild:
     def _exchange(self, send, send_sizes, slot=0):
         """all-to-all of a bucket-grouped tensor; send_sizes[d] rows go to rank d. Returns the rows
         received, ordered by source rank."""
+        recv, sizes = self._exchange_many([(send, send_sizes, slot)])[0]
+        self.last_recv_sizes = sizes
+        return recv
+
+    def _exchange_many(self, items):
+        """Several all-to-alls behind ONE size all-gather and ONE barrier: items = [(send tensor,
+        send_sizes per destination, symmetric slot)]. Returns [(rows received in source-rank order,
+        rows per source)]."""
         torch, dist = self.torch, self.dist
         dev = self.rank.device
-        sizes = torch.tensor(send_sizes, dtype=torch.int64, device=dev)
-        all_sizes = torch.empty((self.world, self.world), dtype=torch.int64, device=dev)
+        ni = len(items)
+        sizes = torch.tensor([list(ss) for _, ss, _ in items], dtype=torch.int64, device=dev)   # [item][dest]
+        all_sizes = torch.empty((self.world, ni, self.world), dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(all_sizes, sizes, group=self.group)   # also orders the ranks: every
-        all_sizes = all_sizes.cpu().numpy()                               # peer has consumed its slot
-        recv_sizes = [int(x) for x in all_sizes[:, self.rank_id]]
-        self.last_recv_sizes = recv_sizes
-        tail = tuple(send.shape[1:])
-        row = 1
-        for t in tail:
-            row *= int(t)
-        own = send_sizes[self.rank_id]
-        self.a2a_bytes += (int(sum(send_sizes)) - own) * send.element_size() * row
+        all_sizes = all_sizes.cpu().numpy()                               # peer has consumed its slots
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        total = int(sum(recv_sizes))
-        if self.use_symm:
-            need = int(all_sizes.sum(axis=0).max()) * send.element_size() * row
-            buf, hdl = self._symm_slot(slot, max(need, 16))
-            send = send.contiguous()
-            cur = torch.cuda.current_stream()
+        out = []
+        if not self.use_symm:
             ev0.record()
-            so = np.concatenate([[0], np.cumsum(send_sizes)])
+            for i, (send, send_sizes, _) in enumerate(items):
+                recv_sizes = [int(x) for x in all_sizes[:, i, self.rank_id]]
+                recv = torch.empty((int(sum(recv_sizes)),) + tuple(send.shape[1:]), dtype=send.dtype, device=dev)
+                dist.all_to_all_single(recv, send.contiguous(), recv_sizes, [int(x) for x in send_sizes],
+                                       group=self.group)
+                out.append((recv, recv_sizes))
+                self.a2a_bytes += (int(sum(send_sizes)) - int(send_sizes[self.rank_id])) * send[0:1].numel() \
+                    * send.element_size() if send.shape[0] else 0
+            ev1.record()
+            ev1.synchronize()
+            self.a2a_ms += ev0.elapsed_time(ev1)
+            return out
+        cur = torch.cuda.current_stream()
+        plans = []
+        for i, (send, send_sizes, slot) in enumerate(items):
+            tail = tuple(send.shape[1:])
+            row = 1
+            for t in tail:
+                row *= int(t)
             esz = send.element_size() * row
-            if self.push_kernel:
-                # one kernel of peer stores (csrc/mtg_peer.cu), every destination served concurrently
-                import ctypes
-                dsts, srcs, nby = [], [], []
+            need = int(all_sizes[:, i, :].sum(axis=0).max()) * esz
+            buf, hdl = self._symm_slot(slot, max(need, 16))
+            plans.append((send.contiguous(), [int(x) for x in send_sizes], tail, row, esz, hdl))
+            self.a2a_bytes += (int(sum(send_sizes)) - int(send_sizes[self.rank_id])) * esz
+        ev0.record()
+        if self.push_kernel:
+            # one kernel of peer stores (csrc/mtg_peer.cu), every destination served concurrently
+            import ctypes
+            dsts, srcs, nby = [], [], []
+            for i, (send, send_sizes, tail, row, esz, hdl) in enumerate(plans):
+                so = np.concatenate([[0], np.cumsum(send_sizes)])
                 for k in range(self.world):
                     d = (self.rank_id + k) % self.world
-                    n_d = int(send_sizes[d])
-                    if n_d == 0:
+                    if send_sizes[d] == 0:
                         continue
-                    off = int(all_sizes[:self.rank_id, d].sum()) * esz     # my rows' place in d's buffer
+                    off = int(all_sizes[:self.rank_id, i, d].sum()) * esz     # my rows' place in d's buffer
                     dsts.append(int(hdl.buffer_ptrs[d]) + off)
                     srcs.append(send.data_ptr() + int(so[d]) * esz)
-                    nby.append(n_d * esz)
-                if dsts:
-                    n = len(dsts)
-                    rc = self.rank.ctor._lib.mtg_peer_push(
-                        ctypes.c_void_p(cur.cuda_stream), n, (ctypes.c_void_p * n)(*dsts),
-                        (ctypes.c_void_p * n)(*srcs), (ctypes.c_uint64 * n)(*nby))
-                    if rc != 0:
-                        raise RuntimeError("mtg_peer_push failed (%d)" % rc)
-            else:
+                    nby.append(send_sizes[d] * esz)
+            if dsts:
+                n = len(dsts)
+                rc = self.rank.ctor._lib.mtg_peer_push(
+                    ctypes.c_void_p(cur.cuda_stream), n, (ctypes.c_void_p * n)(*dsts),
+                    (ctypes.c_void_p * n)(*srcs), (ctypes.c_uint64 * n)(*nby))
+                if rc != 0:
+                    raise RuntimeError("mtg_peer_push failed (%d)" % rc)
+        else:
+            for st in self._streams:
+                st.wait_stream(cur)
+            for i, (send, send_sizes, tail, row, esz, hdl) in enumerate(plans):
+                so = np.concatenate([[0], np.cumsum(send_sizes)])
                 for k in range(self.world):
                     d = (self.rank_id + k) % self.world          # staggered: no peer is hit by all at once
-                    n_d = int(send_sizes[d])
+                    n_d = send_sizes[d]
                     if n_d == 0:
                         continue
-                    off = int(all_sizes[:self.rank_id, d].sum()) * row     # my rows' place in d's buffer
+                    off = int(all_sizes[:self.rank_id, i, d].sum()) * row     # my rows' place in d's buffer
                     dst = hdl.get_buffer(d, (n_d,) + tail, send.dtype, off)
-                    st = self._streams[k]
-                    st.wait_stream(cur)
-                    with torch.cuda.stream(st):
+                    with torch.cuda.stream(self._streams[k]):
                         dst.copy_(send[int(so[d]):int(so[d + 1])], non_blocking=True)
-                for st in self._streams:
-                    cur.wait_stream(st)
-            hdl.barrier()
-            ev1.record()
-            ev1.synchronize()
-            recv = hdl.get_buffer(self.rank_id, (total,) + tail, send.dtype, 0)
-        else:
-            recv = torch.empty((total,) + tail, dtype=send.dtype, device=dev)
-            ev0.record()
-            dist.all_to_all_single(recv, send.contiguous(), recv_sizes, list(send_sizes), group=self.group)
-            ev1.record()
-            ev1.synchronize()
+            for st in self._streams:
+                cur.wait_stream(st)
+        plans[0][5].barrier()
+        ev1.record()
+        ev1.synchronize()
         self.a2a_ms += ev0.elapsed_time(ev1)
-        return recv
+        for i, (send, send_sizes, tail, row, esz, hdl) in enumerate(plans):
+            recv_sizes = [int(x) for x in all_sizes[:, i, self.rank_id]]
+            out.append((hdl.get_buffer(self.rank_id, (int(sum(recv_sizes)),) + tail, send.dtype, 0), recv_sizes))
+        return out
 
     def _route_kmers(self):
         """Exchange #1 fused into the grouping pass: after the per-bucket counts of all ranks are
@@ -458,11 +477,13 @@ class DistBuild:
             dist.all_reduce(hist, group=self.group)
             self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
             xs, rs = split_sizes(xc, self.ranges), split_sizes(rc, self.ranges)
-            rX = self._exchange(X, xs, 1)   # received in rank order = increasing stage-1 key ranges
-            rR = self._exchange(R, rs, 2)   # one sorted run per source rank
-            r_runs = self.last_recv_sizes
-            rXc = self._exchange(Xc, xs, 3) if Xc is not None else None
-            rRc = self._exchange(Rc, rs, 4) if Rc is not None else None
+            # X is received in rank order = increasing stage-1 key ranges; R as one sorted run per source
+            items = [(X, xs, 1), (R, rs, 2)]
+            if Xc is not None:
+                items += [(Xc, xs, 3), (Rc, rs, 4)]
+            got = self._exchange_many(items)
+            rX, rR, r_runs = got[0][0], got[1][0], got[1][1]
+            rXc, rRc = (got[2][0], got[3][0]) if Xc is not None else (None, None)
             self._mark("exchange strands")
             self.rank.merge(rX, rXc, rR, rRc, r_runs)
             del rX, rR, rXc, rRc
