@@ -187,6 +187,16 @@ int mtg_mg_merge(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t n
 /* Sorted distinct target nodes (k-mer minus first char) of this range's k-mers, with the
  * per-bucket counts for routing them to the owner of the node. */
 int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint64_t *n);
+/* mtg_mg_targets with the exchange fused into its scatter pass (cf. mtg_mg_count / mtg_mg_route):
+ * mtg_mg_targets_count computes the target nodes of this range's reals and their counts per routing
+ * bucket (top part_bits of the (k)-char node word); mtg_mg_targets_route scatters them in ONE kernel,
+ * bucket b into the array at owner_dst[bucket_owner[b]]. The caller makes one "owner" per (owner rank,
+ * leading character) SEGMENT: the scatter is stable and the targets of one edge label are sorted, so
+ * every (source, segment) slice is a sorted run, which mtg_mg_dummies merges (run_lengths). Duplicate
+ * targets travel and are folded by mtg_mg_dummies. */
+int mtg_mg_targets_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n);
+int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner /* [2^part_bits] */, uint32_t n_owners,
+                         const uint64_t *owner_dst /* [n_owners] device addresses */);
 /* d_targets_in: all target nodes that fall into this range. Finds the range's dummy sinks
  * (kept inside) and returns its source nodes without incoming edge (forward-lex packing).
  * run_lengths[n_runs] (host, may be NULL): d_targets_in is the concatenation of sorted runs of

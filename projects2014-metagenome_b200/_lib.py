@@ -42,7 +42,7 @@ class MtgChunk(ctypes.Structure):
 EXPORTS = ["mtg_create", "mtg_destroy", "mtg_last_error", "mtg_push_reads",
            "mtg_push_packed_device", "mtg_packed_size", "mtg_pack_reads", "mtg_build_chunk",
            "mtg_build_chunk_device", "mtg_set_stream", "mtg_free_chunk", "mtg_debug_sorted_kmers", "mtg_debug_free", "mtg_debug_sort_u64",
-           "mtg_debug_sort_u128", "mtg_debug_sort_bench", "mtg_debug_unique_bench", "mtg_mg_part_bits", "mtg_mg_extract", "mtg_mg_count", "mtg_mg_route",
+           "mtg_debug_sort_u128", "mtg_debug_sort_bench", "mtg_debug_unique_bench", "mtg_mg_part_bits", "mtg_mg_extract", "mtg_mg_count", "mtg_mg_route", "mtg_mg_targets_count", "mtg_mg_targets_route",
            "mtg_mg_collect", "mtg_mg_strands", "mtg_mg_merge", "mtg_mg_targets", "mtg_mg_dummies", "mtg_mg_build", "mtg_peer_push"]
 
 _lib = None
@@ -109,6 +109,8 @@ def load():
     lib.mtg_mg_extract.argtypes = [ctypes.c_void_p, u64p, vpp, u64p]
     lib.mtg_mg_count.argtypes = [ctypes.c_void_p, u64p, u64p]
     lib.mtg_mg_route.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, u64p]
+    lib.mtg_mg_targets_count.argtypes = [ctypes.c_void_p, u64p, u64p]
+    lib.mtg_mg_targets_route.argtypes = [ctypes.c_void_p, ctypes.POINTER(ctypes.c_uint32), ctypes.c_uint32, u64p]
     lib.mtg_mg_collect.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, u64p]
     lib.mtg_mg_targets.argtypes = [ctypes.c_void_p, u64p, vpp, u64p]
     lib.mtg_peer_push.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(ctypes.c_void_p),
@@ -121,7 +123,7 @@ def load():
                                    u64p, u64p]
     lib.mtg_mg_build.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64,
                                  ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.POINTER(MtgChunk)]
-    for name in ("mtg_mg_extract", "mtg_mg_count", "mtg_mg_route", "mtg_mg_collect", "mtg_mg_strands", "mtg_mg_merge", "mtg_mg_targets", "mtg_mg_dummies", "mtg_mg_build"):
+    for name in ("mtg_mg_extract", "mtg_mg_count", "mtg_mg_route", "mtg_mg_targets_count", "mtg_mg_targets_route", "mtg_mg_collect", "mtg_mg_strands", "mtg_mg_merge", "mtg_mg_targets", "mtg_mg_dummies", "mtg_mg_build"):
         getattr(lib, name).restype = ctypes.c_int
     _lib = lib
     return lib

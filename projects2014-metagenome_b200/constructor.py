@@ -153,6 +153,7 @@ class BOSSChunkConstructor:
         self._lib = _lib.load()
         self._ctx = ctypes.c_void_p()
         self._k = int(k)
+        self._tight_bits = 2 if alphabet == "DNA" else 5   # bits per character of the sort key (alphabets.hpp)
         prm = MtgParams(k=int(k), alphabet=_lib.ALPHABETS[alphabet],
                         both_strands=int(bool(both_strands)), bits_per_count=int(bits_per_count),
                         filter_suffix=filter_suffix.encode() if filter_suffix else None,
@@ -170,6 +171,9 @@ class BOSSChunkConstructor:
 
     def get_k(self):
         return self._k
+
+    def tight_bits(self):
+        return self._tight_bits
 
     def _check(self, rc):
         if rc != _lib.MTG_OK:
@@ -288,6 +292,21 @@ class BOSSChunkConstructor:
         assert own.shape[0] == 1 << self.mg_part_bits()
         self._check(self._lib.mtg_mg_route(self._ctx, own.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
                                            dst.shape[0], dst.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
+
+    def mg_targets_count(self):
+        """target nodes of this range's reals + their per-bucket counts -> (bucket_counts, n)"""
+        counts = np.zeros(1 << self.mg_part_bits(), dtype=np.uint64)
+        n = ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_targets_count(self._ctx, counts.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)),
+                                                   ctypes.byref(n)))
+        return counts, n.value
+
+    def mg_targets_route(self, bucket_owner, owner_dst):
+        own = np.ascontiguousarray(bucket_owner, dtype=np.uint32)
+        dst = np.ascontiguousarray(owner_dst, dtype=np.uint64)
+        assert own.shape[0] == 1 << self.mg_part_bits()
+        self._check(self._lib.mtg_mg_targets_route(self._ctx, own.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
+                                                   dst.shape[0], dst.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
 
     def mg_collect(self, dptr, n):
         m = ctypes.c_uint64()

@@ -211,7 +211,7 @@ struct mtg_ctx {
     struct Mg {
         DevBuf keys, targets, tset, sinks, src, rkeys, rcounts;
         RealSet reals;
-        uint64_t nt = 0, n_sink = 0, n_src = 0, n_input = 0, n_routed = 0;
+        uint64_t nt = 0, n_sink = 0, n_src = 0, n_input = 0, n_routed = 0, n_routed_targets = 0;
     } mg;
 };
 
@@ -1459,33 +1459,77 @@ void mg_count_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, uint64_t 
     ctx->segs.clear();
 }
 
+// one scatter kernel: key with digit dp == b -> array at owner_dst[bucket_owner[b]]
+template <typename KeyT>
+void route_buffer(mtg_ctx *ctx, const KeyT *keys, uint64_t n, DigitPass dp, uint32_t nb, const uint32_t *bucket_owner,
+                  uint32_t n_owners, const uint64_t *owner_dst) {
+    cudaStream_t s = ctx->stream;
+    if (!n) return;
+    // one staging block: RADIX addresses followed by RADIX owner bytes
+    std::vector<unsigned long long> h(RADIX + RADIX / 8, 0ull);
+    unsigned char *ho = reinterpret_cast<unsigned char *>(h.data() + RADIX);
+    for (uint32_t i = 0; i < n_owners; ++i) h[i] = owner_dst[i];
+    for (uint32_t i = 0; i < nb; ++i) ho[i] = (unsigned char)bucket_owner[i];
+    DevBuf route(8 * (RADIX + RADIX / 8), s), tc(sizeof(unsigned int), s);
+    DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
+    MTG_CUDA(cudaMemcpyAsync(route.p, h.data(), 8 * (RADIX + RADIX / 8), cudaMemcpyHostToDevice, s));
+    route_scatter<KeyT>(keys, n, dp, reinterpret_cast<const unsigned char *>(route.as<unsigned long long>() + RADIX),
+                        route.as<unsigned long long>(), status.as<unsigned long long>(), tc.as<unsigned int>(), s,
+                        &ctx->launches);
+    MTG_CUDA(cudaStreamSynchronize(s));   // `h` and the scratch outlive the kernel
+}
+
 template <typename KeyT>
 void mg_route_impl(mtg_ctx *ctx, uint32_t pb, const uint32_t *bucket_owner, uint32_t n_owners,
                    const uint64_t *owner_dst) {
-    cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
-    const uint64_t n = ctx->mg.n_routed;
-    if (n) {
-        const uint32_t nb = 1u << pb;
-        // one staging block: RADIX addresses followed by RADIX owner bytes
-        std::vector<unsigned long long> h(RADIX + RADIX / 8, 0ull);
-        unsigned char *ho = reinterpret_cast<unsigned char *>(h.data() + RADIX);
-        for (uint32_t i = 0; i < n_owners; ++i) h[i] = owner_dst[i];
-        for (uint32_t i = 0; i < nb; ++i) ho[i] = (unsigned char)bucket_owner[i];
-        DevBuf route(8 * (RADIX + RADIX / 8), s), tc(sizeof(unsigned int), s);
-        DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
-        MTG_CUDA(cudaMemcpyAsync(route.p, h.data(), 8 * (RADIX + RADIX / 8), cudaMemcpyHostToDevice, s));
-        // pb = 0: one bucket, a 1-bit digit above the key bits (always 0) keeps the pass generic
-        const DigitPass dp = pb ? DigitPass{0, (int)(al.K * al.L - pb), (int)pb}
-                                : DigitPass{0, (int)(8 * sizeof(KeyT) - 1), 1};
-        route_scatter<KeyT>(ctx->mg.keys.as<KeyT>(), n, dp,
-                            reinterpret_cast<const unsigned char *>(route.as<unsigned long long>() + RADIX),
-                            route.as<unsigned long long>(), status.as<unsigned long long>(), tc.as<unsigned int>(),
-                            s, &ctx->launches);
-        MTG_CUDA(cudaStreamSynchronize(s));   // `h` and the scratch outlive the kernel
-    }
+    // pb = 0: one bucket, a 1-bit digit above the key bits (always 0) keeps the pass generic
+    const DigitPass dp = pb ? DigitPass{0, (int)(al.K * al.L - pb), (int)pb}
+                            : DigitPass{0, (int)(8 * sizeof(KeyT) - 1), 1};
+    route_buffer<KeyT>(ctx, ctx->mg.keys.as<KeyT>(), ctx->mg.n_routed, dp, 1u << pb, bucket_owner, n_owners, owner_dst);
     ctx->mg.keys.release();
     ctx->mg.n_routed = 0;
+}
+
+// Exchange #3 the same way: target nodes of this range's reals, counted per routing bucket, then
+// scattered by ONE kernel into the owners' buffers. The caller's "owners" are SEGMENTS (owner rank x
+// leading character): within a segment the stable scatter keeps the order of the reals, i.e. the
+// targets of one edge label, which are sorted -- every (source, segment) slice arrives as a sorted run.
+template <typename KeyT>
+void mg_targets_count_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, uint64_t *n_out) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const uint64_t m = ctx->mg.reals.m;
+    DevBuf t0(sizeof(KeyT) * std::max<uint64_t>(m, 1), s);
+    target_nodes<KeyT>(ctx->mg.reals.keys.as<KeyT>(), m, al, t0.as<KeyT>(), s, &ctx->launches);
+    const uint32_t nb = 1u << pb;
+    for (uint32_t i = 0; i < nb; ++i) bucket_counts[i] = 0;
+    if (pb == 0 || m == 0) {
+        bucket_counts[0] = m;
+    } else {
+        DevBuf hist(sizeof(unsigned long long) * RADIX, s);
+        digit_histogram<KeyT>(t0.as<KeyT>(), m, DigitPass{0, (int)((al.K - 1) * al.L - pb), (int)pb},
+                              hist.as<unsigned long long>(), s, &ctx->launches);
+        std::vector<unsigned long long> h(RADIX);
+        MTG_CUDA(cudaMemcpyAsync(h.data(), hist.p, 8 * RADIX, cudaMemcpyDeviceToHost, s));
+        MTG_CUDA(cudaStreamSynchronize(s));
+        for (uint32_t i = 0; i < nb; ++i) bucket_counts[i] = h[i];
+    }
+    ctx->mg.targets = std::move(t0);
+    ctx->mg.n_routed_targets = m;
+    *n_out = m;
+}
+
+template <typename KeyT>
+void mg_targets_route_impl(mtg_ctx *ctx, uint32_t pb, const uint32_t *bucket_owner, uint32_t n_owners,
+                           const uint64_t *owner_dst) {
+    const Alpha al = ctx->al;
+    const DigitPass dp = pb ? DigitPass{0, (int)((al.K - 1) * al.L - pb), (int)pb}
+                            : DigitPass{0, (int)(8 * sizeof(KeyT) - 1), 1};
+    route_buffer<KeyT>(ctx, ctx->mg.targets.as<KeyT>(), ctx->mg.n_routed_targets, dp, 1u << pb, bucket_owner, n_owners,
+                       owner_dst);
+    ctx->mg.targets.release();
+    ctx->mg.n_routed_targets = 0;
 }
 
 template <typename KeyT>
@@ -1879,6 +1923,33 @@ int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint
     MG_GUARD(ctx, {
         if (wide) mg_targets_impl<u128>(ctx, mg_part_bits(ctx), bucket_counts, d_targets, n);
         else mg_targets_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_counts, d_targets, n);
+    })
+}
+
+static int check_route_args(mtg_ctx *ctx, bool wide, const uint32_t *bucket_owner, uint32_t n_owners,
+                            const uint64_t *owner_dst) {
+    if (!bucket_owner || !owner_dst || n_owners == 0 || n_owners > 256) return fail(ctx, MTG_ERR_BAD_ARG, "bad owner table");
+    const uint32_t w = wide ? 16 : 8;
+    for (uint32_t i = 0; i < n_owners; ++i)
+        if (owner_dst[i] % w) return fail(ctx, MTG_ERR_BAD_ARG, "destinations must be key-aligned");
+    for (uint32_t i = 0; i < (1u << mg_part_bits(ctx)); ++i)
+        if (bucket_owner[i] >= n_owners) return fail(ctx, MTG_ERR_BAD_ARG, "bucket owner out of range");
+    return MTG_OK;
+}
+
+int mtg_mg_targets_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n) {
+    MG_GUARD(ctx, {
+        if (!bucket_counts || !n) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+        if (wide) mg_targets_count_impl<u128>(ctx, mg_part_bits(ctx), bucket_counts, n);
+        else mg_targets_count_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_counts, n);
+    })
+}
+
+int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner, uint32_t n_owners, const uint64_t *owner_dst) {
+    MG_GUARD(ctx, {
+        if (int rc = check_route_args(ctx, wide, bucket_owner, n_owners, owner_dst)) return rc;
+        if (wide) mg_targets_route_impl<u128>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
+        else mg_targets_route_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
     })
 }
 

@@ -74,6 +74,35 @@ def route_addresses(all_counts, ranges, me, base_ptrs, key_bytes):
     return owner, dst, sizes
 
 
+def route_segments(all_counts, ranges, me, base_ptrs, key_bytes, char_shift):
+    """Plan of mtg_mg_targets_route for source rank `me`. A SEGMENT is the part of a destination's
+    bucket range that shares one leading character (bucket >> char_shift): a source's slice of a
+    segment arrives as a sorted run. Destination d's buffer holds its segments in order, each
+    segment the slices of all sources in rank order.
+    -> (bucket_seg uint32[nb], seg_dst uint64[n_seg], runs[d] = run lengths at destination d in
+    buffer order, sizes int64[source][destination])"""
+    c = np.asarray(all_counts, dtype=np.int64)
+    world, nb = c.shape[0], c.shape[1]
+    bucket_seg = np.zeros(nb, dtype=np.uint32)
+    seg_dst, runs, sizes = [], [], np.zeros((world, len(ranges)), dtype=np.int64)
+    for d, (lo, hi) in enumerate(ranges):
+        off, runs_d = 0, []
+        b = lo
+        while b < hi:
+            e = min(hi, ((b >> char_shift) + 1) << char_shift)       # end of this character's buckets
+            per_src = c[:, b:e].sum(axis=1)
+            bucket_seg[b:e] = len(seg_dst)
+            seg_dst.append(int(base_ptrs[d]) + (off + int(per_src[:me].sum())) * key_bytes)
+            runs_d += [int(x) for x in per_src]
+            off += int(per_src.sum())
+            sizes[:, d] += per_src
+            b = e
+        runs.append(runs_d)
+    if not seg_dst:
+        seg_dst = [0]
+    return bucket_seg, np.asarray(seg_dst, dtype=np.uint64), runs, sizes
+
+
 def concat_chunks(chunks):
     """Host concatenation, exactly BOSS::Chunk::extend in rank (= key range) order."""
     full = chunks[0]
@@ -162,6 +191,19 @@ class RangedRank:
         self._keep = None
         return self.n_real
 
+    def targets_count(self):
+        counts, n = self.ctor.mg_targets_count()
+        return counts
+
+    def targets_route(self, bucket_seg, seg_dst):
+        self.ctor.mg_targets_route(bucket_seg, seg_dst)
+
+    def char_shift(self):
+        """routing-bucket bits below the leading character of a node word, or None if a bucket does
+        not resolve the character (then the targets are exchanged as grouped, folded slices)"""
+        pb, L = self.ctor.mg_part_bits(), self.ctor.tight_bits()
+        return pb - L if pb >= L else None
+
     def targets(self):
         counts, ptr, n = self.ctor.mg_targets()
         return counts, as_tensor(ptr, n, self.words, self.device)
@@ -241,11 +283,23 @@ class VirtualBuild:
             for d, r in enumerate(self.ranks):
                 r.merge(*recv[d], r_runs=[ro[s][d][1] - ro[s][d][0] for s in range(g)])
             del recv, st
-        tg = [r.targets() for r in self.ranks]
-        toffs = [_bucket_offsets(c, self.ranges) for c, _ in tg]
-        recv = [torch.cat([tg[s][1][toffs[s][d][0]:toffs[s][d][1]] for s in range(g)]) for d in range(g)]
+        csh = self.ranks[0].char_shift()
+        if self.fused_route and csh is not None:
+            tcounts = np.stack([r.targets_count() for r in self.ranks])
+            words = self.ranks[0].words
+            _, _, runs, sizes = route_segments(tcounts, self.ranges, 0, [0] * g, 8 * words, csh)
+            recv = [torch.empty((int(sizes[:, d].sum()), words) if words > 1 else (int(sizes[:, d].sum()),),
+                                dtype=torch.int64, device=self.ranks[0].device) for d in range(g)]
+            torch.cuda.synchronize()
+            for s_, r in enumerate(self.ranks):
+                seg, dst, _, _ = route_segments(tcounts, self.ranges, s_, [t.data_ptr() for t in recv], 8 * words, csh)
+                r.targets_route(seg, dst)
+        else:
+            tg = [r.targets() for r in self.ranks]
+            toffs = [_bucket_offsets(c, self.ranges) for c, _ in tg]
+            recv = [torch.cat([tg[s][1][toffs[s][d][0]:toffs[s][d][1]] for s in range(g)]) for d in range(g)]
+            runs = [[toffs[s][d][1] - toffs[s][d][0] for s in range(g)] for d in range(g)]
         torch.cuda.synchronize()
-        runs = [[toffs[s][d][1] - toffs[s][d][0] for s in range(g)] for d in range(g)]
         src = [r.dummies(recv[d], runs[d]).clone() for d, r in enumerate(self.ranks)]
         all_src = torch.cat(src)
         torch.cuda.synchronize()
@@ -437,6 +491,37 @@ class DistBuild:
         self._mark("route (group + exchange)")
         return recv
 
+    def _route_targets(self, char_shift):
+        """Exchange #3 fused into the scatter pass of the targets (mtg_mg_targets_route): every
+        (source, owner, leading character) slice lands as a sorted run in the owner's buffer."""
+        torch, dist = self.torch, self.dist
+        dev = self.rank.device
+        counts = self.rank.targets_count()
+        self._mark("targets (count)")
+        mine = torch.from_numpy(counts.astype(np.int64)).to(dev)
+        allc = torch.empty((self.world, mine.numel()), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allc, mine, group=self.group)   # also: every peer is done with slot 5
+        allc = allc.cpu().numpy()
+        kb = 8 * self.rank.words
+        _, _, _, sizes = route_segments(allc, self.ranges, self.rank_id, [0] * self.world, kb, char_shift)
+        need = int(sizes.sum(axis=0).max()) * kb
+        buf, hdl = self._symm_slot(5, max(need, 16))
+        seg, dst, runs, _ = route_segments(allc, self.ranges, self.rank_id, [int(p) for p in hdl.buffer_ptrs], kb,
+                                           char_shift)
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+        self.rank.targets_route(seg, dst)
+        hdl.barrier()
+        ev1.record()
+        ev1.synchronize()
+        self.a2a_ms += ev0.elapsed_time(ev1)
+        self.a2a_bytes += int(sizes[self.rank_id].sum() - sizes[self.rank_id, self.rank_id]) * kb
+        total = int(sizes[:, self.rank_id].sum())
+        shape = (total, self.rank.words) if self.rank.words > 1 else (total,)
+        tin = hdl.get_buffer(self.rank_id, shape, torch.int64, 0)
+        self._mark("route targets (scatter + exchange)")
+        return tin, runs[self.rank_id]
+
     def _mark(self, name):
         """phase timing (CUDA events on the current stream, which the library shares in bench.py)"""
         if getattr(self, "phase_events", None) is not None:
@@ -488,11 +573,16 @@ class DistBuild:
             self.rank.merge(rX, rXc, rR, rRc, r_runs)
             del rX, rR, rXc, rRc
             self._mark("merge strands")
-        tcounts, tg = self.rank.targets()
-        self._mark("targets")
-        tin = self._exchange(tg, split_sizes(tcounts, self.ranges))
-        self._mark("exchange targets")
-        src = self.rank.dummies(tin, self.last_recv_sizes)   # one sorted run per source rank
+        csh = self.rank.char_shift()
+        if self.use_symm and self.fused_route and csh is not None:
+            tin, runs = self._route_targets(csh)
+        else:
+            tcounts, tg = self.rank.targets()
+            self._mark("targets")
+            tin = self._exchange(tg, split_sizes(tcounts, self.ranges))
+            runs = self.last_recv_sizes                      # one sorted run per source rank
+            self._mark("exchange targets")
+        src = self.rank.dummies(tin, runs)
         self._mark("dummies")
         n_src = torch.tensor([src.shape[0]], dtype=torch.int64, device=dev)
         all_n = torch.empty(self.world, dtype=torch.int64, device=dev)

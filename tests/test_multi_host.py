@@ -121,3 +121,35 @@ def test_route_addresses_layout():
             ends[d] += int(sizes[me, d]) * kb
     for d, (lo, hi) in enumerate(ranges):
         assert ends[d] == counts[:, lo:hi].sum() * kb
+
+
+def test_route_segments_layout():
+    """mtg_mg_targets_route plan: segments split a destination's buckets at leading-character
+    boundaries; the destination buffer is tiled once, segment by segment, sources in rank order."""
+    rng = np.random.default_rng(4)
+    world, nb, kb, csh = 3, 16, 16, 2          # 4 characters x 4 buckets
+    counts = rng.integers(0, 40, (world, nb))
+    ranges = [(0, 6), (6, 7), (7, 16)]
+    bases = [1 << 20, 2 << 20, 3 << 20]
+    plans = [multi_gpu.route_segments(counts, ranges, me, bases, kb, csh) for me in range(world)]
+    seg0, _, runs, sizes = plans[0]
+    assert all(np.array_equal(p[0], seg0) for p in plans)
+    # buckets of one segment share destination and character; segment ids increase with the bucket
+    for b in range(nb - 1):
+        same = (b >> csh == (b + 1) >> csh) and any(lo <= b and b + 1 < hi for lo, hi in ranges)
+        assert (seg0[b] == seg0[b + 1]) == same
+    nseg = int(seg0.max()) + 1
+    for d, (lo, hi) in enumerate(ranges):
+        assert sizes[:, d].tolist() == counts[:, lo:hi].sum(axis=1).tolist()
+        segs = sorted(set(int(x) for x in seg0[lo:hi]))
+        assert len(runs[d]) == world * len(segs)
+        off = 0
+        for j, sg in enumerate(segs):
+            bs = [b for b in range(lo, hi) if seg0[b] == sg]
+            for me in range(world):
+                n_me = int(counts[me, bs].sum())
+                assert int(plans[me][1][sg]) == bases[d] + off * kb
+                assert runs[d][j * world + me] == n_me
+                off += n_me
+        assert off == counts[:, lo:hi].sum()
+    assert nseg == len(plans[0][1])
