@@ -200,9 +200,12 @@ int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner /* [2^part_b
 /* d_targets_in: all target nodes that fall into this range. Finds the range's dummy sinks
  * (kept inside) and returns its source nodes without incoming edge (forward-lex packing).
  * run_lengths[n_runs] (host, may be NULL): d_targets_in is the concatenation of sorted runs of
- * these lengths (every rank sends its targets sorted) -- they are merged instead of re-sorted. */
+ * these lengths (every rank sends its targets sorted) -- they are merged instead of re-sorted.
+ * runs_per_set (0 = all runs overlap): every runs_per_set consecutive runs hold keys that sort
+ * before those of the next set (mtg_mg_targets_route: one set per leading character), so only the
+ * runs inside a set are merged. */
 int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, const uint64_t *run_lengths,
-                   uint32_t n_runs, void **d_src_nodes, uint64_t *n_src, uint64_t *n_sink);
+                   uint32_t n_runs, uint32_t runs_per_set, void **d_src_nodes, uint64_t *n_src, uint64_t *n_sink);
 /* d_all_src_nodes: the gathered source nodes of every range. Emits the chunk of bucket range
  * [lo_bucket, hi_bucket); first_range adds the all-'$' row (boss_chunk_construct.cpp:310-315). */
 int mtg_mg_build(mtg_ctx *ctx, const void *d_all_src_nodes, uint64_t n_all, uint64_t lo_bucket,

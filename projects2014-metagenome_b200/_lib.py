@@ -119,7 +119,7 @@ def load():
     lib.mtg_mg_strands.argtypes = [ctypes.c_void_p, u64p, u64p, vpp, vpp, u64p, vpp, vpp, u64p]
     lib.mtg_mg_merge.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64,
                                  ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, u64p, ctypes.c_uint32, u64p]
-    lib.mtg_mg_dummies.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, u64p, ctypes.c_uint32, vpp,
+    lib.mtg_mg_dummies.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, u64p, ctypes.c_uint32, ctypes.c_uint32, vpp,
                                    u64p, u64p]
     lib.mtg_mg_build.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint64, ctypes.c_uint64,
                                  ctypes.c_uint64, ctypes.c_int, ctypes.c_int, ctypes.POINTER(MtgChunk)]

@@ -341,13 +341,14 @@ class BOSSChunkConstructor:
                                              ctypes.byref(ptr), ctypes.byref(n)))
         return counts, ptr.value or 0, n.value
 
-    def mg_dummies(self, dptr, n_in, runs=None):
-        """runs: lengths of the sorted runs dptr consists of (one per source rank), or None"""
+    def mg_dummies(self, dptr, n_in, runs=None, runs_per_set=0):
+        """runs: lengths of the sorted runs dptr consists of, or None; runs_per_set: consecutive runs
+        that overlap in key space (0 = all; sets are ordered and disjoint)"""
         ptr, n_src, n_sink = ctypes.c_void_p(), ctypes.c_uint64(), ctypes.c_uint64()
         rl = np.ascontiguousarray(runs if runs is not None else [], dtype=np.uint64)
         self._check(self._lib.mtg_mg_dummies(self._ctx, ctypes.c_void_p(dptr), n_in,
                                              rl.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64)) if len(rl) else None,
-                                             len(rl), ctypes.byref(ptr),
+                                             len(rl), int(runs_per_set), ctypes.byref(ptr),
                                              ctypes.byref(n_src), ctypes.byref(n_sink)))
         return ptr.value or 0, n_src.value, n_sink.value
 

@@ -1575,50 +1575,68 @@ void mg_targets_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **
 template <typename KeyT>
 // The runs start in `a` (or, with ext_a, in the caller's receive buffer: the first level of the
 // merge tree then reads them from there and no staging copy is made); the result ends in `a`.
+// group > 0: every `group` consecutive runs form a set whose keys all sort before those of the next
+// set (targets of one leading character): only the runs inside a set are merged.
 void merge_runs(mtg_ctx *ctx, DevBuf &a, DevBuf &b, std::vector<uint64_t> runs, DevBuf *ca = nullptr,
-                DevBuf *cb = nullptr, const void *ext_a = nullptr, const uint32_t *ext_ca = nullptr) {
+                DevBuf *cb = nullptr, const void *ext_a = nullptr, const uint32_t *ext_ca = nullptr,
+                uint32_t group = 0) {
     cudaStream_t s = ctx->stream;
     uint64_t total = 0;
     for (uint64_t r : runs) total += r;
-    if (ext_a && runs.size() <= 1) {
-        MTG_CUDA(cudaMemcpyAsync(a.p, ext_a, sizeof(KeyT) * total, cudaMemcpyDeviceToDevice, s));
-        if (ca) MTG_CUDA(cudaMemcpyAsync(ca->p, ext_ca, 4 * total, cudaMemcpyDeviceToDevice, s));
+    if (group == 0 || group > runs.size()) group = (uint32_t)std::max<size_t>(runs.size(), 1);
+    std::vector<std::vector<uint64_t>> sets;
+    for (size_t i = 0; i < runs.size(); i += group)
+        sets.emplace_back(runs.begin() + i, runs.begin() + std::min(runs.size(), i + group));
+    auto unmerged = [&]() {
+        for (auto &g : sets)
+            if (g.size() > 1) return true;
+        return false;
+    };
+    if (!unmerged()) {
+        if (ext_a) {
+            MTG_CUDA(cudaMemcpyAsync(a.p, ext_a, sizeof(KeyT) * total, cudaMemcpyDeviceToDevice, s));
+            if (ca) MTG_CUDA(cudaMemcpyAsync(ca->p, ext_ca, 4 * total, cudaMemcpyDeviceToDevice, s));
+        }
         return;
     }
     DevBuf part(8 * merge_partition_words(total), s);
     bool from_ext = ext_a != nullptr;
-    while (runs.size() > 1) {
-        std::vector<uint64_t> next;
+    while (unmerged()) {
         uint64_t off = 0;
         const KeyT *ik = from_ext ? static_cast<const KeyT *>(ext_a) : a.as<KeyT>();
         const uint32_t *ic = !ca ? nullptr : from_ext ? ext_ca : ca->as<uint32_t>();
         KeyT *ok = from_ext ? a.as<KeyT>() : b.as<KeyT>();
         uint32_t *oc = !ca ? nullptr : from_ext ? ca->as<uint32_t>() : cb->as<uint32_t>();
-        for (size_t i = 0; i < runs.size(); i += 2) {
-            const uint64_t la = runs[i], lb = i + 1 < runs.size() ? runs[i + 1] : 0;
-            if (lb == 0 || la == 0) {
-                MTG_CUDA(cudaMemcpyAsync(ok + off, ik + off, sizeof(KeyT) * (la + lb), cudaMemcpyDeviceToDevice, s));
-                if (ca) MTG_CUDA(cudaMemcpyAsync(oc + off, ic + off, 4 * (la + lb), cudaMemcpyDeviceToDevice, s));
-            } else {
-                merge_sorted<KeyT>(ik + off, la, ik + off + la, lb, ca ? ic + off : nullptr,
-                                   ca ? ic + off + la : nullptr, ok + off, ca ? oc + off : nullptr,
-                                   part.as<uint64_t>(), s, &ctx->launches);
+        for (auto &g : sets) {
+            std::vector<uint64_t> next;
+            for (size_t i = 0; i < g.size(); i += 2) {
+                const uint64_t la = g[i], lb = i + 1 < g.size() ? g[i + 1] : 0;
+                if (lb == 0 || la == 0) {
+                    if (la + lb) {
+                        MTG_CUDA(cudaMemcpyAsync(ok + off, ik + off, sizeof(KeyT) * (la + lb), cudaMemcpyDeviceToDevice, s));
+                        if (ca) MTG_CUDA(cudaMemcpyAsync(oc + off, ic + off, 4 * (la + lb), cudaMemcpyDeviceToDevice, s));
+                    }
+                } else {
+                    merge_sorted<KeyT>(ik + off, la, ik + off + la, lb, ca ? ic + off : nullptr,
+                                       ca ? ic + off + la : nullptr, ok + off, ca ? oc + off : nullptr,
+                                       part.as<uint64_t>(), s, &ctx->launches);
+                }
+                next.push_back(la + lb);
+                off += la + lb;
             }
-            next.push_back(la + lb);
-            off += la + lb;
+            g.swap(next);
         }
         if (!from_ext) {
             std::swap(a, b);
             if (ca) std::swap(*ca, *cb);
         }
         from_ext = false;
-        runs.swap(next);
     }
 }
 
 template <typename KeyT>
 void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, const uint64_t *run_lengths, uint32_t n_runs,
-                     void **d_src, uint64_t *n_src, uint64_t *n_sink_out) {
+                     uint32_t runs_per_set, void **d_src, uint64_t *n_src, uint64_t *n_sink_out) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const uint32_t K = al.K, L = al.L;
@@ -1635,7 +1653,7 @@ void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, const uint64
         if (run_lengths && n_runs && run_total == n_in) {
             // every source sends its targets sorted: merge the runs (read from the receive buffer)
             merge_runs<KeyT>(ctx, t0, t1, std::vector<uint64_t>(run_lengths, run_lengths + n_runs), nullptr, nullptr,
-                             d_in);
+                             d_in, nullptr, runs_per_set);
         } else {
             SortPlan plan;
             plan.n = 0;
@@ -1954,10 +1972,10 @@ int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner, uint32_t n_
 }
 
 int mtg_mg_dummies(mtg_ctx *ctx, const void *d_targets_in, uint64_t n_in, const uint64_t *run_lengths,
-                   uint32_t n_runs, void **d_src_nodes, uint64_t *n_src, uint64_t *n_sink) {
+                   uint32_t n_runs, uint32_t runs_per_set, void **d_src_nodes, uint64_t *n_src, uint64_t *n_sink) {
     MG_GUARD(ctx, {
-        if (wide) mg_dummies_impl<u128>(ctx, d_targets_in, n_in, run_lengths, n_runs, d_src_nodes, n_src, n_sink);
-        else mg_dummies_impl<uint64_t>(ctx, d_targets_in, n_in, run_lengths, n_runs, d_src_nodes, n_src, n_sink);
+        if (wide) mg_dummies_impl<u128>(ctx, d_targets_in, n_in, run_lengths, n_runs, runs_per_set, d_src_nodes, n_src, n_sink);
+        else mg_dummies_impl<uint64_t>(ctx, d_targets_in, n_in, run_lengths, n_runs, runs_per_set, d_src_nodes, n_src, n_sink);
     })
 }
 

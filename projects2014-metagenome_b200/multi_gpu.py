@@ -208,9 +208,9 @@ class RangedRank:
         counts, ptr, n = self.ctor.mg_targets()
         return counts, as_tensor(ptr, n, self.words, self.device)
 
-    def dummies(self, targets_in, runs=None):
+    def dummies(self, targets_in, runs=None, runs_per_set=0):
         n = targets_in.shape[0]
-        ptr, n_src, n_sink = self.ctor.mg_dummies(targets_in.data_ptr() if n else 0, n, runs)
+        ptr, n_src, n_sink = self.ctor.mg_dummies(targets_in.data_ptr() if n else 0, n, runs, runs_per_set)
         self.n_sink = n_sink
         return as_tensor(ptr, n_src, self.words, self.device)
 
@@ -294,13 +294,15 @@ class VirtualBuild:
             for s_, r in enumerate(self.ranks):
                 seg, dst, _, _ = route_segments(tcounts, self.ranges, s_, [t.data_ptr() for t in recv], 8 * words, csh)
                 r.targets_route(seg, dst)
+            per_set = g
         else:
+            per_set = 0
             tg = [r.targets() for r in self.ranks]
             toffs = [_bucket_offsets(c, self.ranges) for c, _ in tg]
             recv = [torch.cat([tg[s][1][toffs[s][d][0]:toffs[s][d][1]] for s in range(g)]) for d in range(g)]
             runs = [[toffs[s][d][1] - toffs[s][d][0] for s in range(g)] for d in range(g)]
         torch.cuda.synchronize()
-        src = [r.dummies(recv[d], runs[d]).clone() for d, r in enumerate(self.ranks)]
+        src = [r.dummies(recv[d], runs[d], per_set).clone() for d, r in enumerate(self.ranks)]
         all_src = torch.cat(src)
         torch.cuda.synchronize()
         chunks = [r.build(all_src, self.ranges[d][0], self.ranges[d][1], d == 0)
@@ -576,13 +578,15 @@ class DistBuild:
         csh = self.rank.char_shift()
         if self.use_symm and self.fused_route and csh is not None:
             tin, runs = self._route_targets(csh)
+            per_set = self.world                             # one set of `world` runs per leading character
         else:
+            per_set = 0
             tcounts, tg = self.rank.targets()
             self._mark("targets")
             tin = self._exchange(tg, split_sizes(tcounts, self.ranges))
             runs = self.last_recv_sizes                      # one sorted run per source rank
             self._mark("exchange targets")
-        src = self.rank.dummies(tin, runs)
+        src = self.rank.dummies(tin, runs, per_set)
         self._mark("dummies")
         n_src = torch.tensor([src.shape[0]], dtype=torch.int64, device=dev)
         all_n = torch.empty(self.world, dtype=torch.int64, device=dev)
