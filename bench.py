@@ -241,6 +241,7 @@ def run_ours(args, wl):
             return multi_gpu.bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler,
                                    algorithmic_bytes)
         finally:
+            multi_gpu.release_symmetric_buffers()
             dist.destroy_process_group()
 
     # ---- synthetic reads, generated straight into HBM in the packed layout ----

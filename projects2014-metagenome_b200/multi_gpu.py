@@ -319,6 +319,18 @@ class VirtualBuild:
 
 # ---- one process per GPU ------------------------------------------------------------------------
 
+# Symmetric (peer-mapped) receive buffers live as long as the process: keyed by (group, device,
+# slot), shared by every DistBuild of the process and only ever replaced by a larger one.
+_SYMM_SLOTS = {}
+_SYMM_RETIRED = []
+
+
+def release_symmetric_buffers():
+    """Drop the process-wide symmetric buffers (call on every rank before destroy_process_group)."""
+    _SYMM_SLOTS.clear()
+    _SYMM_RETIRED.clear()
+
+
 class DistBuild:
     """The partitioned build of THIS rank inside a torch.distributed (NCCL) group."""
 
@@ -356,15 +368,20 @@ class DistBuild:
         """Symmetric (peer-mapped) receive buffer `slot` of at least need_bytes on EVERY rank; the
         decision to (re)allocate is taken from numbers all ranks share, so the rendezvous is collective."""
         import torch.distributed._symmetric_memory as symm
-        cur = self._slots.get(slot)
+        name = self.group.group_name if self.group is not None else self.dist.group.WORLD.group_name
+        key = (name, str(self.rank.device), slot)
+        cur = _SYMM_SLOTS.get(key)
         if cur is None or cur[0].numel() < need_bytes:
             cap = (int(need_bytes * 1.25) + (1 << 20)) & ~0xFFF
-            self._slots.pop(slot, None)
+            if cur is not None:
+                # An outgrown block is parked, never freed: a block that went through a rendezvous must
+                # not come back from the allocator for ANOTHER slot while peers still map it as the old one
+                _SYMM_RETIRED.append(cur)
             buf = symm.empty(cap, dtype=self.torch.uint8, device=self.rank.device)
-            name = self.group.group_name if self.group is not None else self.dist.group.WORLD.group_name
             hdl = symm.rendezvous(buf, name)
             cur = (buf, hdl)
-            self._slots[slot] = cur
+            _SYMM_SLOTS[key] = cur
+        self._slots[slot] = cur
         return cur
 
     def _exchange(self, send, send_sizes, slot=0):

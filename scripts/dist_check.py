@@ -60,6 +60,7 @@ def main():
                 dist.barrier()
     flag = torch.tensor([1 if ok else 0], device="cuda")
     dist.broadcast(flag, 0)
+    multi_gpu.release_symmetric_buffers()
     dist.destroy_process_group()
     sys.exit(0 if int(flag.item()) else 1)
 
