@@ -759,8 +759,9 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                    "partitioning": "key range (top 8 bits of the k-mer word); all-to-all of canonical k-mers, "
                                    "of both strands of the distinct k-mers and of target nodes (%s); "
                                    "all-gather of source nodes"
-                                   % ("NVLink peer copies into symmetric memory" if db_use_symm
-                                      else "NCCL all_to_all_single"),
+                                   % ("over NVLink into peer-mapped symmetric memory: k-mers and targets by the "
+                                      "stores of their scatter kernels (mtg_mg_route / mtg_mg_targets_route), "
+                                      "strands by peer copies" if db_use_symm else "NCCL all_to_all_single"),
                    "l2_policy": "inputs larger than L2 (%.2f GB of keys per GPU and step)"
                                 % (n_windows * 8 * (2 if wl["canonical"] else 1) / 1e9)},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(counters[4]),
