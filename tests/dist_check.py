@@ -1,5 +1,5 @@
 """Parity of the real one-process-per-GPU build (DistBuild over NCCL / NVLink peer memory) against
-the CPU oracle:  torchrun --nproc-per-node N scripts/dist_check.py
+the CPU oracle:  torchrun --nproc-per-node N tests/dist_check.py
 Every rank pushes its share of seeded reads, the per-range chunks are gathered on rank 0,
 concatenated (Chunk::extend) and compared bit for bit with the oracle's single chunk.
 TEST INFRASTRUCTURE (uses oracle/)."""
@@ -12,7 +12,7 @@ import torch.distributed as dist
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))   # this directory: oracle_lib
 import mtg_b200  # noqa: E402,F401
 from mtg_b200 import multi_gpu, synth  # noqa: E402
 

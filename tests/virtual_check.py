@@ -1,4 +1,4 @@
-"""dist_check.py's cases as g virtual ranks on ONE GPU: python scripts/virtual_check.py [world ...]"""
+"""dist_check.py's cases as g virtual ranks on ONE GPU: python tests/virtual_check.py [world ...]"""
 import os
 import sys
 
@@ -6,7 +6,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
-sys.path.insert(0, os.path.join(ROOT, "tests"))
+sys.path.insert(0, os.path.join(ROOT, "tests"))   # this directory: oracle_lib
 import mtg_b200  # noqa: E402,F401
 import oracle_lib  # noqa: E402
 from mtg_b200 import multi_gpu, synth  # noqa: E402
