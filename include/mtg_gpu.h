@@ -147,7 +147,8 @@ int mtg_debug_sort_u128(int device, uint64_t *keys_lohi, uint32_t *vals /*nullab
  *   mtg_push_reads* -> mtg_mg_extract -> [all-to-all by bucket]   (or: mtg_mg_count -> mtg_mg_route)
  *   -> mtg_mg_collect
  *   [canonical: -> mtg_mg_strands -> [all-to-all of both strands by final range] -> mtg_mg_merge]
- *   -> mtg_mg_targets -> [all-to-all by bucket] -> mtg_mg_dummies -> [all-gather]
+ *   -> mtg_mg_targets -> [all-to-all by bucket]   (or: mtg_mg_targets_count -> mtg_mg_targets_route)
+ *   -> mtg_mg_dummies -> [all-gather]
  *   -> mtg_mg_build  (chunk of this range; the host concatenates with Chunk::extend). */
 uint32_t mtg_mg_part_bits(const mtg_ctx *ctx);
 /* Extracts the pushed reads (the canonical k-mers in canonical mode) and groups the k-mers by bucket:
