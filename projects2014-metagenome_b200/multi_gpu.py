@@ -399,9 +399,9 @@ class DistBuild:
         dev = self.rank.device
         ni = len(items)
         sizes = torch.tensor([list(ss) for _, ss, _ in items], dtype=torch.int64, device=dev)   # [item][dest]
-        all_sizes = torch.empty((self.world, ni, self.world), dtype=torch.int64, device=dev)
+        all_sizes = torch.empty((self.world * ni, self.world), dtype=torch.int64, device=dev)   # concatenated form
         dist.all_gather_into_tensor(all_sizes, sizes, group=self.group)   # also orders the ranks: every
-        all_sizes = all_sizes.cpu().numpy()                               # peer has consumed its slots
+        all_sizes = all_sizes.cpu().numpy().reshape(self.world, ni, self.world)   # peer has consumed its slots
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         out = []
         if not self.use_symm:

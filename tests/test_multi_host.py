@@ -153,3 +153,59 @@ def test_route_segments_layout():
                 off += n_me
         assert off == counts[:, lo:hi].sum()
     assert nseg == len(plans[0][1])
+
+
+def _exchange_worker(rank, world, port, tmp):
+    """DistBuild._exchange_many (the size bookkeeping shared by the NVLink and the NCCL path) on the
+    gloo backend: a bare DistBuild without a CUDA context, two items of different row shapes."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        class _Rank:
+            device = torch.device("cpu")
+        db = multi_gpu.DistBuild.__new__(multi_gpu.DistBuild)
+        db.torch, db.dist, db.group = torch, dist, None
+        db.world, db.rank_id, db.rank = world, rank, _Rank()
+        db.use_symm, db.push_kernel, db.a2a_bytes, db.a2a_ms = False, False, 0, 0.0
+
+        class _Ev:   # CUDA events are not available on the CPU box
+            def __init__(self, **kw): pass
+            def record(self): pass
+            def synchronize(self): pass
+            def elapsed_time(self, other): return 0.0
+        real_event, torch.cuda.Event = torch.cuda.Event, _Ev
+        try:
+            rng = np.random.default_rng(7)
+            sizes = rng.integers(0, 6, (2, world, world))           # [item][source][destination]
+            sizes[0, 1 % world, :] = 0                               # a source with nothing to send
+            def rows(item, src, dst, n):                             # recognisable payloads
+                base = 1000 * item + 100 * src + 10 * dst
+                return [base + j for j in range(n)]
+            keys = torch.tensor([[v, -v] for d in range(world) for v in rows(0, rank, d, sizes[0, rank, d])],
+                                dtype=torch.int64).reshape(-1, 2)
+            cnts = torch.tensor([v for d in range(world) for v in rows(1, rank, d, sizes[1, rank, d])],
+                                dtype=torch.int32)
+            got = db._exchange_many([(keys, [int(x) for x in sizes[0, rank]], 1),
+                                     (cnts, [int(x) for x in sizes[1, rank]], 2)])
+            exp_k = [v for s in range(world) for v in rows(0, s, rank, sizes[0, s, rank])]
+            exp_c = [v for s in range(world) for v in rows(1, s, rank, sizes[1, s, rank])]
+            assert got[0][0][:, 0].tolist() == exp_k and got[0][0][:, 1].tolist() == [-v for v in exp_k]
+            assert got[1][0].tolist() == exp_c
+            assert got[0][1] == [int(sizes[0, s, rank]) for s in range(world)]
+            assert got[1][1] == [int(sizes[1, s, rank]) for s in range(world)]
+            one = db._exchange(cnts, [int(x) for x in sizes[1, rank]])
+            assert one.tolist() == exp_c and db.last_recv_sizes == got[1][1]
+        finally:
+            torch.cuda.Event = real_event
+        dist.barrier()
+        if rank == 0:
+            open(os.path.join(tmp, "ok_exchange"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [3])
+def test_gloo_exchange_many_bookkeeping(world, tmp_path):
+    mp.spawn(_exchange_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    assert os.path.exists(tmp_path / "ok_exchange")
