@@ -46,6 +46,8 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-reads", type=int, default=1_000_000)
+    ap.add_argument("--no-parity-check", action="store_true",
+                    help="N > 1: skip the untimed DistBuild-vs-oracle verification builds")
     return ap.parse_args()
 
 
@@ -237,9 +239,17 @@ def run_ours(args, wl):
     n_reads = wl["n_reads"]
     if world > 1:
         from mtg_b200 import multi_gpu
+        parity = None
+        if not args.no_parity_check:
+            # untimed: the six tests/dist_check.py cases through the real DistBuild, checker = oracle
+            import dist_check
+
+            def parity(rank_, world_, local_):
+                return dist_check.run_cases(rank_, world_, local_, variants=("1",), repeats=1,
+                                            log=lambda m: print(m, file=sys.stderr, flush=True))
         try:
             return multi_gpu.bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler,
-                                   algorithmic_bytes)
+                                   algorithmic_bytes, parity=parity)
         finally:
             multi_gpu.release_symmetric_buffers()
             dist.destroy_process_group()

@@ -198,6 +198,10 @@ int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint
 int mtg_mg_targets_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n);
 int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner /* [2^part_bits] */, uint32_t n_owners,
                          const uint64_t *owner_dst /* [n_owners] device addresses */);
+/* Verification hook of the fused exchanges (multi_gpu.py, MTG_MG_VERIFY): the device array the next
+ * route call will scatter -- which = 0: the k-mers counted by mtg_mg_count, which = 1: the target nodes
+ * counted by mtg_mg_targets_count. Library memory, valid until that route call. */
+int mtg_mg_debug_pending(mtg_ctx *ctx, int which, void **d_keys, uint64_t *n);
 /* d_targets_in: all target nodes that fall into this range. Finds the range's dummy sinks
  * (kept inside) and returns its source nodes without incoming edge (forward-lex packing).
  * run_lengths[n_runs] (host, may be NULL): d_targets_in is the concatenation of sorted runs of

@@ -308,6 +308,13 @@ class BOSSChunkConstructor:
         self._check(self._lib.mtg_mg_targets_route(self._ctx, own.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
                                                    dst.shape[0], dst.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
 
+    def mg_debug_pending(self, which):
+        """verification hook: (device pointer, n) of the array the next route call scatters
+        (which = 0: k-mers after mg_count, 1: target nodes after mg_targets_count)"""
+        ptr, n = ctypes.c_void_p(), ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_debug_pending(self._ctx, int(which), ctypes.byref(ptr), ctypes.byref(n)))
+        return ptr.value or 0, n.value
+
     def mg_collect(self, dptr, n):
         m = ctypes.c_uint64()
         self._check(self._lib.mtg_mg_collect(self._ctx, ctypes.c_void_p(dptr), n, ctypes.byref(m)))

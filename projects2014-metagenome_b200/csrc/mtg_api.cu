@@ -126,11 +126,16 @@ struct DevBuf {   // arena-backed device allocation (stream-ordered by construct
     template <typename T> T *as() const { return reinterpret_cast<T *>(p); }
 };
 
+// Pinned staging buffer of mtg_push_reads. FILLING: a pushing thread owns it (it fills it outside the
+// context mutex); IN_FLIGHT: its H2D copies are enqueued and `ev` was recorded behind them FOR THIS USE --
+// only then does the event say anything about the buffer (a never-recorded or previously completed
+// event reads "done"). The pool is a deque: pointers into it stay valid while other threads add buffers.
 struct PinnedBuf {
+    enum State { FREE, FILLING, IN_FLIGHT };
     void *p = nullptr;
     size_t bytes = 0;
     cudaEvent_t ev = nullptr;
-    bool busy = false;
+    State state = FREE;
 };
 
 struct ReadSegment {
@@ -248,26 +253,27 @@ void build_lut(uint32_t alphabet, ExtractLut *lut) {
     lut->code[0] = 0xff;   // read separator of the packed layout
 }
 
+// caller holds ctx->mu
 PinnedBuf *get_pinned(mtg_ctx *ctx, size_t bytes) {
-    for (auto &b : ctx->pinned) {
-        if (b.busy && cudaEventQuery(b.ev) == cudaSuccess) b.busy = false;
-    }
     for (auto &b : ctx->pinned)
-        if (!b.busy && b.bytes >= bytes) { b.busy = true; return &b; }
+        if (b.state == PinnedBuf::IN_FLIGHT && cudaEventQuery(b.ev) == cudaSuccess) b.state = PinnedBuf::FREE;
     for (auto &b : ctx->pinned)
-        if (!b.busy) {   // grow an idle one
+        if (b.state == PinnedBuf::FREE && b.bytes >= bytes) { b.state = PinnedBuf::FILLING; return &b; }
+    for (auto &b : ctx->pinned)
+        if (b.state == PinnedBuf::FREE) {   // grow an idle one
             cudaFreeHost(b.p);
             b.p = nullptr;
+            b.bytes = 0;
             MTG_CUDA(cudaMallocHost(&b.p, bytes));
             b.bytes = bytes;
-            b.busy = true;
+            b.state = PinnedBuf::FILLING;
             return &b;
         }
     PinnedBuf nb;
     MTG_CUDA(cudaMallocHost(&nb.p, bytes));
     nb.bytes = bytes;
     MTG_CUDA(cudaEventCreateWithFlags(&nb.ev, cudaEventDisableTiming));
-    nb.busy = true;
+    nb.state = PinnedBuf::FILLING;
     ctx->pinned.push_back(nb);
     return &ctx->pinned.back();
 }
@@ -513,6 +519,7 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
                                   want_starts ? seg.starts.as<uint64_t>() : nullptr, s);
                 ctx->launches += 1;
                 MTG_CUDA(cudaEventRecord(pb->ev, s));
+                pb->state = PinnedBuf::IN_FLIGHT;
                 seg.d_packed = seg.own_packed.as<uint8_t>();
                 seg.nbytes = padded;
                 seg.n_windows_max = nwin;
@@ -1968,6 +1975,16 @@ int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner, uint32_t n_
         if (int rc = check_route_args(ctx, wide, bucket_owner, n_owners, owner_dst)) return rc;
         if (wide) mg_targets_route_impl<u128>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
         else mg_targets_route_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
+    })
+}
+
+/* verification hook of the fused exchanges: the k-mers (which = 0, after mtg_mg_count) or target
+ * nodes (which = 1, after mtg_mg_targets_count) that the next route call will scatter */
+int mtg_mg_debug_pending(mtg_ctx *ctx, int which, void **d_keys, uint64_t *n) {
+    MG_GUARD(ctx, {
+        if (!d_keys || !n) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
+        *d_keys = which ? ctx->mg.targets.p : ctx->mg.keys.p;
+        *n = which ? ctx->mg.n_routed_targets : ctx->mg.n_routed;
     })
 }
 

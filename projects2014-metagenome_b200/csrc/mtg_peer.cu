@@ -44,28 +44,33 @@ peer_push_kernel(PushPlan plan, uint32_t blocks_per_dest) {
 extern "C" int mtg_peer_push(void *cuda_stream, uint32_t n_dest, void *const *dst_ptrs,
                              const void *const *src_ptrs, const uint64_t *nbytes) {
     using namespace mtg;
-    if (n_dest > PP_MAX_DEST) return MTG_ERR_BAD_ARG;
-    PushPlan plan;
-    plan.n = 0;
-    uint64_t align = 0;
-    for (uint32_t i = 0; i < n_dest; ++i) {
-        if (!nbytes[i]) continue;
-        plan.dst[plan.n] = (unsigned char *)dst_ptrs[i];
-        plan.src[plan.n] = (const unsigned char *)src_ptrs[i];
-        plan.bytes[plan.n] = nbytes[i];
-        align |= (uint64_t)(uintptr_t)dst_ptrs[i] | (uint64_t)(uintptr_t)src_ptrs[i] | nbytes[i];
-        ++plan.n;
-    }
-    if (plan.n == 0) return MTG_OK;
     int dev = 0, sms = 148;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    uint32_t bpd = (uint32_t)((sms * 4 + plan.n - 1) / plan.n);
     cudaStream_t s = (cudaStream_t)cuda_stream;
-    const unsigned grid = bpd * plan.n;
-    if ((align & 15) == 0) peer_push_kernel<uint4><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
-    else if ((align & 7) == 0) peer_push_kernel<uint2><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
-    else if ((align & 3) == 0) peer_push_kernel<uint32_t><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
-    else peer_push_kernel<unsigned char><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
-    return cudaGetLastError() == cudaSuccess ? MTG_OK : MTG_ERR_CUDA;
+    // any number of (destination, item) ranges: one launch per PP_MAX_DEST of them (8 GPUs x 4 items
+    // of the counting canonical build = 32 ranges)
+    uint32_t i = 0;
+    while (i < n_dest) {
+        PushPlan plan;
+        plan.n = 0;
+        uint64_t align = 0;
+        for (; i < n_dest && plan.n < (uint32_t)PP_MAX_DEST; ++i) {
+            if (!nbytes[i]) continue;
+            plan.dst[plan.n] = (unsigned char *)dst_ptrs[i];
+            plan.src[plan.n] = (const unsigned char *)src_ptrs[i];
+            plan.bytes[plan.n] = nbytes[i];
+            align |= (uint64_t)(uintptr_t)dst_ptrs[i] | (uint64_t)(uintptr_t)src_ptrs[i] | nbytes[i];
+            ++plan.n;
+        }
+        if (plan.n == 0) continue;
+        const uint32_t bpd = (uint32_t)((sms * 4 + plan.n - 1) / plan.n);
+        const unsigned grid = bpd * plan.n;
+        if ((align & 15) == 0) peer_push_kernel<uint4><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
+        else if ((align & 7) == 0) peer_push_kernel<uint2><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
+        else if ((align & 3) == 0) peer_push_kernel<uint32_t><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
+        else peer_push_kernel<unsigned char><<<grid, PP_THREADS, 0, s>>>(plan, bpd);
+        if (cudaGetLastError() != cudaSuccess) return MTG_ERR_CUDA;
+    }
+    return MTG_OK;
 }

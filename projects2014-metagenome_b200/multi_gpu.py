@@ -331,10 +331,55 @@ def release_symmetric_buffers():
     _SYMM_RETIRED.clear()
 
 
-class DistBuild:
-    """The partitioned build of THIS rank inside a torch.distributed (NCCL) group."""
+class ExchangeMismatch(RuntimeError):
+    """An exchange delivered other rows than the ones that were sent (MTG_MG_VERIFY)."""
 
-    def __init__(self, K, canonical=False, bits_per_count=0, alphabet="DNA", device=0, group=None):
+
+def row_sums(t):
+    """int64 wrap-around checksum of every row of a 1-D / 2-D integer tensor"""
+    import torch
+    if t.dim() == 1:
+        return t.to(torch.int64)
+    return t.to(torch.int64).sum(dim=1)
+
+
+def segment_sums(t, sizes):
+    """checksums of consecutive row segments of t (lengths `sizes`) -> int64[len(sizes)] on t's device"""
+    import torch
+    cs = torch.zeros(t.shape[0] + 1, dtype=torch.int64, device=t.device)
+    if t.shape[0]:
+        cs[1:] = torch.cumsum(row_sums(t), 0)
+    ends = torch.cumsum(torch.as_tensor([int(x) for x in sizes], dtype=torch.int64), 0).to(t.device)
+    starts = ends - torch.as_tensor([int(x) for x in sizes], dtype=torch.int64).to(t.device)
+    return cs[ends] - cs[starts]
+
+
+def routing_buckets(keys, words, shift, part_bits):
+    """routing bucket (bits [shift, shift + part_bits) of the k-mer word) of every row of a device array
+    of 64-bit (words = 1) or 128-bit (words = 2: low word first) keys -- the digit of the ROUTE scatter"""
+    import torch
+    if part_bits == 0:
+        return torch.zeros(keys.shape[0], dtype=torch.int64, device=keys.device)
+    mask = (1 << part_bits) - 1
+    if words == 1:
+        return (keys >> shift) & mask
+    lo, hi = keys[:, 0], keys[:, 1]
+    if shift >= 64:
+        return (hi >> (shift - 64)) & mask
+    return (((lo >> shift) & ((1 << (64 - shift)) - 1)) | (hi << (64 - shift))) & mask
+
+
+class DistBuild:
+    """The partitioned build of THIS rank inside a torch.distributed (NCCL) group.
+
+    All library work of the rank runs on the torch stream that is current when the object is
+    created (mtg_set_stream): the NCCL collectives, the symmetric-memory barriers and the peer
+    copies issued here are ordered against the kernels of the mtg_mg_* phases through that stream.
+    verify=True (or MTG_MG_VERIFY=1): after every exchange the receiver checks, per source rank,
+    the number of rows and a 64-bit checksum against what the sender addressed to it, and all ranks
+    raise ExchangeMismatch together if any slice differs."""
+
+    def __init__(self, K, canonical=False, bits_per_count=0, alphabet="DNA", device=0, group=None, verify=None):
         import torch
         import torch.distributed as dist
         self.torch, self.dist, self.group = torch, dist, group
@@ -342,6 +387,12 @@ class DistBuild:
         self.rank_id = dist.get_rank(group)
         self.rank = RangedRank(K, canonical, bits_per_count, alphabet, device)
         self.canonical = canonical
+        self.K = K
+        self.key_bits = K * (2 if alphabet == "DNA" else 5)
+        if self.rank.device.type == "cuda":
+            with torch.cuda.device(self.rank.device):
+                self.stream = torch.cuda.current_stream()
+            self.rank.ctor.set_stream(self.stream.cuda_stream)
         # MTG_A2A=nccl forces the NCCL all-to-all; default: peer stores over NVLink (symmetric memory)
         import os
         self.use_symm = (os.environ.get("MTG_A2A", "peer") != "nccl" and dist.get_backend(group) == "nccl"
@@ -362,6 +413,49 @@ class DistBuild:
         self.a2a_bytes = 0
         self.a2a_ms = 0.0
         self.phase_events = None
+        self.verify = (os.environ.get("MTG_MG_VERIFY", "0") != "0") if verify is None else bool(verify)
+        self.verified = []      # names of the exchanges checked by the last build
+
+    # ---- verification of an exchange (debug / parity runs) --------------------------------------
+    def _verify(self, what, sent_sums, sent_counts, got_sums, got_counts, column=None):
+        """sent_*: int64[n] device tensors, one entry per destination slot this rank addressed;
+        got_*: int64[world] (or [n_mine, world]) of what arrived here per source. `column` = the
+        indices of MY slots in the senders' vectors (default: my rank). All ranks raise together."""
+        torch, dist = self.torch, self.dist
+        dev = self.rank.device
+        mine = torch.stack([sent_sums.to(torch.int64), sent_counts.to(torch.int64)]).contiguous()   # [2, n]
+        allv = torch.empty((self.world,) + tuple(mine.shape), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(allv.view(self.world * 2, -1), mine, group=self.group)
+        cols = [self.rank_id] if column is None else list(column)
+        idx = torch.as_tensor(cols, dtype=torch.int64, device=dev)
+        exp_sums = allv[:, 0, :].index_select(1, idx).t()      # [my slots, source]
+        exp_counts = allv[:, 1, :].index_select(1, idx).t()
+        got_sums = got_sums.to(dev).view(len(cols), self.world)
+        got_counts = torch.as_tensor(got_counts, dtype=torch.int64).to(dev).view(len(cols), self.world)
+        bad = (exp_sums != got_sums) | (exp_counts != got_counts)
+        n_bad = bad.sum().view(1)
+        dist.all_reduce(n_bad, group=self.group)
+        if int(n_bad):
+            for j, s_ in bad.nonzero().tolist():
+                print("mtg_b200 VERIFY %s: rank %d slot %d: rows of source rank %d differ: expected n=%d sum=%d, "
+                      "received n=%d sum=%d" % (what, self.rank_id, cols[j], s_, int(exp_counts[j, s_]),
+                                                int(exp_sums[j, s_]), int(got_counts[j, s_]), int(got_sums[j, s_])),
+                      file=sys.stderr, flush=True)
+            raise ExchangeMismatch("exchange '%s': %d (source, destination) slices differ from what was sent"
+                                   % (what, int(n_bad)))
+        self.verified.append(what)
+
+    def _pending_sums(self, which, bucket_slot, n_slots, shift):
+        """checksum / number of the rows the next route call will store into every destination slot"""
+        torch = self.torch
+        ptr, n = self.rank.ctor.mg_debug_pending(which)
+        keys = as_tensor(ptr, n, self.rank.words, self.rank.device)
+        pb = self.rank.ctor.mg_part_bits()
+        slot = torch.as_tensor(np.asarray(bucket_slot, dtype=np.int64), device=self.rank.device)[
+            routing_buckets(keys, self.rank.words, shift, pb)]
+        sums = torch.zeros(n_slots, dtype=torch.int64, device=self.rank.device).scatter_add_(0, slot, row_sums(keys))
+        counts = torch.bincount(slot, minlength=n_slots)
+        return sums, counts
 
     # ---- exchange: NVLink peer stores into symmetric memory, NCCL all_to_all as the fallback ----
     def _symm_slot(self, slot, need_bytes):
@@ -384,14 +478,14 @@ class DistBuild:
         self._slots[slot] = cur
         return cur
 
-    def _exchange(self, send, send_sizes, slot=0):
+    def _exchange(self, send, send_sizes, slot=0, what="exchange"):
         """all-to-all of a bucket-grouped tensor; send_sizes[d] rows go to rank d. Returns the rows
         received, ordered by source rank."""
-        recv, sizes = self._exchange_many([(send, send_sizes, slot)])[0]
+        recv, sizes = self._exchange_many([(send, send_sizes, slot)], what)[0]
         self.last_recv_sizes = sizes
         return recv
 
-    def _exchange_many(self, items):
+    def _exchange_many(self, items, what="exchange"):
         """Several all-to-alls behind ONE size all-gather and ONE barrier: items = [(send tensor,
         send_sizes per destination, symmetric slot)]. Returns [(rows received in source-rank order,
         rows per source)]."""
@@ -417,6 +511,7 @@ class DistBuild:
             ev1.record()
             ev1.synchronize()
             self.a2a_ms += ev0.elapsed_time(ev1)
+            self._verify_items(items, out, what)
             return out
         cur = torch.cuda.current_stream()
         plans = []
@@ -475,7 +570,17 @@ class DistBuild:
         for i, (send, send_sizes, tail, row, esz, hdl) in enumerate(plans):
             recv_sizes = [int(x) for x in all_sizes[:, i, self.rank_id]]
             out.append((hdl.get_buffer(self.rank_id, (int(sum(recv_sizes)),) + tail, send.dtype, 0), recv_sizes))
+        self._verify_items(items, out, what)
         return out
+
+    def _verify_items(self, items, out, what):
+        if not self.verify:
+            return
+        torch = self.torch
+        for i, ((send, send_sizes, _), (recv, recv_sizes)) in enumerate(zip(items, out)):
+            self._verify("%s item %d" % (what, i), segment_sums(send, send_sizes),
+                         torch.as_tensor([int(x) for x in send_sizes], dtype=torch.int64, device=self.rank.device),
+                         segment_sums(recv, recv_sizes), recv_sizes)
 
     def _route_kmers(self):
         """Exchange #1 fused into the grouping pass: after the per-bucket counts of all ranks are
@@ -495,6 +600,8 @@ class DistBuild:
         need = int(sizes.sum(axis=0).max()) * kb
         buf, hdl = self._symm_slot(0, max(need, 16))
         owner, dst, _ = route_addresses(allc, self.ranges, self.rank_id, [int(p) for p in hdl.buffer_ptrs], kb)
+        if self.verify:
+            sent = self._pending_sums(0, owner, self.world, self.key_bits - self.rank.ctor.mg_part_bits())
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         self.rank.route(owner, dst)
@@ -507,6 +614,9 @@ class DistBuild:
         total = int(sizes[:, self.rank_id].sum())
         shape = (total, self.rank.words) if self.rank.words > 1 else (total,)
         recv = hdl.get_buffer(self.rank_id, shape, torch.int64, 0)
+        if self.verify:
+            self._verify("k-mers (fused route)", sent[0], sent[1], segment_sums(recv, self.last_recv_sizes),
+                         self.last_recv_sizes)
         self._mark("route (group + exchange)")
         return recv
 
@@ -527,6 +637,9 @@ class DistBuild:
         buf, hdl = self._symm_slot(5, max(need, 16))
         seg, dst, runs, _ = route_segments(allc, self.ranges, self.rank_id, [int(p) for p in hdl.buffer_ptrs], kb,
                                            char_shift)
+        if self.verify:
+            L = self.rank.ctor.tight_bits()
+            sent = self._pending_sums(1, seg, len(dst), self.key_bits - L - self.rank.ctor.mg_part_bits())
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         ev0.record()
         self.rank.targets_route(seg, dst)
@@ -538,6 +651,15 @@ class DistBuild:
         total = int(sizes[:, self.rank_id].sum())
         shape = (total, self.rank.words) if self.rank.words > 1 else (total,)
         tin = hdl.get_buffer(self.rank_id, shape, torch.int64, 0)
+        if self.verify:
+            seg0 = sum(len(r) for r in runs[:self.rank_id]) // self.world      # my first segment (global index)
+            mine = list(range(seg0, seg0 + len(runs[self.rank_id]) // self.world))
+            if mine:
+                self._verify("targets (fused route)", sent[0], sent[1], segment_sums(tin, runs[self.rank_id]),
+                             runs[self.rank_id], column=mine)
+            else:   # a rank without a segment still takes part in the collectives
+                self._verify("targets (fused route)", sent[0], sent[1],
+                             torch.zeros(0, dtype=torch.int64, device=dev), [], column=[])
         self._mark("route targets (scatter + exchange)")
         return tin, runs[self.rank_id]
 
@@ -559,6 +681,7 @@ class DistBuild:
     def build(self, device_output=False):
         torch, dist = self.torch, self.dist
         dev = self.rank.device
+        self.verified = []
         self._mark("start")
         if self.use_symm and self.fused_route:
             recv = self._route_kmers()
@@ -568,7 +691,7 @@ class DistBuild:
             hist = torch.from_numpy(counts.astype(np.int64)).to(dev)
             dist.all_reduce(hist, group=self.group)
             self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
-            recv = self._exchange(keys, split_sizes(counts, self.ranges))
+            recv = self._exchange(keys, split_sizes(counts, self.ranges), what="k-mers")
             self._mark("exchange kmers")
         self.rank.collect(recv)
         del recv
@@ -585,7 +708,7 @@ class DistBuild:
             items = [(X, xs, 1), (R, rs, 2)]
             if Xc is not None:
                 items += [(Xc, xs, 3), (Rc, rs, 4)]
-            got = self._exchange_many(items)
+            got = self._exchange_many(items, "strands (X, R, X counts, R counts)")
             rX, rR, r_runs = got[0][0], got[1][0], got[1][1]
             rXc, rRc = (got[2][0], got[3][0]) if Xc is not None else (None, None)
             self._mark("exchange strands")
@@ -600,7 +723,7 @@ class DistBuild:
             per_set = 0
             tcounts, tg = self.rank.targets()
             self._mark("targets")
-            tin = self._exchange(tg, split_sizes(tcounts, self.ranges))
+            tin = self._exchange(tg, split_sizes(tcounts, self.ranges), what="targets")
             runs = self.last_recv_sizes                      # one sorted run per source rank
             self._mark("exchange targets")
         src = self.rank.dummies(tin, runs, per_set)
@@ -612,6 +735,20 @@ class DistBuild:
         parts = [torch.empty((n,) + tuple(src.shape[1:]), dtype=torch.int64, device=dev) for n in all_n]
         self._all_gather_ragged(parts, src, all_n)
         all_src = torch.cat(parts)
+        if self.verify:
+            # every rank must hold the same list: compare the per-source checksums with the owners' own
+            mine = torch.zeros(self.world, dtype=torch.int64, device=dev)
+            mine[self.rank_id] = row_sums(src).sum()
+            cnt = torch.zeros(self.world, dtype=torch.int64, device=dev)
+            cnt[self.rank_id] = src.shape[0]
+            dist.all_reduce(mine, group=self.group)
+            dist.all_reduce(cnt, group=self.group)
+            got = segment_sums(all_src, all_n)
+            bad = ((got != mine) | (cnt != torch.as_tensor(all_n, dtype=torch.int64, device=dev))).sum().view(1)
+            dist.all_reduce(bad, group=self.group)
+            if int(bad):
+                raise ExchangeMismatch("gathered source nodes differ from the owners' lists")
+            self.verified.append("source nodes (all-gather)")
         lo, hi = self.ranges[self.rank_id]
         self._mark("gather sources")
         out = self.rank.build(all_src, lo, hi, self.rank_id == 0, device_output)
@@ -644,10 +781,13 @@ def gather_chunks(chunk, dist, group=None, dst=0):
 
 # ---- bench.py --gpus N (N > 1) -------------------------------------------------------------------
 
-def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_bytes):
+def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_bytes, parity=None):
     """Weak scaling of the bench workload: every rank holds its own shard of wl['n_reads'] reads
     of a genome that grows with the number of ranks (same coverage, same duplication), generated
-    straight into HBM. value = k-mers of all ranks / max-over-ranks time."""
+    straight into HBM. value = k-mers of all ranks / max-over-ranks time.
+    parity: callable(rank, world, local device) -> dict, run untimed before the measurement (bench.py
+    passes tests/dist_check.run_cases: the real DistBuild against the oracle); a failed check is
+    printed in the line and makes the process exit non-zero."""
     import json
     import os
     import time
@@ -655,6 +795,7 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
     import torch.distributed as dist
     from . import synth
 
+    parity_res = parity(rank, world, dev.index) if parity is not None else None
     K, L = wl["K"], wl["read_len"]
     n_local = wl["n_reads"]
     n_total = n_local * world
@@ -735,6 +876,8 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
     db_use_symm = db.use_symm
     db.close()
     if rank != 0:
+        if parity_res is not None and not parity_res.get("ok"):
+            raise SystemExit(1)
         return
     ms_total = float(ms)
     N = int(counters[0])
@@ -763,7 +906,7 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                                       "stores of their scatter kernels (mtg_mg_route / mtg_mg_targets_route), "
                                       "strands by peer copies" if db_use_symm else "NCCL all_to_all_single"),
                    "l2_policy": "inputs larger than L2 (%.2f GB of keys per GPU and step)"
-                                % (n_windows * 8 * (2 if wl["canonical"] else 1) / 1e9)},
+                                % (n_windows * 8 * (1 if K * 2 <= 64 else 2) / 1e9)},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(counters[4]),
         "roofline": {"bound": "hbm", "kernel": "whole path per GPU (SURVEY 8d byte model)",
                      "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None,
@@ -772,9 +915,12 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                                   "peak_GBps": 900.0, "frac": a2a_gbs / 900.0},
                      "phases_ms_per_rank": all_phases},
         "cpu_baseline": None,
+        "parity_check": parity_res,
     }
     fd = os.environ.pop("MTG_BENCH_STDOUT_FD", None)
     if fd is not None:   # bench.py parked the real stdout while NCCL could write to fd 1
         sys.stdout.flush()
         os.dup2(int(fd), 1)
     print(json.dumps(line), flush=True)
+    if parity_res is not None and not parity_res.get("ok"):
+        raise SystemExit("bench.py: multi-GPU parity check FAILED: %s" % parity_res.get("mismatches"))

@@ -383,3 +383,39 @@ def test_full_size_chunk_invariants():
     # every real k-mer and every dummy source has an edge label; sinks and the root row carry '$'
     assert int(counts[1:5].sum() + counts[6:10].sum()) == st["n_real"] + sum(st["n_dummy_source"]) - (2 - extra)
     ctor.close()
+
+
+@pytest.mark.parametrize("canonical,bpc,explicit", [(True, 8, False), (False, 16, True)])
+def test_push_reads_from_many_threads(canonical, bpc, explicit):
+    """mtg_push_reads is documented thread-safe because the reference calls add_sequences from an
+    `omp parallel for` over files (cli/build.cpp:35-52): 8 threads push interleaved batches of pageable
+    memory (pinned staging pool under contention); the chunk must equal the oracle's on the same reads."""
+    import threading
+    reads = dna_reads(77, 24_000, 110, 150_000, n_frac=0.002)
+    counts = [1 + (i % 5) for i in range(len(reads))] if explicit else None
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(30, canonical, bpc)
+    errors = []
+
+    def worker(t):
+        try:
+            for i in range(t, 240, 8):            # 240 batches of 100 reads, round-robin over the threads
+                lo, hi = i * 100, (i + 1) * 100
+                if explicit:
+                    ctor.add_sequences(list(zip(reads[lo:hi], counts[lo:hi])))
+                else:
+                    ctor.add_sequences(reads[lo:hi])
+        except Exception as e:   # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(t,)) for t in range(8)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    assert not errors, errors
+    chunk = ctor.build_chunk()
+    ctor.close()
+    ref = oracle_lib.oracle_build(reads, 31, canonical=canonical, bits_per_count=bpc, counts=counts)
+    assert chunk.n_rows == ref["n_rows"]
+    assert np.array_equal(chunk.W, ref["W"]) and np.array_equal(chunk.last, ref["last"])
+    assert np.array_equal(chunk.F, ref["F"]) and np.array_equal(chunk.weights, ref["weights"])

@@ -168,6 +168,7 @@ def _exchange_worker(rank, world, port, tmp):
         db.torch, db.dist, db.group = torch, dist, None
         db.world, db.rank_id, db.rank = world, rank, _Rank()
         db.use_symm, db.push_kernel, db.a2a_bytes, db.a2a_ms = False, False, 0, 0.0
+        db.verify, db.verified = True, []      # per-slice row count + checksum of every exchange
 
         class _Ev:   # CUDA events are not available on the CPU box
             def __init__(self, **kw): pass
@@ -196,6 +197,20 @@ def _exchange_worker(rank, world, port, tmp):
             assert got[1][1] == [int(sizes[1, s, rank]) for s in range(world)]
             one = db._exchange(cnts, [int(x) for x in sizes[1, rank]])
             assert one.tolist() == exp_c and db.last_recv_sizes == got[1][1]
+            assert db.verified == ["exchange item 0", "exchange item 1", "exchange item 0"]
+            # a slice that arrives damaged on ONE rank makes ALL ranks raise (no rank is left in a collective)
+            recv = got[1][0].clone()
+            if rank == world - 1 and recv.numel():
+                recv[0] += 1
+            damaged = bool(rank == world - 1 and recv.numel())
+            flag = torch.tensor([int(damaged)])
+            dist.all_reduce(flag)
+            try:
+                db._verify_items([(cnts, [int(x) for x in sizes[1, rank]], 2)], [(recv, got[1][1])], "tampered")
+                raised = False
+            except multi_gpu.ExchangeMismatch:
+                raised = True
+            assert raised == bool(int(flag))
         finally:
             torch.cuda.Event = real_event
         dist.barrier()
