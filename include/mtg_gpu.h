@@ -222,7 +222,8 @@ int mtg_peer_push(void *cuda_stream, uint32_t n_dest, void *const *dst_ptrs, con
                   const uint64_t *nbytes);
 
 /* Device-resident timing of the radix sort alone on n pseudo-random keys of key_bits bits
- * (tuning aid): ms_out[0] = digit-histogram kernel, [1] = mean onesweep pass, [2] = whole sort. */
+ * (tuning aid): ms_out[5]: [0] = digit-histogram kernel, [1] = mean onesweep pass, [2] = whole sort,
+ * [3] = first pass, [4] = mean of the later passes. */
 int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_vals, int iters,
                          float *ms_out);
 /* test/bench hook: times the unique (fold) kernel alone on keys[i] = i / dup; ms_out[0] = best ms,

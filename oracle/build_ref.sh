@@ -19,7 +19,8 @@ mkdir -p "$OUT/obj_sdsl" "$OUT/obj_DNA" "$OUT/obj_Protein"
 EXT="$REF/external-libraries"
 SDSL="$EXT/sdsl-lite"
 
-CXXFLAGS_COMMON="-std=gnu++17 -O2 -fopenmp -mcx16 -msse4.2 -mavx2 -mbmi -mbmi2 -mfma \
+# -O3: what the reference's own Release build type uses (CMAKE_BUILD_TYPE=Release)
+CXXFLAGS_COMMON="-std=gnu++17 -O3 -fopenmp -mcx16 -msse4.2 -mavx2 -mbmi -mbmi2 -mfma \
  -DMODE_TI -DNDEBUG -D_THREAD_SAFE -pthread -w -include cstdint -include stdexcept"
 INC="-I$REF/src -I$SDSL/include -I$EXT/ips4o -I$EXT/spdlog/include \
  -I$EXT/hopscotch-map/include -I$EXT/ordered-map/include -I$EXT/cpp_progress_bar \

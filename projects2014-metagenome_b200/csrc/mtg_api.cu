@@ -700,6 +700,7 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
         if (n >= min_n && n > 0 && p < plan.n) split_pass = p;
     }
     SortPlan plan_lo = plan, plan_hi;
+    plan_lo.unstable_first = true;   // equal k-mers are folded (counts summed, saturating: order-free)
     plan_hi.n = 0;
     if (split_pass) {
         plan_lo.n = split_pass;
@@ -774,6 +775,7 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
                                      counting ? cb0.as<uint32_t>() : nullptr, m, al, ctx->cmax, d_ctr + 2, s,
                                      &ctx->launches);
     const uint64_t mb = read_counter(d_ctr + 2, s);
+    plan.unstable_first = true;      // the reverse complements are distinct keys
     sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s,
                     &ctx->launches);
     rb1.release();
@@ -811,6 +813,7 @@ void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64
         SortPlan plan;
         plan.n = 0;
         plan_add_key_bits(plan, 0, (K - 1) * L);
+        plan.unstable_first = true;
         sort_keys<KeyT>(src, srcB, nullptr, nullptr, d1, plan, s, &ctx->launches);
     }
     srcB.release();
@@ -1285,12 +1288,13 @@ int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_val
             SortPlan plan;
             plan.n = 0;
             plan_add_key_bits(plan, 0, key_bits);
+            plan.unstable_first = getenv("MTG_BENCH_UNSTABLE_FIRST") != nullptr;
             uint32_t top = wide ? key_bits - 64 : key_bits;
             uint64_t hi_mask = top >= 64 ? ~0ull : ((1ull << top) - 1);
             cudaEvent_t ev[2 * MAX_SORT_PASSES + 2], e0, e1;
             for (auto &e : ev) cudaEventCreate(&e);
             cudaEventCreate(&e0); cudaEventCreate(&e1);
-            ms_out[0] = ms_out[1] = ms_out[2] = 1e30f;
+            ms_out[0] = ms_out[1] = ms_out[2] = ms_out[3] = ms_out[4] = 1e30f;
             for (int it = 0; it < iters; ++it) {
                 DevBuf &cur = a;
                 fill_random_words(cur.as<uint64_t>(), n * (wide ? 2 : 1), it + 1, hi_mask, wide, s);
@@ -1304,6 +1308,9 @@ int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_val
                 float t = 0, sum = 0;
                 for (int p = 0; p < plan.n; ++p) { cudaEventElapsedTime(&t, ev[2 * p], ev[2 * p + 1]); sum += t; }
                 ms_out[1] = std::min(ms_out[1], sum / plan.n);
+                cudaEventElapsedTime(&t, ev[0], ev[1]);
+                ms_out[3] = std::min(ms_out[3], t);
+                if (plan.n > 1) ms_out[4] = std::min(ms_out[4], (sum - t) / (plan.n - 1));
                 cudaEventElapsedTime(&t, ev[2 * MAX_SORT_PASSES], ev[2 * MAX_SORT_PASSES + 1]);
                 ms_out[0] = std::min(ms_out[0], t);
                 cudaEventElapsedTime(&t, e0, e1);
@@ -1407,6 +1414,7 @@ void mg_extract_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **
         SortPlan plan;
         plan.n = 0;
         plan.p[plan.n++] = DigitPass{0, (int)(al.K * al.L - pb), (int)pb};
+        plan.unstable_first = true;   // grouping only: mtg_mg_collect sorts
         SortWorkspace ws;
         DevBuf status(sizeof(unsigned long long) * sort_status_words<KeyT>(n), s);
         DevBuf hist(sizeof(unsigned long long) * MAX_SORT_PASSES * RADIX, s);
@@ -1469,7 +1477,7 @@ void mg_count_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, uint64_t 
 // one scatter kernel: key with digit dp == b -> array at owner_dst[bucket_owner[b]]
 template <typename KeyT>
 void route_buffer(mtg_ctx *ctx, const KeyT *keys, uint64_t n, DigitPass dp, uint32_t nb, const uint32_t *bucket_owner,
-                  uint32_t n_owners, const uint64_t *owner_dst) {
+                  uint32_t n_owners, const uint64_t *owner_dst, bool stable) {
     cudaStream_t s = ctx->stream;
     if (!n) return;
     // one staging block: RADIX addresses followed by RADIX owner bytes
@@ -1482,7 +1490,7 @@ void route_buffer(mtg_ctx *ctx, const KeyT *keys, uint64_t n, DigitPass dp, uint
     MTG_CUDA(cudaMemcpyAsync(route.p, h.data(), 8 * (RADIX + RADIX / 8), cudaMemcpyHostToDevice, s));
     route_scatter<KeyT>(keys, n, dp, reinterpret_cast<const unsigned char *>(route.as<unsigned long long>() + RADIX),
                         route.as<unsigned long long>(), status.as<unsigned long long>(), tc.as<unsigned int>(), s,
-                        &ctx->launches);
+                        &ctx->launches, stable);
     MTG_CUDA(cudaStreamSynchronize(s));   // `h` and the scratch outlive the kernel
 }
 
@@ -1493,7 +1501,9 @@ void mg_route_impl(mtg_ctx *ctx, uint32_t pb, const uint32_t *bucket_owner, uint
     // pb = 0: one bucket, a 1-bit digit above the key bits (always 0) keeps the pass generic
     const DigitPass dp = pb ? DigitPass{0, (int)(al.K * al.L - pb), (int)pb}
                             : DigitPass{0, (int)(8 * sizeof(KeyT) - 1), 1};
-    route_buffer<KeyT>(ctx, ctx->mg.keys.as<KeyT>(), ctx->mg.n_routed, dp, 1u << pb, bucket_owner, n_owners, owner_dst);
+    // the k-mers arrive unordered and are sorted by mtg_mg_collect: the scatter need not be stable
+    route_buffer<KeyT>(ctx, ctx->mg.keys.as<KeyT>(), ctx->mg.n_routed, dp, 1u << pb, bucket_owner, n_owners, owner_dst,
+                       false);
     ctx->mg.keys.release();
     ctx->mg.n_routed = 0;
 }
@@ -1533,8 +1543,9 @@ void mg_targets_route_impl(mtg_ctx *ctx, uint32_t pb, const uint32_t *bucket_own
     const Alpha al = ctx->al;
     const DigitPass dp = pb ? DigitPass{0, (int)((al.K - 1) * al.L - pb), (int)pb}
                             : DigitPass{0, (int)(8 * sizeof(KeyT) - 1), 1};
+    // stable: every (source, segment) slice must arrive as the sorted run it is
     route_buffer<KeyT>(ctx, ctx->mg.targets.as<KeyT>(), ctx->mg.n_routed_targets, dp, 1u << pb, bucket_owner, n_owners,
-                       owner_dst);
+                       owner_dst, true);
     ctx->mg.targets.release();
     ctx->mg.n_routed_targets = 0;
 }
@@ -1665,6 +1676,7 @@ void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, const uint64
             SortPlan plan;
             plan.n = 0;
             plan_add_key_bits(plan, 0, (K - 1) * L);
+            plan.unstable_first = true;
             sort_keys<KeyT>(t0, t1, nullptr, nullptr, n_in, plan, s, &ctx->launches, nullptr, d_in);
         }
         DevBuf status(sizeof(unsigned long long) * unique_status_words(n_in), s), tctr(sizeof(unsigned int), s);
@@ -1728,6 +1740,7 @@ void mg_strands_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *x_counts, uint64_t *r_
         SortPlan plan;
         plan.n = 0;
         plan_add_key_bits(plan, 0, KL);
+        plan.unstable_first = true;
         sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s, &ctx->launches);
     } else {
         if (mb) {
@@ -1737,6 +1750,7 @@ void mg_strands_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *x_counts, uint64_t *r_
             SortPlan plan;
             plan.n = 0;
             plan_add_key_bits(plan, 0, KL);
+            plan.unstable_first = true;
             sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s,
                             &ctx->launches);
             std::vector<uint64_t> rbounds(nb + 1, 0);
@@ -1789,6 +1803,7 @@ void mg_merge_impl(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t
         SortPlan plan;
         plan.n = 0;
         plan_add_key_bits(plan, 0, al.K * al.L);
+        plan.unstable_first = true;
         sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, nr, plan, s, &ctx->launches);
     }
     rb1.release(); cb1.release();

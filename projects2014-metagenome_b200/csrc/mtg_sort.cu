@@ -312,23 +312,28 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
 }
 
 // ---------------------------------------------------------------------------
-// Kernel S3 (v4): ballot-ranked onesweep pass.
-// The ncu capture of v3 (profiles/r01_ncu_full_v2_101ms.txt) shows the pass bound by the
-// shared-memory pipe (L1TEX 80 %, 35 wavefronts per warp-row of keys, 57 % of them bank
-// conflicts of the two atomics + mask read-back + mask reset per key). Here the peer mask of a
-// key is built from 8 warp ballots (one per digit bit; VOTE does not touch shared memory), so a
-// key costs one counter read, one leader write, and the tile-order scatter:
-//   peers = AND_b (bit_b(d) ? ballot(bit_b) : ~ballot(bit_b))
-//   rank  = my_hist[d] + popc(peers & lanemask_lt);  leader: my_hist[d] += popc(peers)
-// The tile's digit counts are known after the ranking loop (no separate counting pass).
+// Kernel S3 (v5): the default pass. Same tile structure as v3 (early per-warp digit counts by shared
+// atomics, early publish, tile-sorted staging, decoupled look-back, coalesced write-out); what changes is
+// the ranking, which is where v3 spends its shared-memory bandwidth (ncu, profiles/r01_ncu_full_v6_82ms.txt:
+// L1TEX 81 %, 57 % of the wavefronts bank conflicts): per key v3 issues atomicOr(mask), a mask read-back,
+// a counter read and two leader stores. Here a key takes its slot with ONE atomicAdd (with return) on the
+// running per-warp digit offset:
+//   UNSTABLE: that is all -- lanes of one warp-row that share a digit get consecutive slots in
+//     arbitrary order. Legal for the FIRST pass of an LSD sort (no earlier order to preserve) and for the
+//     k-mer routing scatter.
+//   stable: the lanes read the offset before the atomics of the row (`before`); a lane whose slot differs
+//     from `before` shares its digit with another lane of the row (12 % of the keys of a random 8-bit
+//     digit). Only those groups are repaired: per group one shuffle + one ballot give the group mask and
+//     slot = before + popc(group & lanes below). ~1.9 groups per row on random digits; rows without
+//     a collision pay one ballot.
 // ---------------------------------------------------------------------------
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, bool UNSTABLE, bool ROUTE = false>
 __global__ void __launch_bounds__(THREADS, MINB)
-onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out_keys,
+onesweep_pass_v5_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out_keys,
                         const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
                         uint64_t n, DigitPass dp, const unsigned long long *__restrict__ digit_offsets,
                         unsigned long long *__restrict__ status, unsigned int *tile_counter,
-                        unsigned epoch) {
+                        unsigned epoch, const unsigned char *__restrict__ route_owner = nullptr) {
     constexpr int WARPS = THREADS / 32;
     constexpr int TILE = THREADS * IPT;
     static_assert(THREADS >= RADIX, "one digit per thread in the scan phases");
@@ -339,8 +344,14 @@ onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     long long *goff = reinterpret_cast<long long *>(whist + WARPS * RADIX);  // [RADIX]
     uint32_t *warp_tot = reinterpret_cast<uint32_t *>(goff + RADIX);         // [WARPS + 1]
     __shared__ unsigned int sh_tile;
+    __shared__ unsigned char sh_owner[ROUTE ? RADIX : 1];
+    auto dig = [&](KeyT k, uint32_t v) -> uint32_t {
+        const uint32_t d = digit_of(k, v, dp);
+        return ROUTE ? (uint32_t)sh_owner[d] : d;
+    };
 
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (ROUTE && tid < RADIX) sh_owner[tid] = route_owner[tid];
     if (tid == 0) sh_tile = atomicAdd(tile_counter, 1u);
     for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;
     __syncthreads();
@@ -349,6 +360,7 @@ onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     const uint32_t tile_valid = (uint32_t)(n - tile_base < (uint64_t)TILE ? n - tile_base : TILE);
     const bool full = tile_valid == TILE;
 
+    // ---- load (coalesced, warp-striped) + early per-warp digit counts ----
     KeyT key[IPT];
     uint32_t val[IPT];
     uint32_t *my_hist = whist + warp * RADIX;
@@ -364,32 +376,14 @@ onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
             val[r] = 0;
         }
     }
-
-    // ---- rank inside the warp: 8 ballots per row, running per-warp digit counters ----
-    const unsigned lt = lanemask_lt();
-    uint32_t rank[IPT];
 #pragma unroll
     for (int r = 0; r < IPT; ++r) {
-        const uint32_t idx = warp_base + r * 32 + lane;
-        const bool valid = full || idx < tile_valid;
-        const uint32_t d = digit_of(key[r], val[r], dp);
-        unsigned peers = full ? 0xffffffffu : __ballot_sync(0xffffffffu, valid);
-#pragma unroll
-        for (int b = 0; b < RADIX_BITS; ++b) {
-            const bool bit = (d >> b) & 1u;
-            const unsigned bal = __ballot_sync(0xffffffffu, bit);
-            peers &= bit ? bal : ~bal;
-        }
-        uint32_t before = 0;
-        if (valid) before = my_hist[d];
-        __syncwarp();
-        if (valid && (peers & lt) == 0) my_hist[d] = before + __popc(peers);
-        __syncwarp();
-        rank[r] = before + __popc(peers & lt);
+        uint32_t idx = warp_base + r * 32 + lane;
+        if (full || idx < tile_valid) atomicAdd(&my_hist[dig(key[r], val[r])], 1u);
     }
     __syncthreads();
 
-    // ---- per digit: exclusive prefix over warps, tile count, publish, tile-local digit start ----
+    // ---- per digit: tile count, early publish, tile-local digit start ----
     uint32_t count = 0;
     if (tid < RADIX) {
 #pragma unroll
@@ -409,7 +403,8 @@ onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     if (tid < RADIX) {
         for (unsigned w = 0; w < warp; ++w) local_base += warp_tot[w];
         local_base += inc - count;
-        uint32_t run = local_base;   // whist[w][d] := tile position of warp w's first key with digit d
+        // whist[w][d] := tile position of warp w's first key with digit d
+        uint32_t run = local_base;
 #pragma unroll
         for (int w = 0; w < WARPS; ++w) {
             uint32_t t = whist[w * RADIX + tid];
@@ -419,38 +414,58 @@ onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     }
     __syncthreads();
 
-    // ---- scatter into shared memory in tile-sorted order ----
+    // ---- rank + scatter into tile-sorted order ----
+    const unsigned lt = lanemask_lt();
 #pragma unroll
     for (int r = 0; r < IPT; ++r) {
         const uint32_t idx = warp_base + r * 32 + lane;
-        if (full || idx < tile_valid) {
-            const uint32_t d = digit_of(key[r], val[r], dp);
-            const uint32_t pos = my_hist[d] + rank[r];
-            sh_keys[pos] = key[r];
-            if (HAS_VAL) sh_vals[pos] = val[r];
+        const bool valid = full || idx < tile_valid;
+        const uint32_t d = dig(key[r], val[r]);
+        uint32_t slot = 0;
+        if (UNSTABLE) {
+            if (valid) slot = atomicAdd(&my_hist[d], 1u);
+        } else {
+            uint32_t before = 0;
+            if (valid) before = my_hist[d];
+            __syncwarp();                       // every lane has read the offsets of the row
+            if (valid) slot = atomicAdd(&my_hist[d], 1u);
+            unsigned todo = __ballot_sync(0xffffffffu, valid && slot != before);
+            while (todo) {                      // warp-uniform: one iteration per group of equal digits
+                const int leader = __ffs(todo) - 1;
+                const uint32_t dl = __shfl_sync(0xffffffffu, d, leader);
+                const bool mine = valid && d == dl;
+                const unsigned grp = __ballot_sync(0xffffffffu, mine);
+                if (mine) slot = before + __popc(grp & lt);
+                todo &= ~grp;
+            }
+            __syncwarp();                       // the atomics are visible to the next row's reads
+        }
+        if (valid) {
+            sh_keys[slot] = key[r];
+            if (HAS_VAL) sh_vals[slot] = val[r];
         }
     }
 
     // ---- decoupled look-back per digit ----
     if (tid < RADIX) {
         unsigned long long excl = 0;
-        if (LB == 0) {
-            if (tile > 0) {
-                long long t = (long long)tile - 1;
-                while (true) {
-                    unsigned long long s = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
-                    unsigned flag = (unsigned)(s >> 62);
-                    if (flag == 0 || ((s >> 56) & 63) != epoch) continue;   // not published yet
-                    excl += s & OS_VALUE_MASK;
-                    if (flag == 2) break;
-                    --t;
-                }
+        if (tile > 0) {
+            long long t = (long long)tile - 1;
+            while (true) {
+                unsigned long long s = ld_relaxed_u64(status + (size_t)t * RADIX + tid);
+                unsigned flag = (unsigned)(s >> 62);
+                if (flag == 0 || ((s >> 56) & 63) != epoch) continue;   // not published yet
+                excl += s & OS_VALUE_MASK;
+                if (flag == 2) break;
+                --t;
             }
-        } else {
-            excl = lookback_digit<(LB > 0 ? LB : 1)>(status, tile, tid, epoch);
         }
         st_relaxed_u64(status + (size_t)tile * RADIX + tid, os_pack(2, epoch, excl + count));
-        goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
+        if (ROUTE)   // digit_offsets = the 2^bits destination addresses; goff = byte address of tile slot 0
+            goff[tid] = (long long)digit_offsets[tid]
+                        + ((long long)excl - (long long)local_base) * (long long)sizeof(KeyT);
+        else
+            goff[tid] = (long long)(digit_offsets[tid] + excl) - (long long)local_base;
     }
     __syncthreads();
 
@@ -459,29 +474,33 @@ onesweep_pass_v4_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     for (uint32_t p = tid; p < tile_valid; p += THREADS) {
         KeyT k = sh_keys[p];
         uint32_t v = HAS_VAL ? sh_vals[p] : 0;
-        uint32_t d = digit_of(k, v, dp);
-        size_t dst = (size_t)(goff[d] + (long long)p);
-        out_keys[dst] = k;
-        if (HAS_VAL) out_vals[dst] = v;
+        uint32_t d = dig(k, v);
+        if (ROUTE) {
+            *reinterpret_cast<KeyT *>(goff[d] + (long long)p * (long long)sizeof(KeyT)) = k;
+        } else {
+            size_t dst = (size_t)(goff[d] + (long long)p);
+            out_keys[dst] = k;
+            if (HAS_VAL) out_vals[dst] = v;
+        }
     }
 }
 
-template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB>
-void launch_v4(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
+template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, bool UNSTABLE, bool ROUTE = false>
+void launch_v5(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
                uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
-               unsigned int *ctr, unsigned epoch, cudaStream_t stream) {
+               unsigned int *ctr, unsigned epoch, cudaStream_t stream, const unsigned char *route_owner = nullptr) {
     constexpr int TILE = THREADS * IPT;
     size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
                   + sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
                   + sizeof(uint32_t) * (THREADS / 32 + 1);
-    auto kern = onesweep_pass_v4_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB, LB>;
+    auto kern = onesweep_pass_v5_kernel<KeyT, HAS_VAL, THREADS, IPT, MINB, UNSTABLE, ROUTE>;
     static bool attr_set = false;
     if (!attr_set) {
         MTG_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
     kern<<<(unsigned)div_up(n, (size_t)TILE), THREADS, smem, stream>>>(in_keys, out_keys, in_vals, out_vals, n,
-                                                                      dp, offs, status, ctr, epoch);
+                                                                      dp, offs, status, ctr, epoch, route_owner);
 }
 
 template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB, bool ROUTE = false>
@@ -502,24 +521,28 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
                                                                       dp, offs, status, ctr, epoch, route_owner);
 }
 
-// variant selection (experiments): MTG_SORT_VARIANT, see the switch in radix_sort_impl
+// MTG_SORT_VARIANT=3 selects the round-1 pass (v3: peer masks through shared memory) for A/B timing;
+// anything else: v5. MTG_SORT_UNSTABLE_FIRST=0 keeps the first pass of a sort stable as well.
 static int sort_variant() {
     static int v = -1;
     if (v < 0) {
         const char *e = getenv("MTG_SORT_VARIANT");
-        v = e ? atoi(e) : 20;
+        v = e ? atoi(e) : 5;
     }
     return v;
 }
-
-// (THREADS, IPT) per variant; tile = THREADS * IPT keys
-template <typename KeyT>
-static int variant_tile(int v) {
-    constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;   // u128 tiles hold half the keys
-    switch (v) {
-        case 22: case 31: case 33: return 8192 / S;
-        default: return 4096 / S;
+static bool unstable_first_allowed() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("MTG_SORT_UNSTABLE_FIRST");
+        v = e ? atoi(e) : 1;
     }
+    return v != 0;
+}
+
+template <typename KeyT>
+static int variant_tile(int) {
+    return sizeof(KeyT) == 8 ? 4096 : 2048;   // u128 tiles hold half the keys
 }
 
 template <typename KeyT, bool HAS_VAL>
@@ -572,22 +595,15 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         const unsigned long long *offs = ws.hist + (size_t)p * RADIX;
         unsigned int *ctr = ws.tile_counters + p;
         const unsigned ep = (unsigned)(p + 1);
-#define V3(T, I, B, LBW) launch_v3<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
-#define V4(T, I, B, LBW) launch_v4<KeyT, HAS_VAL, T, I / S, B, LBW>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream)
-        switch (variant) {   // measured alternatives (scripts/sort_bench.py); 20 is the default
-            case 21: V3(256, 16, 4, 0); break;    // 4 blocks per SM
-            case 22: V3(512, 16, 2, 0); break;    // 8192-key tiles
-            case 25: V3(256, 16, 3, 4); break;    // look-back windows of 4 / 8 / 16 / 2 predecessors
-            case 26: V3(256, 16, 3, 8); break;
-            case 27: V3(256, 16, 3, 16); break;
-            case 28: V3(256, 16, 3, 2); break;
-            case 30: V4(256, 16, 3, 0); break;    // ballot-ranked
-            case 31: V4(512, 16, 2, 0); break;
-            case 33: V4(512, 16, 2, 4); break;
-            default: V3(256, 16, 3, 0); break;
-        }
-#undef V3
-#undef V4
+        // the first pass of a sort has no earlier order to preserve: unstable ranking (one shared atomic
+        // per key) when the caller allows it (equal keys may then leave the sort in any order)
+        const bool unstable = p == 0 && plan.unstable_first && unstable_first_allowed();
+        if (variant == 3)
+            launch_v3<KeyT, HAS_VAL, 256, 16 / S, 3, 0>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
+        else if (unstable)
+            launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, true>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
+        else
+            launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, false>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
         if (ws.events) cudaEventRecord(ws.events[2 * p + 1], stream);
         *launches += 1;
         cur ^= 1;
@@ -634,23 +650,30 @@ template void digit_histogram<u128>(const u128 *, uint64_t, DigitPass, unsigned 
 template <typename KeyT>
 void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned char *owner,
                    const unsigned long long *route, unsigned long long *status, unsigned int *tile_counter,
-                   cudaStream_t stream, unsigned *launches) {
+                   cudaStream_t stream, unsigned *launches, bool stable) {
     if (n == 0) return;
     constexpr int S = sizeof(KeyT) == 8 ? 1 : 2;
     const size_t tiles = div_up(n, (size_t)4096 / S);
     MTG_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream));
     MTG_CUDA(cudaMemsetAsync(status, 0, sizeof(unsigned long long) * tiles * RADIX, stream));
-    launch_v3<KeyT, false, 256, 16 / S, 3, 0, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
-                                                    tile_counter, 1u, stream, owner);
+    if (sort_variant() == 3)
+        launch_v3<KeyT, false, 256, 16 / S, 3, 0, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
+                                                        tile_counter, 1u, stream, owner);
+    else if (stable || !unstable_first_allowed())
+        launch_v5<KeyT, false, 256, 16 / S, 4, false, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
+                                                            tile_counter, 1u, stream, owner);
+    else
+        launch_v5<KeyT, false, 256, 16 / S, 4, true, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
+                                                           tile_counter, 1u, stream, owner);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }
 template void route_scatter<uint64_t>(const uint64_t *, uint64_t, DigitPass, const unsigned char *,
                                       const unsigned long long *, unsigned long long *, unsigned int *,
-                                      cudaStream_t, unsigned *);
+                                      cudaStream_t, unsigned *, bool);
 template void route_scatter<u128>(const u128 *, uint64_t, DigitPass, const unsigned char *,
                                   const unsigned long long *, unsigned long long *, unsigned int *, cudaStream_t,
-                                  unsigned *);
+                                  unsigned *, bool);
 
 namespace {
 __global__ void fill_random_kernel(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask,

@@ -21,6 +21,9 @@ struct DigitPass {
 struct SortPlan {
     int n;
     DigitPass p[MAX_SORT_PASSES];
+    // the caller does not care in which order EQUAL keys (with their payloads) leave the sort: the first
+    // pass may then rank unstably (one shared-memory atomic per key instead of the stable ranking)
+    bool unstable_first = false;
 };
 
 // plan covering key bits [lo, hi) in 8-bit digits
@@ -66,13 +69,13 @@ template <typename KeyT>
 void digit_histogram(const KeyT *keys, uint64_t n, DigitPass dp, unsigned long long *hist, cudaStream_t stream,
                      unsigned *launches);
 
-// Grouping + exchange in one kernel: a stable scatter pass in which a key whose digit dp is b goes
+// Grouping + exchange in one kernel: a scatter pass (stable unless stable = false) in which a key whose digit dp is b goes
 // to owner[b] (device array of RADIX bytes) and is stored into the array at address route[owner]
 // (device array of RADIX addresses, local or peer-mapped memory of another GPU).
 // status: sort_status_words(n) words, tile_counter: one word.
 template <typename KeyT>
 void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned char *owner,
                    const unsigned long long *route, unsigned long long *status, unsigned int *tile_counter,
-                   cudaStream_t stream, unsigned *launches);
+                   cudaStream_t stream, unsigned *launches, bool stable = true);
 
 }  // namespace mtg

@@ -25,11 +25,11 @@ def one(variant):
     o2 = np.lexsort((lo, hi))
     ok = ok and bool(np.array_equal(kk[:, 0], lo[o2]) and np.array_equal(kk[:, 1], hi[o2]))
     res = {"variant": variant, "correct": ok}
-    ms = (ctypes.c_float * 3)()
+    ms = (ctypes.c_float * 5)()
     for name, n, bits, wv in (("u64", 400_000_000, 62, 0), ("u64+val", 300_000_000, 62, 1), ("u128", 200_000_000, 126, 0)):
         rc = lib.mtg_debug_sort_bench(0, n, bits, wv, 3, ms)
         bpk = (16 if bits > 64 else 8) + (4 if wv else 0)
-        res[name] = {"rc": rc, "ms_hist": round(ms[0], 3), "ms_pass": round(ms[1], 3), "ms_sort": round(ms[2], 3),
+        res[name] = {"rc": rc, "ms_hist": round(ms[0], 3), "ms_pass": round(ms[1], 3), "ms_sort": round(ms[2], 3), "ms_first_pass": round(ms[3], 3), "ms_later_passes": round(ms[4], 3),
                      "pass_GBps": round(2 * n * bpk / (ms[1] * 1e-3) / 1e9, 1), "n": n}
     print(json.dumps(res), flush=True)
 
@@ -37,6 +37,9 @@ if __name__ == "__main__":
     if len(sys.argv) > 1:
         one(int(sys.argv[1]))
     else:
-        for v in (os.environ.get("VARIANTS", "0,1,2,3,4,5,6")).split(","):
+        # 3 = the round-1 pass kernel (peer masks in shared memory), 5 = atomic slot + collision repair
+        for v in (os.environ.get("VARIANTS", "3,5")).split(","):
             env = dict(os.environ, MTG_SORT_VARIANT=v)
             subprocess.call([sys.executable, __file__, v], env=env)
+        env = dict(os.environ, MTG_SORT_VARIANT="5", MTG_BENCH_UNSTABLE_FIRST="1")
+        subprocess.call([sys.executable, __file__, "5"], env=env)

@@ -1,0 +1,180 @@
+"""The end product and the boundary, through the reference's OWN host code (`-m gpu`):
+
+oracle/_ref/metagraph_gpu_DNA is the reference CLI built from its unmodified sources (oracle/build_ref_cli.sh)
+with ONE hunk in IBOSSChunkConstructor::initialize (boss_chunk_construct.cpp:1134) that asks the binding
+projects2014-metagenome_b200/host/metagraph_binding/boss_chunk_construct_gpu.cpp first; everything after the
+chunk (BOSS::initialize, wt_huff / rank-select construction, DBGSuccinct::serialize, mask_dummy_kmers, node
+weights) is the reference's code. oracle/_ref/metagraph_DNA is the same CLI without the hunk.
+
+  * `.dbg` / `.dbg.weights` byte-identical to the reference's (BASELINE cfg #1 fixture, hashes recorded in
+    SURVEY.md 8c; synthetic reads at 1 M reads; --mask-dummy; chunked --suffix build + concatenate)
+  * the reference's gtest file tests/graph/succinct/test_boss_construct.cpp, unmodified, with MTG_GPU=1
+  * cfg #2 at its full size (10 M reads): the four chunk files of the GPU build against the reference's
+    constructor (oracle/_ref/ref_driver_DNA) run on the same box
+
+TEST INFRASTRUCTURE (runs oracle/_ref binaries)."""
+import hashlib
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import mtg_b200
+import oracle_lib
+from mtg_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.path.join(ROOT, "oracle", "_ref")
+CPU_CLI = os.path.join(REF, "metagraph_DNA")
+GPU_CLI = os.path.join(REF, "metagraph_gpu_DNA")
+UNIT = os.path.join(REF, "unit_tests_gpu_DNA")
+FIXTURE = os.path.join(ROOT, "tests", "data", "transcripts_1000.fa")
+
+# SURVEY.md 8c, recorded from the reference's own `metagraph build` (re-generated in this round:
+# oracle/_ref/metagraph_DNA reproduces all three)
+DBG_K12 = "cc1b643af786a33017baf3c7f058ede1f6f83d229ca2667cf595d45d71935122"
+DBG_K12_CANON_COUNT = "2cb0dbaa1a918f272d583df3aa3ddd7ad7be37657f42a47a804110cde146c42f"
+WEIGHTS_K12_CANON_COUNT = "f1edd9e0c197e029b2804bf184f6f543bf036cfbe53a6c962ae4ac3fd6026cb8"
+
+
+def need(path):
+    if not os.path.exists(path):
+        pytest.fail("%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` where "
+                    "/root/reference is present (oracle/build_ref_cli.sh)" % path)
+
+
+def sha(path):
+    h = hashlib.sha256()
+    with open(path, "rb") as f:
+        for blk in iter(lambda: f.read(1 << 24), b""):
+            h.update(blk)
+    return h.hexdigest()
+
+
+def run(binary, args, gpu, cwd):
+    env = dict(os.environ)
+    env.pop("MTG_GPU", None)
+    if gpu:
+        env["MTG_GPU"] = "1"
+        env["MTG_GPU_REPORT"] = "1"
+    p = subprocess.run([binary] + args, cwd=cwd, env=env, capture_output=True, text=True, timeout=1800)
+    assert p.returncode == 0, p.stdout[-2000:] + p.stderr[-2000:]
+    return p
+
+
+def write_fasta(path, packed):
+    """one read per record, header '>r' """
+    n, L1 = packed.shape
+    out = np.empty((n, 3 + L1), dtype=np.uint8)
+    out[:, 0], out[:, 1], out[:, 2] = ord(">"), ord("r"), ord("\n")
+    out[:, 3:] = packed
+    out[:, -1] = ord("\n")
+    out.tofile(path)
+
+
+def test_cfg1_dbg_matches_recorded_reference_hashes(tmp_path):
+    """BASELINE cfg #1: `metagraph build -k 12` on tests/data/transcripts_1000.fa."""
+    need(GPU_CLI)
+    p = run(GPU_CLI, ["build", "-k", "12", "-o", "basic", FIXTURE], True, tmp_path)
+    assert "chunks built on the GPU: 1" in p.stderr, p.stderr[-500:]
+    assert sha(tmp_path / "basic.dbg") == DBG_K12
+    run(GPU_CLI, ["build", "-k", "12", "--mode", "canonical", "--count-kmers", "-o", "cc", FIXTURE], True, tmp_path)
+    assert sha(tmp_path / "cc.dbg") == DBG_K12_CANON_COUNT
+    assert sha(tmp_path / "cc.dbg.weights") == WEIGHTS_K12_CANON_COUNT
+
+
+@pytest.mark.parametrize("args", [
+    ["-k", "31", "--mode", "canonical"],                       # cfg #2's mode
+    ["-k", "31", "--count-kmers", "--count-width", "8"],        # cfg #3's mode
+    ["-k", "63"],                                               # cfg #4: 128-bit k-mers
+    ["-k", "20", "--mask-dummy", "-p", "4"],                    # every integration_tests/test_build.py command
+    ["-k", "25", "--mode", "canonical", "--count-kmers", "--count-width", "16", "--mask-dummy"],
+    ["-k", "31", "--mode", "canonical", "--disk-swap", "SWAP"],  # VECTOR_DISK container: accepted, HBM either way
+])
+def test_dbg_equals_reference_cli_on_same_box(args, tmp_path):
+    """Every output file of `metagraph build` from the GPU constructor == the CPU reference's, same reads."""
+    need(GPU_CLI)
+    need(CPU_CLI)
+    n_reads = 300_000 if "63" not in args else 150_000
+    packed = synth.dna_reads_packed_np(4242, n_reads, 150, 3_000_000, 0.005)
+    fa = str(tmp_path / "reads.fa")
+    write_fasta(fa, packed)
+    args = [a if a != "SWAP" else str(tmp_path) for a in args]
+    for name, binary, gpu in (("cpu", CPU_CLI, False), ("gpu", GPU_CLI, True)):
+        d = tmp_path / name
+        d.mkdir()
+        p = run(binary, ["build"] + args + ["-o", "g", fa], gpu, d)
+        if gpu:
+            assert "chunks built on the GPU: 1" in p.stderr, p.stderr[-500:]
+    files = sorted(os.listdir(tmp_path / "cpu"))
+    assert "g.dbg" in files and files == sorted(os.listdir(tmp_path / "gpu"))
+    for f in files:
+        assert sha(tmp_path / "cpu" / f) == sha(tmp_path / "gpu" / f), f
+
+
+def test_chunked_suffix_build_and_concatenate(tmp_path):
+    """`build --suffix` chunks (KmerExtractorBOSS path) from the GPU + the reference's `concatenate`."""
+    need(GPU_CLI)
+    need(CPU_CLI)
+    packed = synth.dna_reads_packed_np(99, 60_000, 120, 500_000, 0.01)
+    fa = str(tmp_path / "reads.fa")
+    write_fasta(fa, packed)
+    for name, binary, gpu in (("cpu", CPU_CLI, False), ("gpu", GPU_CLI, True)):
+        d = tmp_path / name
+        d.mkdir()
+        for sfx in ("$", "A", "C", "G", "T"):
+            run(binary, ["build", "-k", "21", "--suffix", sfx, "-o", "part", fa], gpu, d)
+        chunks = sorted(f for f in os.listdir(d) if f.endswith(".dbg.chunk"))
+        assert len(chunks) == 5
+        run(binary, ["concatenate", "-l", "1", "-i", "part", "-o", "full"], gpu, d)
+    full = sorted(f for f in os.listdir(tmp_path / "cpu") if f.startswith("full"))
+    assert "full.dbg" in full
+    for f in full:
+        assert sha(tmp_path / "cpu" / f) == sha(tmp_path / "gpu" / f), f
+
+
+def test_reference_gtest_suite_through_the_c_abi():
+    """The reference's own unit tests of this path (test_boss_construct.cpp:51-331: construction ==
+    dynamic insertion for every k, weighted, canonical, chunks), unmodified, with the constructor
+    replaced by the CUDA library. k + 1 > 64 (keys wider than 128 bits) stays on the reference's CPU
+    constructor and is reported."""
+    need(UNIT)
+    os.makedirs(os.path.join(REF, "test_data"), exist_ok=True)
+    p = run(UNIT, ["--gtest_filter=BOSSConstruct*:WeightedBOSSConstruct*"], True, REF)
+    out = p.stdout + p.stderr
+    assert "[  PASSED  ] 11 tests" in out, out[-3000:]
+    line = [ln for ln in p.stderr.splitlines() if "chunks built on the GPU" in ln][-1]
+    n_gpu = int(line.split("chunks built on the GPU:")[1].split(",")[0])
+    assert n_gpu > 500, line          # 11 tests x k = 1..63 (and chunked variants)
+
+
+def test_cfg2_full_size_chunk_files_equal_reference(tmp_path):
+    """BASELINE cfg #2 at the benchmarked size: 10 M x 150 bp reads, k = 31, canonical. The reference's
+    constructor (all host threads) and the GPU build must write identical chunk files."""
+    import torch
+    drv = oracle_lib.ref_driver("DNA")
+    assert drv, "oracle/_ref/ref_driver_DNA is missing"
+    n_reads, L, K, G = 10_000_000, 150, 31, 100_000_000
+    packed = synth.dna_reads_packed_torch(1, n_reads, L, G, 0.005, device="cuda")
+    src = "/dev/shm/mtg_cfg2_reads.txt" if os.path.isdir("/dev/shm") else str(tmp_path / "reads.txt")
+    try:
+        host = packed.cpu().numpy()
+        host[:, -1] = ord("\n")
+        host.tofile(src)
+        del host
+        subprocess.check_call([drv, "-k", str(K), "--canonical", "-p", str(os.cpu_count() or 8), "--mem-gb", "16",
+                               "-o", str(tmp_path / "ref"), src], stdout=subprocess.DEVNULL)
+    finally:
+        if os.path.exists(src):
+            os.remove(src)
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, True, 0)
+    ctor.add_packed_device(packed.data_ptr(), packed.numel(), n_reads * (L - K + 1))
+    torch.cuda.synchronize()
+    chunk = ctor.build_chunk(copy=False)
+    chunk.serialize(str(tmp_path / "gpu"))
+    ctor.close()
+    for ext in ("", ".W", ".last", ".weights"):
+        assert sha(str(tmp_path / ("ref.dbg.chunk" + ext))) == sha(str(tmp_path / ("gpu.dbg.chunk" + ext))), ext
