@@ -45,7 +45,10 @@ def parse_args():
     ap.add_argument("--reads", type=int, default=0, help="override the number of reads (debug)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--cpu-sample-reads", type=int, default=1_000_000)
+    ap.add_argument("--cpu-sample-reads", type=int, default=0,
+                    help="reads of the CPU legs (0 = the whole workload, the default: same config as the GPU arm)")
+    ap.add_argument("--cpu-mem-gb", type=float, default=16.0,
+                    help="--mem-cap of the reference build (16 GB: its best case, no shrink cycles on cfg #2)")
     ap.add_argument("--no-parity-check", action="store_true",
                     help="N > 1: skip the untimed DistBuild-vs-oracle verification builds")
     return ap.parse_args()
@@ -125,7 +128,7 @@ def algorithmic_bytes(st, R, w, c, P, canonical, W_width, bpc):
     return b
 
 
-def cpu_reference_run(wl, n_reads, threads, repeats=1):
+def cpu_reference_run(wl, n_reads, threads, repeats=1, mem_gb=16.0):
     """Times the reference's own CPU implementation (oracle/_ref/ref_driver_DNA, built from the
     unmodified /root/reference sources) on a bounded sample of the workload. Returns
     (kmers_per_s, info) or (None, why)."""
@@ -151,7 +154,8 @@ def cpu_reference_run(wl, n_reads, threads, repeats=1):
             return n_kmers / dt, dict(kind="port", cores=1, seconds=dt, all_seconds=[dt] * repeats,
                                       n_reads=n_reads, sample="%d reads x %d bp "
                                       "(same coverage), oracle/mtg_oracle.cpp" % (n_reads, wl["read_len"]))
-        path = os.path.join(td, "reads.txt")
+        shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else td
+        path = os.path.join(shm, "mtg_bench_reads_%d.txt" % os.getpid())
         genome = synth.genome_np(wl["seed"], G)
         with open(path, "wb") as f:
             for r0 in range(0, n_reads, 200_000):
@@ -160,25 +164,35 @@ def cpu_reference_run(wl, n_reads, threads, repeats=1):
                                               genome=genome)
                 p[:, -1] = ord("\n")
                 f.write(p.tobytes())
-        cmd = [drv, "-k", str(wl["K"]), "-p", str(threads), "--mem-gb", "8", "-o",
+        cmd = [drv, "-k", str(wl["K"]), "-p", str(threads), "--mem-gb", str(mem_gb), "-o",
                os.path.join(td, "out"), path]
         if wl["canonical"]:
             cmd.append("--canonical")
         if wl["bpc"]:
             cmd += ["--count-width", str(wl["bpc"])]
-        secs = []
-        for _ in range(repeats):
-            out = subprocess.run(cmd, capture_output=True, text=True, timeout=1500)
-            if out.returncode != 0:
-                return None, "ref_driver failed: " + out.stderr[-200:]
-            fields = out.stdout.split()
-            secs.append(float(fields[fields.index("build_sec") + 1]))
+        secs, push, read = [], [], []
+        try:
+            for _ in range(repeats):
+                out = subprocess.run(cmd, capture_output=True, text=True, timeout=3000)
+                if out.returncode != 0:
+                    return None, "ref_driver failed: " + out.stderr[-200:]
+                fields = out.stdout.split()
+                secs.append(float(fields[fields.index("build_sec") + 1]))
+                push.append(float(fields[fields.index("push_sec") + 1]))
+                read.append(float(fields[fields.index("read_sec") + 1]))
+        finally:
+            if os.path.exists(path):
+                os.remove(path)
         build_sec = secs[-1]
+        whole = n_reads == wl["n_reads"]
         return n_kmers / build_sec, dict(
             kind="reference", cores=threads, seconds=build_sec, all_seconds=secs, n_reads=n_reads,
-            sample="%d reads x %d bp, genome %d bp (same coverage as the workload), "
-                   "reference IBOSSChunkConstructor add_sequences+build_chunk, -p %d"
-                   % (n_reads, wl["read_len"], G, threads))
+            push_seconds=push, read_seconds_untimed=read,
+            sample="%s: %d reads x %d bp, genome %d bp; the reference's IBOSSChunkConstructor (unmodified sources, "
+                   "g++ -O3) add_sequences + build_chunk from reads parsed into host memory beforehand, "
+                   "-p %d, --mem-cap %g GB"
+                   % ("the WHOLE workload" if whole else "a sample with the workload's coverage",
+                      n_reads, wl["read_len"], G, threads, mem_gb))
 
 
 def run_reference(args, wl):
@@ -186,12 +200,15 @@ def run_reference(args, wl):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    n_reads = min(wl["n_reads"], args.cpu_sample_reads)
-    v, info = cpu_reference_run(wl, n_reads, threads, repeats=args.warmup + args.steps)
+    n_reads = min(wl["n_reads"], args.cpu_sample_reads) if args.cpu_sample_reads else wl["n_reads"]
+    # a full-size reference build takes ~30 s: at most 3 of them (1 warm-up + 2 timed), said in the line
+    runs = max(1, min(3, args.warmup + args.steps))
+    n_warm = 1 if runs > 1 and args.warmup > 0 else 0
+    v, info = cpu_reference_run(wl, n_reads, threads, repeats=runs, mem_gb=args.cpu_mem_gb)
     if v is None:
         print(json.dumps({"impl": "reference", "unavailable": info}))
         return
-    secs = info["all_seconds"][args.warmup:]
+    secs = info["all_seconds"][n_warm:]
     per_step = info["n_reads"] * (wl["read_len"] - wl["K"] + 1)
     value = per_step * len(secs) / sum(secs)
     vals = [(value, x) for x in secs]
@@ -200,9 +217,15 @@ def run_reference(args, wl):
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": 1e3 * sum(s for _, s in vals) / len(vals), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": wl["name"], "sample": info["sample"]},
+        "config": {"workload": wl["name"], "n_reads": info["n_reads"], "read_len": wl["read_len"], "k": wl["K"],
+                   "mode": "canonical" if wl["canonical"] else "basic", "count_width": wl["bpc"],
+                   "sample": info["sample"],
+                   "repeats": "%d full builds run (%d warm-up + %d timed): capped at 3, each takes tens of "
+                              "seconds" % (runs, n_warm, len(secs))},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": info["cores"],
-                         "kind": info["kind"], "sample": info["sample"]},
+                         "kind": info["kind"], "sample": info["sample"],
+                         "seconds_per_build": secs, "push_seconds": info.get("push_seconds"),
+                         "read_seconds_untimed": info.get("read_seconds_untimed")},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line))
@@ -376,10 +399,13 @@ def run_ours(args, wl):
     cpu = None
     if not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
-        v, info = cpu_reference_run(wl, min(n_reads, args.cpu_sample_reads), threads)
+        n_cpu = min(n_reads, args.cpu_sample_reads) if args.cpu_sample_reads else n_reads
+        v, info = cpu_reference_run(wl, n_cpu, threads, mem_gb=args.cpu_mem_gb)
         if v is not None:
             cpu = {"value": v, "unit": UNIT, "cores": info["cores"], "kind": info["kind"],
-                   "sample": info["sample"], "seconds": info["seconds"]}
+                   "sample": info["sample"], "seconds": info["seconds"],
+                   "push_seconds": info.get("push_seconds"),
+                   "read_seconds_untimed": info.get("read_seconds_untimed")}
         else:
             cpu = {"value": None, "unit": UNIT, "cores": threads, "kind": "reference", "sample": info}
 
