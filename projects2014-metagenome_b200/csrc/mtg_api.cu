@@ -212,11 +212,19 @@ struct mtg_ctx {
     std::vector<uint8_t> suffix;   // --suffix filter in BOSS codes (0 = '$'); empty = default build
     std::string error;
     unsigned launches = 0;
+    // Super-batching (SortedSet::shrink_data, common/sorted_sets/sorted_set.hpp:69-82: "buffer full ->
+    // sort + dedupe what is there, go on appending"): once the pushed reads hold batch_limit k-mer
+    // windows they are extracted, sorted and folded into a sorted run of distinct k-mers (+ counts) and
+    // the reads are dropped; mtg_build_chunk merges the runs (saturating count sums).
+    std::vector<RealSet> runs;
+    uint64_t pending_windows = 0, batch_limit = 0, n_batches = 0;
     // range-partitioned (multi-GPU) build state, see mtg_mg_* below
     struct Mg {
         DevBuf keys, targets, tset, sinks, src, rkeys, rcounts;
         RealSet reals;
         uint64_t nt = 0, n_sink = 0, n_src = 0, n_input = 0, n_routed = 0, n_routed_targets = 0;
+        RealSet acc;        // mtg_mg_accumulate: the folded k-mers of the earlier rounds of this range
+        bool has_acc = false;
     } mg;
 };
 
@@ -412,6 +420,12 @@ int mtg_create(const mtg_params *p, mtg_ctx **out) {
         }
         MTG_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
         ctx->stream = ctx->own_stream;
+        // super-batch size: the sort ping-pongs two key arrays, which may take ~35 % of the device
+        // memory; the rest is for the reads, the folded runs and the later stages. MTG_BATCH_KMERS
+        // overrides (the tests force the batched path on small inputs with it)
+        const uint64_t kb = ctx->al.K * ctx->al.L <= 64 ? 8 : 16;
+        ctx->batch_limit = (uint64_t)(0.35 * (double)prop.totalGlobalMem / (2.0 * (double)(kb + (p->bits_per_count ? 4 : 0))));
+        if (const char *e = getenv("MTG_BATCH_KMERS")) ctx->batch_limit = strtoull(e, nullptr, 10);
     } catch (const CudaError &e) {
         int rc = fail_cuda(nullptr, e);
         delete ctx;
@@ -445,6 +459,10 @@ void mtg_pack_reads(const char *bases, const uint64_t *offsets, size_t n_reads, 
     pack_parallel(bases, offsets, 0, n_reads, dst);
     memset(dst + raw, 0, mtg_packed_size(offsets, n_reads) - raw);
 }
+
+}  // extern "C"
+namespace { void maybe_flush_batch(mtg_ctx *ctx, uint64_t new_windows); }
+extern "C" {
 
 int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, const uint64_t *counts,
                    size_t n_reads) {
@@ -527,6 +545,10 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
                 ctx->segs.push_back(std::move(seg));
                 // d_raw / d_off go back to the arena here: all work of the context is ordered on s
             }
+            {
+                std::lock_guard<std::mutex> lk(ctx->mu);
+                maybe_flush_batch(ctx, nwin);
+            }
             r0 = r1;
         }
         if (pinned_src) MTG_CUDA(cudaStreamSynchronize(ctx->stream));   // the caller's memory is free again
@@ -540,11 +562,18 @@ int mtg_push_packed_device(mtg_ctx *ctx, const void *d_packed, size_t n_bytes, u
     if (!ctx || !d_packed) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
     if (((uintptr_t)d_packed & 15) != 0) return fail(ctx, MTG_ERR_BAD_ARG, "packed reads must be 16-byte aligned");
     std::lock_guard<std::mutex> lk(ctx->mu);
-    ReadSegment seg;
-    seg.d_packed = (const uint8_t *)d_packed;
-    seg.nbytes = n_bytes;
-    seg.n_windows_max = n_windows_max;
-    ctx->segs.push_back(std::move(seg));
+    try {
+        MTG_CUDA(cudaSetDevice(ctx->device));
+        t_arena = ctx->arena;
+        ReadSegment seg;
+        seg.d_packed = (const uint8_t *)d_packed;
+        seg.nbytes = n_bytes;
+        seg.n_windows_max = n_windows_max;
+        ctx->segs.push_back(std::move(seg));
+        maybe_flush_batch(ctx, n_windows_max);   // a full batch is folded into a run here (the buffer is read now)
+    } catch (const CudaError &e) {
+        return fail_cuda(ctx, e);
+    }
     return MTG_OK;
 }
 
@@ -654,8 +683,11 @@ void run_extraction(mtg_ctx *ctx, bool both, bool payload, KeyT *out_keys, uint3
 // With ext_keys (multi-GPU: the k-mers routed to this key range, both strands already present)
 // extraction and rc completion are skipped.
 template <typename KeyT>
+void complete_reverse_complements(mtg_ctx *ctx, DevBuf &keysB, DevBuf &counts, uint64_t m, RealSet *rs);
+
+template <typename KeyT>
 void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nullptr,
-                   const void *ext_keys = nullptr, uint64_t ext_n = 0) {
+                   const void *ext_keys = nullptr, uint64_t ext_n = 0, bool skip_rc = false) {
     cudaStream_t s = ctx->stream;
     const Alpha al = ctx->al;
     const bool counting = ctx->prm.bits_per_count > 0;
@@ -759,15 +791,32 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
     const uint64_t cap = canon ? 2 * m : m;
     if (tm) tm->mark();
 
-    if (!canon || ext_keys) {
+    if (!canon || ext_keys || skip_rc) {
         rs->keys = std::move(keysB);
         rs->counts = std::move(counts);
         rs->m = m;
         if (tm) tm->mark();
         return;
     }
-    // canonical: reverse complements of the non-palindromes, sorted on their own and merged with
-    // the (already sorted) canonical half == add_reverse_complements' re-sort of the doubled array
+    (void)cap;
+    complete_reverse_complements<KeyT>(ctx, keysB, counts, m, rs);
+    if (tm) tm->mark();
+}
+
+// canonical: reverse complements of the non-palindromes, sorted on their own and merged with
+// the (already sorted) canonical half == add_reverse_complements' re-sort of the doubled array
+// (boss_chunk_construct.cpp:179-222). keysB / counts: the m sorted distinct canonical k-mers.
+template <typename KeyT>
+void complete_reverse_complements(mtg_ctx *ctx, DevBuf &keysB, DevBuf &counts, uint64_t m, RealSet *rs) {
+    cudaStream_t s = ctx->stream;
+    const Alpha al = ctx->al;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
+    SortPlan plan;
+    plan.n = 0;
+    plan_add_key_bits(plan, 0, al.K * al.L);
     DevBuf rb0(sizeof(KeyT) * std::max<uint64_t>(m, 1), s), rb1(sizeof(KeyT) * std::max<uint64_t>(m, 1), s);
     DevBuf cb0, cb1;
     if (counting) { cb0.alloc(4 * std::max<uint64_t>(m, 1), s); cb1.alloc(4 * std::max<uint64_t>(m, 1), s); }
@@ -793,8 +842,76 @@ void collect_reals(mtg_ctx *ctx, RealSet *rs, Timer *tm, SortProfile *prof = nul
     rs->keys = std::move(merged);
     rs->counts = std::move(merged_counts);
     rs->m = m2;
-    (void)cap;
-    if (tm) tm->mark();
+}
+
+// Two sorted runs of distinct k-mers (+ counts) -> one: merge-path merge, then equal neighbours are
+// folded with saturating count sums (sorted_multiset.cpp:70-82). This is the merge step of the
+// super-batched build (SortedSet::shrink_data semantics) and of mtg_mg_accumulate.
+template <typename KeyT>
+void merge_fold_runs(mtg_ctx *ctx, RealSet &a, RealSet &b, RealSet *out) {
+    cudaStream_t s = ctx->stream;
+    const bool counting = ctx->prm.bits_per_count > 0;
+    const uint64_t n = a.m + b.m;
+    DevBuf ctr(64, s);
+    unsigned long long *d_ctr = ctr.as<unsigned long long>();
+    MTG_CUDA(cudaMemsetAsync(d_ctr, 0, 64, s));
+    DevBuf mk(sizeof(KeyT) * std::max<uint64_t>(n, 1) + 16, s), mc;
+    if (counting) mc.alloc(4 * std::max<uint64_t>(n, 1), s);
+    {
+        DevBuf part(8 * merge_partition_words(n), s);
+        merge_sorted<KeyT>(a.keys.as<KeyT>(), a.m, b.keys.as<KeyT>(), b.m, counting ? a.counts.as<uint32_t>() : nullptr,
+                           counting ? b.counts.as<uint32_t>() : nullptr, mk.as<KeyT>(),
+                           counting ? mc.as<uint32_t>() : nullptr, part.as<uint64_t>(), s, &ctx->launches);
+    }
+    const uint64_t n_input = a.n_input + b.n_input;
+    a.keys.release(); a.counts.release(); b.keys.release(); b.counts.release();
+    DevBuf dst(sizeof(KeyT) * std::max<uint64_t>(n, 1) + 16, s), starts;
+    if (counting) starts.alloc(8 * (n + 1), s);
+    {
+        DevBuf status(sizeof(unsigned long long) * unique_status_words(n), s), tctr(sizeof(unsigned int), s);
+        unique_keys<KeyT>(mk.as<KeyT>(), n, dst.as<KeyT>(), counting ? starts.as<uint64_t>() : nullptr, d_ctr,
+                          status.as<unsigned long long>(), tctr.as<unsigned int>(), s, &ctx->launches);
+    }
+    const uint64_t m = read_counter(d_ctr, s);
+    DevBuf dc;
+    if (counting) {
+        dc.alloc(4 * std::max<uint64_t>(m, 1), s);
+        run_counts(starts.as<uint64_t>(), mc.as<uint32_t>(), m, ctx->cmax, dc.as<uint32_t>(), s, &ctx->launches);
+    }
+    out->keys = std::move(dst);
+    out->counts = std::move(dc);
+    out->m = m;
+    out->n_input = n_input;
+}
+
+// the reads pushed so far -> one sorted run of distinct (canonical) k-mers; the reads are dropped
+template <typename KeyT>
+void flush_batch(mtg_ctx *ctx) {
+    if (ctx->segs.empty()) return;
+    RealSet rs;
+    collect_reals<KeyT>(ctx, &rs, nullptr, nullptr, nullptr, 0, /*skip_rc=*/true);
+    ctx->runs.push_back(std::move(rs));
+    ctx->segs.clear();
+    ctx->any_explicit_counts = false;
+    ctx->pending_windows = 0;
+    ctx->n_batches += 1;
+}
+
+// pairwise merge rounds over the runs -> one run
+template <typename KeyT>
+void merge_all_runs(mtg_ctx *ctx, std::vector<RealSet> &runs, RealSet *out) {
+    while (runs.size() > 1) {
+        std::vector<RealSet> next;
+        for (size_t i = 0; i + 1 < runs.size(); i += 2) {
+            RealSet m;
+            merge_fold_runs<KeyT>(ctx, runs[i], runs[i + 1], &m);
+            next.push_back(std::move(m));
+        }
+        if (runs.size() & 1) next.push_back(std::move(runs.back()));
+        runs.swap(next);
+    }
+    *out = std::move(runs[0]);
+    runs.clear();
 }
 
 // sources-1 nodes (forward-lex, unsorted) -> all dummy source k-mers; the result arrays hold
@@ -984,7 +1101,25 @@ void build_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
     Timer tm(s);
     RealSet rs;
     SortProfile prof;
-    collect_reals<KeyT>(ctx, &rs, &tm, &prof);   // marks 0..4: start, extract, sort, unique, rc
+    if (ctx->runs.empty()) {
+        collect_reals<KeyT>(ctx, &rs, &tm, &prof);   // marks 0..4: start, extract, sort, unique, rc
+    } else {
+        // super-batched input: last batch, merge of the runs, then the second strand
+        tm.mark();
+        flush_batch<KeyT>(ctx);
+        tm.mark();
+        tm.mark();
+        RealSet all;
+        merge_all_runs<KeyT>(ctx, ctx->runs, &all);
+        tm.mark();
+        if (ctx->prm.both_strands) {
+            complete_reverse_complements<KeyT>(ctx, all.keys, all.counts, all.m, &rs);
+            rs.n_input = all.n_input;
+        } else {
+            rs = std::move(all);
+        }
+        tm.mark();
+    }
     const uint64_t m = rs.m;
     const KeyT *reals = rs.keys.as<KeyT>();
 
@@ -1150,7 +1285,17 @@ void build_suffix_impl(mtg_ctx *ctx, mtg_chunk *out, bool device_output) {
 
 void clear_ctx(mtg_ctx *ctx) {
     ctx->segs.clear();
+    ctx->runs.clear();
+    ctx->pending_windows = 0;
     ctx->any_explicit_counts = false;
+}
+
+// caller holds ctx->mu: cut a batch when the pending reads hold batch_limit k-mer windows
+void maybe_flush_batch(mtg_ctx *ctx, uint64_t new_windows) {
+    ctx->pending_windows += new_windows;
+    if (!ctx->batch_limit || ctx->pending_windows < ctx->batch_limit || !ctx->suffix.empty()) return;
+    if (ctx->al.K * ctx->al.L <= 64) flush_batch<uint64_t>(ctx);
+    else flush_batch<u128>(ctx);
 }
 
 }  // namespace

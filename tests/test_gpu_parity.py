@@ -419,3 +419,39 @@ def test_push_reads_from_many_threads(canonical, bpc, explicit):
     assert chunk.n_rows == ref["n_rows"]
     assert np.array_equal(chunk.W, ref["W"]) and np.array_equal(chunk.last, ref["last"])
     assert np.array_equal(chunk.F, ref["F"]) and np.array_equal(chunk.weights, ref["weights"])
+
+
+@pytest.mark.parametrize("K,alphabet,canonical,bpc,explicit", [
+    (31, "DNA", True, 0, False), (31, "DNA", True, 8, False), (31, "DNA", False, 12, True),
+    (63, "DNA", True, 16, False), (12, "DNA", False, 0, False), (9, "Protein", False, 8, False)])
+def test_super_batched_build(K, alphabet, canonical, bpc, explicit, monkeypatch):
+    """Inputs larger than one sort buffer: with MTG_BATCH_KMERS forced small the pushed reads are folded
+    into sorted runs batch by batch and mtg_build_chunk merges the runs (SortedSet::shrink_data semantics,
+    sorted_set.hpp:69-82; saturating count sums, sorted_multiset.cpp:70-82; palindrome doubling after the
+    merge, boss_chunk_construct.cpp:205-211). The chunk must equal the oracle's single-pass chunk."""
+    monkeypatch.setenv("MTG_BATCH_KMERS", "40000")
+    if alphabet == "DNA":
+        reads = dna_reads(500 + K, 6000, 100, 40_000, n_frac=0.001)
+        reads[7] = "ACGT" * 25          # palindromic k-mers: counts are doubled once, after the merge
+        reads += reads[:800]             # the same k-mers in different batches
+    else:
+        rng = np.random.default_rng(5)
+        reads = ["".join(rng.choice(list("ACDEFGHIKLMNPQRSTVWY"), 60)) for _ in range(3000)]
+        reads += reads[:500]
+    counts = [1 + (i % 300) for i in range(len(reads))] if explicit else None
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, canonical, bpc, alphabet=alphabet)
+    step = 500
+    for i in range(0, len(reads), step):
+        if explicit:
+            ctor.add_sequences(list(zip(reads[i:i + step], counts[i:i + step])))
+        else:
+            ctor.add_sequences(reads[i:i + step])
+    chunk = ctor.build_chunk()
+    ctor.close()
+    ref = oracle_lib.oracle_build(reads, K, alphabet=alphabet, canonical=canonical, bits_per_count=bpc, counts=counts)
+    assert chunk.n_rows == ref["n_rows"] and chunk.stats["n_real"] == ref["n_real"]
+    assert chunk.stats["n_input_kmers"] == sum(max(0, len(r) - K + 1) for r in reads) or "N" in "".join(reads[:50])
+    assert np.array_equal(chunk.W, ref["W"]) and np.array_equal(chunk.last, ref["last"])
+    assert np.array_equal(chunk.F, ref["F"])
+    if bpc:
+        assert np.array_equal(chunk.weights, ref["weights"])
