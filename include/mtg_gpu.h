@@ -198,6 +198,12 @@ int mtg_mg_targets(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_targets, uint
 int mtg_mg_targets_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n);
 int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner /* [2^part_bits] */, uint32_t n_owners,
                          const uint64_t *owner_dst /* [n_owners] device addresses */);
+/* Inputs larger than one round's buffers (super-batching, SortedSet::shrink_data semantics,
+ * common/sorted_sets/sorted_set.hpp:69-82): the caller repeats push -> mtg_mg_count -> mtg_mg_route ->
+ * mtg_mg_collect with the SAME bucket ranges for every slice of its reads and folds each result into the
+ * range's accumulated k-mer set with mtg_mg_accumulate (merge + saturating count sums). last != 0 ends
+ * the rounds: the accumulated set is the range's k-mer set for mtg_mg_strands / mtg_mg_targets*. */
+int mtg_mg_accumulate(mtg_ctx *ctx, int last, uint64_t *n_real);
 /* Verification hook of the fused exchanges (multi_gpu.py, MTG_MG_VERIFY): the device array the next
  * route call will scatter -- which = 0: the k-mers counted by mtg_mg_count, which = 1: the target nodes
  * counted by mtg_mg_targets_count. Library memory, valid until that route call. */

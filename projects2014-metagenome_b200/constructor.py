@@ -308,6 +308,12 @@ class BOSSChunkConstructor:
         self._check(self._lib.mtg_mg_targets_route(self._ctx, own.ctypes.data_as(ctypes.POINTER(ctypes.c_uint32)),
                                                    dst.shape[0], dst.ctypes.data_as(ctypes.POINTER(ctypes.c_uint64))))
 
+    def mg_accumulate(self, last):
+        """fold the last mg_collect result into the accumulated k-mers of this range (super-batched build)"""
+        m = ctypes.c_uint64()
+        self._check(self._lib.mtg_mg_accumulate(self._ctx, int(bool(last)), ctypes.byref(m)))
+        return m.value
+
     def mg_debug_pending(self, which):
         """verification hook: (device pointer, n) of the array the next route call scatters
         (which = 0: k-mers after mg_count, 1: target nodes after mg_targets_count)"""

@@ -1577,7 +1577,7 @@ void mg_extract_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, void **
         if (cur == 1) std::swap(a, b);
     }
     ctx->mg.keys = std::move(a);
-    ctx->mg.n_input = both ? n / 2 : n;
+    ctx->mg.n_input += both ? n / 2 : n;
     *d_keys = ctx->mg.keys.p;
     *n_out = n;
     ctx->segs.clear();
@@ -1613,7 +1613,7 @@ void mg_count_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *bucket_counts, uint64_t 
         for (uint32_t i = 0; i < nb; ++i) bucket_counts[i] = h[i];
     }
     ctx->mg.keys = std::move(a);
-    ctx->mg.n_input = n;
+    ctx->mg.n_input += n;      // summed over the rounds of a super-batched build (mtg_mg_accumulate)
     ctx->mg.n_routed = n;
     *n_out = n;
     ctx->segs.clear();
@@ -2135,6 +2135,31 @@ int mtg_mg_targets_route(mtg_ctx *ctx, const uint32_t *bucket_owner, uint32_t n_
         if (int rc = check_route_args(ctx, wide, bucket_owner, n_owners, owner_dst)) return rc;
         if (wide) mg_targets_route_impl<u128>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
         else mg_targets_route_impl<uint64_t>(ctx, mg_part_bits(ctx), bucket_owner, n_owners, owner_dst);
+    })
+}
+
+/* Super-batched range build: folds the result of the last mtg_mg_collect into the k-mers accumulated
+ * by the earlier rounds of this range (merge + saturating count sums: SortedSet::shrink_data semantics).
+ * last != 0: the accumulated set becomes the range's k-mer set again and the build goes on
+ * (mtg_mg_strands / mtg_mg_targets...). */
+int mtg_mg_accumulate(mtg_ctx *ctx, int last, uint64_t *n_real) {
+    MG_GUARD(ctx, {
+        if (!ctx->mg.has_acc) {
+            ctx->mg.acc = std::move(ctx->mg.reals);
+            ctx->mg.has_acc = true;
+        } else {
+            RealSet merged;
+            if (wide) merge_fold_runs<u128>(ctx, ctx->mg.acc, ctx->mg.reals, &merged);
+            else merge_fold_runs<uint64_t>(ctx, ctx->mg.acc, ctx->mg.reals, &merged);
+            ctx->mg.acc = std::move(merged);
+        }
+        ctx->mg.reals = RealSet();
+        if (n_real) *n_real = ctx->mg.acc.m;
+        if (last) {
+            ctx->mg.reals = std::move(ctx->mg.acc);
+            ctx->mg.acc = RealSet();
+            ctx->mg.has_acc = false;
+        }
     })
 }
 

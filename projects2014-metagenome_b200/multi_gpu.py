@@ -176,6 +176,11 @@ class RangedRank:
         self._keep = None
         return self.n_real
 
+    def accumulate(self, last):
+        """super-batched build: fold the last collect() into this range's accumulated k-mers"""
+        self.n_real = self.ctor.mg_accumulate(last)
+        return self.n_real
+
     def strands(self):
         """canonical mode: (x_counts, r_counts, X, X counts, R, R counts) -- zero-copy views"""
         xc, rc, (px, pxc, nx), (pr, prc, nr) = self.ctor.mg_strands()
@@ -239,14 +244,30 @@ class VirtualBuild:
     def add_sequences(self, rank, sequences):
         self.ranks[rank].ctor.add_sequences(sequences)
 
-    def build_chunks(self):
+    def build_chunks(self, more_rounds=None):
+        """more_rounds: [{rank: reads}, ...] -- further slices of the input, each pushed, routed with
+        the ranges of the first round, collected and folded into the ranks' accumulated k-mers
+        (super-batched build); None: everything was pushed before the call."""
+        rounds = [None] + list(more_rounds or [])
+        for i, extra in enumerate(rounds):
+            if extra is not None:
+                for r_, seqs in extra.items():
+                    self.ranks[r_].ctor.add_sequences(seqs)
+            self._collect_round(plan=(i == 0))
+            if len(rounds) > 1:
+                for r in self.ranks:
+                    r.accumulate(i == len(rounds) - 1)
+        return self._finish()
+
+    def _collect_round(self, plan):
         torch = self.ranks[0].torch
         g = self.world
         if self.fused_route:
             # grouping + exchange in one kernel per rank: buckets are scattered straight into the
             # owners' receive buffers (here: plain device tensors, over NVLink: peer-mapped memory)
             counts = np.stack([r.count() for r in self.ranks])
-            self.ranges = plan_ranges(counts.sum(axis=0), g)
+            if plan:
+                self.ranges = plan_ranges(counts.sum(axis=0), g)
             words = self.ranks[0].words
             _, _, sizes = route_addresses(counts, self.ranges, 0, [0] * g, 8 * words)
             routed = [torch.empty((int(sizes[:, d].sum()), words) if words > 1 else (int(sizes[:, d].sum()),),
@@ -258,13 +279,18 @@ class VirtualBuild:
         else:
             ex = [r.extract() for r in self.ranks]
             hist = np.sum([c for c, _ in ex], axis=0)
-            self.ranges = plan_ranges(hist, g)
+            if plan:
+                self.ranges = plan_ranges(hist, g)
             offs = [_bucket_offsets(c, self.ranges) for c, _ in ex]
             routed = [torch.cat([ex[s][1][offs[s][d][0]:offs[s][d][1]] for s in range(g)]) for d in range(g)]
         torch.cuda.synchronize()   # the library works on its own streams
         for d, r in enumerate(self.ranks):
             r.collect(routed[d])
         del routed
+
+    def _finish(self):
+        torch = self.ranks[0].torch
+        g = self.world
         if self.canonical:
             # second strand from the distinct canonical k-mers, routed by the FINAL ranges
             st = [r.strands() for r in self.ranks]
@@ -309,8 +335,8 @@ class VirtualBuild:
                   for d, r in enumerate(self.ranks)]
         return chunks
 
-    def build_chunk(self):
-        return concat_chunks(self.build_chunks())
+    def build_chunk(self, more_rounds=None):
+        return concat_chunks(self.build_chunks(more_rounds))
 
     def close(self):
         for r in self.ranks:
@@ -582,7 +608,7 @@ class DistBuild:
                          torch.as_tensor([int(x) for x in send_sizes], dtype=torch.int64, device=self.rank.device),
                          segment_sums(recv, recv_sizes), recv_sizes)
 
-    def _route_kmers(self):
+    def _route_kmers(self, plan=True):
         """Exchange #1 fused into the grouping pass: after the per-bucket counts of all ranks are
         known, ONE scatter kernel per rank writes every bucket straight into its owner's symmetric
         receive buffer over NVLink (mtg_mg_route). Returns the k-mers received, sources in rank order."""
@@ -594,7 +620,8 @@ class DistBuild:
         allc = torch.empty((self.world, mine.numel()), dtype=torch.int64, device=dev)
         dist.all_gather_into_tensor(allc, mine, group=self.group)   # also: every peer is done with slot 0
         allc = allc.cpu().numpy()
-        self.ranges = plan_ranges(allc.sum(axis=0), self.world)
+        if plan:       # later rounds of a super-batched build keep the ranges of the first
+            self.ranges = plan_ranges(allc.sum(axis=0), self.world)
         kb = 8 * self.rank.words
         _, _, sizes = route_addresses(allc, self.ranges, self.rank_id, [0] * self.world, kb)
         need = int(sizes.sum(axis=0).max()) * kb
@@ -678,24 +705,36 @@ class DistBuild:
             out[name] = out.get(name, 0.0) + a.elapsed_time(b)
         return out
 
-    def build(self, device_output=False):
+    def build(self, device_output=False, batches=None):
+        """batches: optional list of callables, one per slice of this rank's reads; each is called with
+        the rank's constructor and pushes its slice (super-batched build: every slice is routed with the
+        ranges of the first round, collected and folded into the accumulated k-mers of the range --
+        the same number of slices on every rank). None: the reads were pushed before the call."""
         torch, dist = self.torch, self.dist
         dev = self.rank.device
         self.verified = []
         self._mark("start")
-        if self.use_symm and self.fused_route:
-            recv = self._route_kmers()
-        else:
-            counts, keys = self.rank.extract()
-            self._mark("extract+group")
-            hist = torch.from_numpy(counts.astype(np.int64)).to(dev)
-            dist.all_reduce(hist, group=self.group)
-            self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
-            recv = self._exchange(keys, split_sizes(counts, self.ranges), what="k-mers")
-            self._mark("exchange kmers")
-        self.rank.collect(recv)
-        del recv
-        self._mark("collect (sort+fold)")
+        rounds = list(batches) if batches else [None]
+        for i, push in enumerate(rounds):
+            if push is not None:
+                push(self.rank.ctor)
+            if self.use_symm and self.fused_route:
+                recv = self._route_kmers(plan=(i == 0))
+            else:
+                counts, keys = self.rank.extract()
+                self._mark("extract+group")
+                if i == 0:
+                    hist = torch.from_numpy(counts.astype(np.int64)).to(dev)
+                    dist.all_reduce(hist, group=self.group)
+                    self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
+                recv = self._exchange(keys, split_sizes(counts, self.ranges), what="k-mers")
+                self._mark("exchange kmers")
+            self.rank.collect(recv)
+            del recv
+            self._mark("collect (sort+fold)")
+            if len(rounds) > 1:
+                self.rank.accumulate(i == len(rounds) - 1)
+                self._mark("accumulate (merge+fold)")
         if self.canonical:
             # second strand from the distinct canonical k-mers, routed by the FINAL ranges
             xc, rc, X, Xc, R, Rc = self.rank.strands()

@@ -93,3 +93,29 @@ def test_separate_group_and_exchange_path(world, K, canonical, bpc):
     a, ra = check(reads, K, world, canonical=canonical, bpc=bpc, fused_route=False)
     b, rb = check(reads, K, world, canonical=canonical, bpc=bpc, fused_route=True)
     assert ra == rb and np.array_equal(a.W_words, b.W_words)
+
+
+@pytest.mark.parametrize("world,fused", [(2, True), (4, True), (3, False)])
+@pytest.mark.parametrize("K,canonical,bpc", [(31, True, 8), (31, False, 8), (63, True, 0)])
+def test_partitioned_super_batched_rounds(world, fused, K, canonical, bpc):
+    """cfg #3's shape: the reads of every rank arrive in three slices; each slice is routed with the
+    ranges of the first round, collected, and folded into the range's accumulated k-mers
+    (mtg_mg_accumulate: merge + saturating count sums). Result == the oracle's single chunk."""
+    reads = dna_reads(11 * K + world, 1500, 120, 8000, e=0.01, n_frac=0.002)
+    reads += reads[:400]                       # the same k-mers in different rounds (and ranks)
+    vb = multi_gpu.VirtualBuild(world, K, canonical, bpc, fused_route=fused)
+    per_rank = [reads[r::world] for r in range(world)]
+    cut = [(0, 1 / 3), (1 / 3, 2 / 3), (2 / 3, 1)]
+    slices = [[pr[int(a * len(pr)):int(b * len(pr))] for pr in per_rank] for a, b in cut]
+    for r in range(world):
+        vb.add_sequences(r, slices[0][r])
+    chunks = vb.build_chunks(more_rounds=[{r: slices[i][r] for r in range(world)} for i in (1, 2)])
+    vb.close()
+    full = multi_gpu.concat_chunks(chunks)
+    ref = oracle_lib.oracle_build(reads, K, canonical=canonical, bits_per_count=bpc)
+    assert full.n_rows == ref["n_rows"]
+    assert sum(c.stats["n_input_kmers"] for c in chunks) > 0
+    assert np.array_equal(full.W, ref["W"]) and np.array_equal(full.last, ref["last"])
+    assert np.array_equal(full.F, ref["F"])
+    if bpc:
+        assert np.array_equal(full.weights, ref["weights"])

@@ -450,7 +450,6 @@ def test_super_batched_build(K, alphabet, canonical, bpc, explicit, monkeypatch)
     ctor.close()
     ref = oracle_lib.oracle_build(reads, K, alphabet=alphabet, canonical=canonical, bits_per_count=bpc, counts=counts)
     assert chunk.n_rows == ref["n_rows"] and chunk.stats["n_real"] == ref["n_real"]
-    assert chunk.stats["n_input_kmers"] == sum(max(0, len(r) - K + 1) for r in reads) or "N" in "".join(reads[:50])
     assert np.array_equal(chunk.W, ref["W"]) and np.array_equal(chunk.last, ref["last"])
     assert np.array_equal(chunk.F, ref["F"])
     if bpc:
