@@ -30,9 +30,18 @@ WORKLOADS = {
     # name: (n_reads, read_len, genome, seed, e, K, canonical, bits_per_count)
     "cfg2": dict(name="synthetic 10Mx150bp DNA reads, k=31, canonical", n_reads=10_000_000,
                  read_len=150, G=100_000_000, seed=1, e=0.005, K=31, canonical=True, bpc=0),
+    # the other BASELINE configs (named sizes; `--workload cfgN`): secondary lines under profiles/
     "cfg3": dict(name="synthetic 100Mx150bp DNA reads, k=31, --count-kmers", n_reads=100_000_000,
-                 read_len=150, G=1_000_000_000, seed=2, e=0.005, K=31, canonical=False, bpc=8),
+                 read_len=150, G=1_000_000_000, seed=2, e=0.005, K=31, canonical=False, bpc=8,
+                 scaling="strong"),
+    "cfg4": dict(name="synthetic 50Mx150bp DNA reads, k=63 (128-bit k-mers)", n_reads=50_000_000,
+                 read_len=150, G=500_000_000, seed=3, e=0.005, K=63, canonical=False, bpc=0,
+                 scaling="strong"),
+    "cfg5": dict(name="synthetic 5Mx300aa protein sequences, k=12 (Protein alphabet)", n_reads=5_000_000,
+                 read_len=300, G=0, seed=4, e=0.0, K=12, canonical=False, bpc=0, alphabet="Protein",
+                 scaling="strong"),
 }
+SLICE_READS = 12_500_000     # reads are generated and pushed in slices of at most this many
 
 
 def parse_args():
@@ -136,7 +145,8 @@ def cpu_reference_run(wl, n_reads, threads, repeats=1, mem_gb=16.0):
     import mtg_b200
     from mtg_b200 import synth
     import oracle_lib
-    drv = oracle_lib.ref_driver("DNA")
+    alphabet = wl.get("alphabet", "DNA")
+    drv = oracle_lib.ref_driver(alphabet)
     G = max(wl["read_len"] * 2, int(wl["G"] * n_reads / wl["n_reads"]))   # same coverage
     n_kmers = n_reads * (wl["read_len"] - wl["K"] + 1)
     with tempfile.TemporaryDirectory() as td:
@@ -156,12 +166,15 @@ def cpu_reference_run(wl, n_reads, threads, repeats=1, mem_gb=16.0):
                                       "(same coverage), oracle/mtg_oracle.cpp" % (n_reads, wl["read_len"]))
         shm = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else td
         path = os.path.join(shm, "mtg_bench_reads_%d.txt" % os.getpid())
-        genome = synth.genome_np(wl["seed"], G)
+        genome = synth.genome_np(wl["seed"], G) if alphabet == "DNA" else None
         with open(path, "wb") as f:
             for r0 in range(0, n_reads, 200_000):
                 r1 = min(n_reads, r0 + 200_000)
-                p = synth.dna_reads_packed_np(wl["seed"], n_reads, wl["read_len"], G, wl["e"], r0, r1,
-                                              genome=genome)
+                if alphabet == "DNA":
+                    p = synth.dna_reads_packed_np(wl["seed"], n_reads, wl["read_len"], G, wl["e"], r0, r1,
+                                                  genome=genome)
+                else:
+                    p = synth.protein_reads_packed_np(wl["seed"], n_reads, wl["read_len"], r0, r1)
                 p[:, -1] = ord("\n")
                 f.write(p.tobytes())
         cmd = [drv, "-k", str(wl["K"]), "-p", str(threads), "--mem-gb", str(mem_gb), "-o",
@@ -278,15 +291,30 @@ def run_ours(args, wl):
             dist.destroy_process_group()
 
     # ---- synthetic reads, generated straight into HBM in the packed layout ----
-    packed = synth.dna_reads_packed_torch(wl["seed"], n_reads, L, wl["G"], wl["e"], device=dev)
-    n_bytes = packed.numel()
+    alphabet = wl.get("alphabet", "DNA")
+    slices = []
+    genome = synth.genome_torch(wl["seed"], wl["G"], dev) if alphabet == "DNA" else None
+    for r0 in range(0, n_reads, SLICE_READS):
+        r1 = min(n_reads, r0 + SLICE_READS)
+        if alphabet == "DNA":
+            slices.append(synth.dna_reads_packed_torch(wl["seed"], n_reads, L, wl["G"], wl["e"], device=dev,
+                                                       r0=r0, r1=r1, genome=genome))
+        else:
+            slices.append(synth.protein_reads_packed_torch(wl["seed"], n_reads, L, device=dev, r0=r0, r1=r1))
+    del genome
+    packed = slices[0]
+    n_bytes = sum(p.numel() for p in slices)
     n_windows = n_reads * (L - K + 1)
     stream = torch.cuda.current_stream()
-    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, wl["canonical"], wl["bpc"], device=local)
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, wl["canonical"], wl["bpc"], device=local,
+                                                    alphabet=alphabet)
     ctor.set_stream(stream.cuda_stream)
 
     def step_device():
-        ctor.add_packed_device(packed.data_ptr(), n_bytes, n_windows)
+        # inputs beyond one sort buffer are folded into sorted runs slice by slice inside the library
+        # (super-batching) and merged by the build
+        for p in slices:
+            ctor.add_packed_device(p.data_ptr(), p.numel(), p.shape[0] * (L - K + 1))
         return ctor.build_chunk_device()
 
     for _ in range(args.warmup):
@@ -318,14 +346,15 @@ def run_ours(args, wl):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     peak_src = "MEASURED_PEAKS.json hbm_gbs (measured copy)" if "hbm_gbs" in peaks else "fallback 6650 GB/s"
-    n_launch = sum(s["n_onesweep"] for s in stats)
+    n_launch = sum(s["n_onesweep"] for s in stats)      # 0 when the build was super-batched
     ms_kernel = sum(s["ms_onesweep_sum"] for s in stats) / max(n_launch, 1)
     bytes_launch = st["onesweep_keys"] * st["onesweep_bytes_per_key"]
     achieved = bytes_launch / (ms_kernel * 1e-3) / 1e9 if ms_kernel else 0.0
-    w = 8 if K * 2 <= 64 else 16
+    Lb = 2 if alphabet == "DNA" else 5
+    w = 8 if K * Lb <= 64 else 16
     c = 0
-    P = (K * 2 + 7) // 8
-    alg = algorithmic_bytes(st, n_bytes, w, c, P, wl["canonical"], 4, wl["bpc"])
+    P = (K * Lb + 7) // 8
+    alg = algorithmic_bytes(st, n_bytes, w, c, P, wl["canonical"], 4 if alphabet == "DNA" else 6, wl["bpc"])
     device_ms = sum(s["ms_total"] for s in stats) / len(stats)
     # DRAM traffic of that kernel from the committed ncu --set full capture of this same workload
     traffic, traffic_src = None, None
@@ -356,13 +385,17 @@ def run_ours(args, wl):
 
     # ---- end to end through the host C ABI: pinned host reads in, pinned chunk out ----
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and len(slices) > 1:
+        e2e = {"value": None, "unit": UNIT, "skipped": "the end-to-end leg is measured on the headline workload "
+               "(cfg2); this workload's reads (%.1f GB) are kept device-resident" % (n_bytes / 1e9)}
+    elif not args.no_e2e:
         host = torch.empty((n_reads, L), dtype=torch.uint8, pin_memory=True)
         host.copy_(packed[:, :L])
         torch.cuda.synchronize()
         bases = host.numpy().reshape(-1)
         offsets = np.arange(n_reads + 1, dtype=np.uint64) * np.uint64(L)
-        ctor2 = mtg_b200.BOSSChunkConstructor.initialize(K - 1, wl["canonical"], wl["bpc"], device=local)
+        ctor2 = mtg_b200.BOSSChunkConstructor.initialize(K - 1, wl["canonical"], wl["bpc"], device=local,
+                                                         alphabet=alphabet)
 
         host_ms = {"push": 0.0, "build": 0.0}
 
@@ -397,7 +430,10 @@ def run_ours(args, wl):
 
     # ---- CPU baseline: the reference's own implementation on this box's host cores ----
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and (args.workload or "cfg2") != "cfg2" and not args.cpu_sample_reads:
+        cpu = {"value": None, "unit": UNIT, "kind": "reference",
+               "sample": "not run by default for this workload (pass --cpu-sample-reads N)"}
+    elif not args.no_cpu_baseline:
         threads = os.cpu_count() or 1
         n_cpu = min(n_reads, args.cpu_sample_reads) if args.cpu_sample_reads else n_reads
         v, info = cpu_reference_run(wl, n_cpu, threads, mem_gb=args.cpu_mem_gb)
@@ -412,8 +448,8 @@ def run_ours(args, wl):
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": 1, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": wl["name"], "n_reads": n_reads, "read_len": L, "k": K,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64" if w == 8 else "u128", "data": "synthetic",
+        "config": {"workload": wl["name"], "alphabet": alphabet, "n_reads": n_reads, "read_len": L, "k": K,
                    "mode": "canonical" if wl["canonical"] else "basic", "count_width": wl["bpc"],
                    "genome_bp": wl["G"], "subst_rate": wl["e"], "seed": wl["seed"],
                    "input_kmers": N, "real_kmers": st["n_real"], "rows": st["n_rows"],

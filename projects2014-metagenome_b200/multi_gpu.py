@@ -429,6 +429,7 @@ class DistBuild:
         # MTG_ROUTE=0: grouping pass, then a separate exchange (the first design)
         self.fused_route = os.environ.get("MTG_ROUTE", "1") != "0"
         self._slots = {}
+        self._legacy_slots = os.environ.get("MTG_SYMM_LEGACY", "0") == "1"
         self._streams = [torch.cuda.Stream(device=self.rank.device) for _ in range(self.world)] if self.use_symm else []
         if self.use_symm:
             try:
@@ -489,6 +490,17 @@ class DistBuild:
         decision to (re)allocate is taken from numbers all ranks share, so the rendezvous is collective."""
         import torch.distributed._symmetric_memory as symm
         name = self.group.group_name if self.group is not None else self.dist.group.WORLD.group_name
+        if self._legacy_slots:
+            # round-1 behaviour, kept ONLY to reproduce its 8-GPU parity miss under the exchange verifier
+            # (MTG_SYMM_LEGACY=1): every DistBuild allocates, rendezvouses and frees its own buffers
+            cur = self._slots.get(slot)
+            if cur is None or cur[0].numel() < need_bytes:
+                cap = (int(need_bytes * 1.25) + (1 << 20)) & ~0xFFF
+                self._slots.pop(slot, None)
+                buf = symm.empty(cap, dtype=self.torch.uint8, device=self.rank.device)
+                cur = (buf, symm.rendezvous(buf, name))
+                self._slots[slot] = cur
+            return cur
         key = (name, str(self.rank.device), slot)
         cur = _SYMM_SLOTS.get(key)
         if cur is None or cur[0].numel() < need_bytes:
@@ -836,21 +848,43 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
 
     parity_res = parity(rank, world, dev.index) if parity is not None else None
     K, L = wl["K"], wl["read_len"]
-    n_local = wl["n_reads"]
-    n_total = n_local * world
-    G = wl["G"] * world
-    # rows [rank*n_local, (rank+1)*n_local) of the world-sized read set
-    packed = synth.dna_reads_packed_torch(wl["seed"], n_total, L, G, wl["e"], device=dev,
-                                          r0=rank * n_local, r1=(rank + 1) * n_local)
-    n_bytes = packed.numel()
+    alphabet = wl.get("alphabet", "DNA")
+    strong = wl.get("scaling") == "strong"
+    if strong:      # the named input is split across the ranks (BASELINE cfg #3 / #4 / #5)
+        n_total, G = wl["n_reads"], wl["G"]
+        n_local = n_total // world
+    else:           # cfg #2 per GPU, the genome grows with the number of ranks (same coverage)
+        n_local = wl["n_reads"]
+        n_total = n_local * world
+        G = wl["G"] * world
+    words = key_words(K, alphabet)
+    # rounds of a super-batched build: one round's k-mers are held 4 x (a, the symmetric receive
+    # buffer, the sort's ping-pong), so a round takes at most ~1.6 G 64-bit (0.8 G 128-bit) k-mers
+    per_round = int(os.environ.get("MTG_MG_ROUND_KMERS", str(1_600_000_000 // words)))
+    n_rounds = max(1, -(-(n_local * (L - K + 1)) // per_round))
+    rows = -(-n_local // n_rounds)
+    genome = synth.genome_torch(wl["seed"], G, dev) if alphabet == "DNA" else None
+    slices = []
+    for j in range(n_rounds):
+        a0 = rank * n_local + j * rows
+        a1 = min((rank + 1) * n_local, a0 + rows)
+        if alphabet == "DNA":
+            slices.append(synth.dna_reads_packed_torch(wl["seed"], n_total, L, G, wl["e"], device=dev,
+                                                       r0=a0, r1=a1, genome=genome))
+        else:
+            slices.append(synth.protein_reads_packed_torch(wl["seed"], n_total, L, device=dev, r0=a0, r1=a1))
+    del genome
+    packed = slices[0]
+    n_bytes = sum(p.numel() for p in slices)
     n_windows = n_local * (L - K + 1)
-    db = DistBuild(K, wl["canonical"], wl["bpc"], device=dev.index)
+    db = DistBuild(K, wl["canonical"], wl["bpc"], alphabet=alphabet, device=dev.index)
     stream = torch.cuda.current_stream()
-    db.rank.ctor.set_stream(stream.cuda_stream)
+
+    def pusher(p):
+        return lambda ctor: ctor.add_packed_device(p.data_ptr(), p.numel(), p.shape[0] * (L - K + 1))
 
     def step():
-        db.rank.ctor.add_packed_device(packed.data_ptr(), n_bytes, n_windows)
-        return db.build(device_output=True)
+        return db.build(device_output=True, batches=[pusher(p) for p in slices])
 
     for _ in range(args.warmup):
         st = step()
@@ -885,7 +919,9 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
 
     # end to end: host reads in (pinned), per-rank chunk out to host memory
     e2e = None
-    if not args.no_e2e:
+    if not args.no_e2e and n_rounds > 1:
+        e2e = {"value": None, "unit": UNIT, "skipped": "end to end is measured on the single-round workloads"}
+    elif not args.no_e2e:
         host = torch.empty((n_local, L), dtype=torch.uint8, pin_memory=True)
         host.copy_(packed[:, :L])
         torch.cuda.synchronize()
@@ -931,10 +967,12 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
     line = {
         "metric": METRIC, "value": N * args.steps / (ms_total * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "u64" if K * 2 <= 64 else "u128", "data": "synthetic",
-        "config": {"workload": wl["name"] + " per GPU (weak scaling: %d reads, genome %d bp in total)"
-                               % (n_total, G),
+        "higher_is_better": True, "scaling": "strong" if strong else "weak", "vs_baseline": None,
+        "dtype": "u64" if words == 1 else "u128", "data": "synthetic",
+        "config": {"workload": (wl["name"] + " split across the GPUs (strong scaling)") if strong else
+                               (wl["name"] + " per GPU (weak scaling: %d reads, genome %d bp in total)"
+                                % (n_total, G)),
+                   "alphabet": alphabet, "rounds_per_build": n_rounds,
                    "n_reads_per_gpu": n_local, "read_len": L, "k": K,
                    "mode": "canonical" if wl["canonical"] else "basic", "count_width": wl["bpc"],
                    "input_kmers": N, "real_kmers": int(counters[1]), "rows": int(counters[2]) + 1,
@@ -945,7 +983,7 @@ def bench(args, wl, rank, world, dev, METRIC, UNIT, ClockSampler, algorithmic_by
                                       "stores of their scatter kernels (mtg_mg_route / mtg_mg_targets_route), "
                                       "strands by peer copies" if db_use_symm else "NCCL all_to_all_single"),
                    "l2_policy": "inputs larger than L2 (%.2f GB of keys per GPU and step)"
-                                % (n_windows * 8 * (1 if K * 2 <= 64 else 2) / 1e9)},
+                                % (n_windows * 8 * words / 1e9)},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(counters[4]),
         "roofline": {"bound": "hbm", "kernel": "whole path per GPU (SURVEY 8d byte model)",
                      "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None,

@@ -108,15 +108,22 @@ def _h_t(seed, stream, idx):
     return _mix_t(idx + _to_i64((seed * _C1) + (stream * _C2)))
 
 
-def dna_reads_packed_torch(seed, n_reads, read_len, G, e=0.005, device="cuda", chunk=1 << 20, r0=0,
-                           r1=None):
-    """Rows r0..r1 of the packed (n_reads, read_len+1) uint8 matrix, generated on `device`."""
+def genome_torch(seed, G, device="cuda"):
+    """the genome codes (uint8, 0..3) on `device`"""
     import torch
     gen = torch.empty(G, dtype=torch.uint8, device=device)
     for lo in range(0, G, 1 << 26):
         hi = min(G, lo + (1 << 26))
         j = torch.arange(lo, hi, dtype=torch.int64, device=device)
         gen[lo:hi] = _lsr(_h_t(seed, 0, j), 62).to(torch.uint8)
+    return gen
+
+
+def dna_reads_packed_torch(seed, n_reads, read_len, G, e=0.005, device="cuda", chunk=1 << 20, r0=0,
+                           r1=None, genome=None):
+    """Rows r0..r1 of the packed (n_reads, read_len+1) uint8 matrix, generated on `device`."""
+    import torch
+    gen = genome if genome is not None else genome_torch(seed, G, device)
     r_end = n_reads if r1 is None else r1
     r_begin = r0
     out = torch.zeros((r_end - r_begin, read_len + 1), dtype=torch.uint8, device=device)
@@ -138,13 +145,15 @@ def dna_reads_packed_torch(seed, n_reads, read_len, G, e=0.005, device="cuda", c
     return out
 
 
-def protein_reads_packed_torch(seed, n_reads, read_len, device="cuda", chunk=1 << 20):
+def protein_reads_packed_torch(seed, n_reads, read_len, device="cuda", chunk=1 << 20, r0=0, r1=None):
+    """Rows r0..r1 of the packed (n_reads, read_len+1) matrix of i.i.d. amino acids."""
     import torch
-    out = torch.zeros((n_reads, read_len + 1), dtype=torch.uint8, device=device)
+    r_begin, r_end = r0, (n_reads if r1 is None else r1)
+    out = torch.zeros((r_end - r_begin, read_len + 1), dtype=torch.uint8, device=device)
     lut = torch.tensor(list(AA), dtype=torch.uint8, device=device)
-    for r0 in range(0, n_reads, chunk):
-        r1 = min(n_reads, r0 + chunk)
-        idx = torch.arange(r0 * read_len, r1 * read_len, dtype=torch.int64, device=device)
+    for a0 in range(r_begin, r_end, chunk):
+        a1 = min(r_end, a0 + chunk)
+        idx = torch.arange(a0 * read_len, a1 * read_len, dtype=torch.int64, device=device)
         a = _lsr(_h_t(seed, 4, idx), 32) % 20
-        out[r0:r1, :read_len] = lut[a].reshape(r1 - r0, read_len)
+        out[a0 - r_begin:a1 - r_begin, :read_len] = lut[a].reshape(a1 - a0, read_len)
     return out
