@@ -108,6 +108,11 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets,
 int mtg_push_packed_device(mtg_ctx *ctx, const void *d_packed, size_t n_bytes,
                            uint64_t n_windows_max);
 
+/* Page-locked host memory for the caller's read batches: mtg_push_reads copies straight out of such
+ * buffers (no staging copy) and returns when the copies are done. NULL when it cannot be allocated. */
+void *mtg_alloc_pinned(size_t bytes);
+void mtg_free_pinned(void *p);
+
 /* Host helper producing that packed layout (for callers that keep reads resident). */
 size_t mtg_packed_size(const uint64_t *offsets, size_t n_reads);
 void mtg_pack_reads(const char *bases, const uint64_t *offsets, size_t n_reads, char *dst);

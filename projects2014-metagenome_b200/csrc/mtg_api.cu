@@ -558,6 +558,19 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
     return MTG_OK;
 }
 
+void *mtg_alloc_pinned(size_t bytes) {
+    void *p = nullptr;
+    if (cudaMallocHost(&p, bytes ? bytes : 1) != cudaSuccess) {
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void mtg_free_pinned(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
 int mtg_push_packed_device(mtg_ctx *ctx, const void *d_packed, size_t n_bytes, uint64_t n_windows_max) {
     if (!ctx || !d_packed) return fail(ctx, MTG_ERR_BAD_ARG, "null argument");
     if (((uintptr_t)d_packed & 15) != 0) return fail(ctx, MTG_ERR_BAD_ARG, "packed reads must be 16-byte aligned");
@@ -824,7 +837,8 @@ void complete_reverse_complements(mtg_ctx *ctx, DevBuf &keysB, DevBuf &counts, u
                                      counting ? cb0.as<uint32_t>() : nullptr, m, al, ctx->cmax, d_ctr + 2, s,
                                      &ctx->launches);
     const uint64_t mb = read_counter(d_ctr + 2, s);
-    plan.unstable_first = true;      // the reverse complements are distinct keys
+    // (no unstable first pass here: the low digits of rc(x) come from x's leading characters, i.e. they
+    // arrive in long runs of equal digits, where the returning atomics of the unstable ranking serialise)
     sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s,
                     &ctx->launches);
     rb1.release();
@@ -930,7 +944,6 @@ void expand_sources(mtg_ctx *ctx, DevBuf &src, uint64_t d1, DevBuf &sink, uint64
         SortPlan plan;
         plan.n = 0;
         plan_add_key_bits(plan, 0, (K - 1) * L);
-        plan.unstable_first = true;
         sort_keys<KeyT>(src, srcB, nullptr, nullptr, d1, plan, s, &ctx->launches);
     }
     srcB.release();
@@ -1821,7 +1834,6 @@ void mg_dummies_impl(mtg_ctx *ctx, const void *d_in, uint64_t n_in, const uint64
             SortPlan plan;
             plan.n = 0;
             plan_add_key_bits(plan, 0, (K - 1) * L);
-            plan.unstable_first = true;
             sort_keys<KeyT>(t0, t1, nullptr, nullptr, n_in, plan, s, &ctx->launches, nullptr, d_in);
         }
         DevBuf status(sizeof(unsigned long long) * unique_status_words(n_in), s), tctr(sizeof(unsigned int), s);
@@ -1885,7 +1897,6 @@ void mg_strands_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *x_counts, uint64_t *r_
         SortPlan plan;
         plan.n = 0;
         plan_add_key_bits(plan, 0, KL);
-        plan.unstable_first = true;
         sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s, &ctx->launches);
     } else {
         if (mb) {
@@ -1895,7 +1906,6 @@ void mg_strands_impl(mtg_ctx *ctx, uint32_t pb, uint64_t *x_counts, uint64_t *r_
             SortPlan plan;
             plan.n = 0;
             plan_add_key_bits(plan, 0, KL);
-            plan.unstable_first = true;
             sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, mb, plan, s,
                             &ctx->launches);
             std::vector<uint64_t> rbounds(nb + 1, 0);
@@ -1948,7 +1958,6 @@ void mg_merge_impl(mtg_ctx *ctx, const void *d_x, const uint32_t *d_xc, uint64_t
         SortPlan plan;
         plan.n = 0;
         plan_add_key_bits(plan, 0, al.K * al.L);
-        plan.unstable_first = true;
         sort_keys<KeyT>(rb0, rb1, counting ? &cb0 : nullptr, counting ? &cb1 : nullptr, nr, plan, s, &ctx->launches);
     }
     rb1.release(); cb1.release();

@@ -521,13 +521,17 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
                                                                       dp, offs, status, ctr, epoch, route_owner);
 }
 
-// MTG_SORT_VARIANT=3 selects the round-1 pass (v3: peer masks through shared memory) for A/B timing;
-// anything else: v5. MTG_SORT_UNSTABLE_FIRST=0 keeps the first pass of a sort stable as well.
+// Stable passes: v3 (peer masks through shared memory). MTG_SORT_VARIANT=5 selects v5's stable ranking
+// (atomic slot + collision repair) instead -- measured on B200 (profiles/r02_sort_variants.jsonl): 4 %
+// faster than v3 on random 64-bit keys, 11 % on 128-bit keys, but slower on clustered digits (the
+// reverse-complement sort, the passes after the fold): 85.4 vs 81.3 ms on the whole cfg #2 build, so it
+// is not the default. The UNSTABLE v5 ranking (first pass of a sort that allows it) is 17 % faster
+// than a stable pass on random digits and is used; MTG_SORT_UNSTABLE_FIRST=0 switches it off.
 static int sort_variant() {
     static int v = -1;
     if (v < 0) {
         const char *e = getenv("MTG_SORT_VARIANT");
-        v = e ? atoi(e) : 5;
+        v = e ? atoi(e) : 3;
     }
     return v;
 }
@@ -598,12 +602,12 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         // the first pass of a sort has no earlier order to preserve: unstable ranking (one shared atomic
         // per key) when the caller allows it (equal keys may then leave the sort in any order)
         const bool unstable = p == 0 && plan.unstable_first && unstable_first_allowed();
-        if (variant == 3)
-            launch_v3<KeyT, HAS_VAL, 256, 16 / S, 3, 0>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
-        else if (unstable)
+        if (unstable)
             launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, true>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
-        else
+        else if (variant == 5)
             launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, false>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
+        else
+            launch_v3<KeyT, HAS_VAL, 256, 16 / S, 3, 0>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
         if (ws.events) cudaEventRecord(ws.events[2 * p + 1], stream);
         *launches += 1;
         cur ^= 1;
@@ -656,15 +660,12 @@ void route_scatter(const KeyT *keys, uint64_t n, DigitPass dp, const unsigned ch
     const size_t tiles = div_up(n, (size_t)4096 / S);
     MTG_CUDA(cudaMemsetAsync(tile_counter, 0, sizeof(unsigned int), stream));
     MTG_CUDA(cudaMemsetAsync(status, 0, sizeof(unsigned long long) * tiles * RADIX, stream));
-    if (sort_variant() == 3)
-        launch_v3<KeyT, false, 256, 16 / S, 3, 0, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
-                                                        tile_counter, 1u, stream, owner);
-    else if (stable || !unstable_first_allowed())
-        launch_v5<KeyT, false, 256, 16 / S, 4, false, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
-                                                            tile_counter, 1u, stream, owner);
-    else
+    if (!stable && unstable_first_allowed())
         launch_v5<KeyT, false, 256, 16 / S, 4, true, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
                                                            tile_counter, 1u, stream, owner);
+    else
+        launch_v3<KeyT, false, 256, 16 / S, 3, 0, true>(keys, nullptr, nullptr, nullptr, n, dp, route, status,
+                                                        tile_counter, 1u, stream, owner);
     MTG_CUDA(cudaGetLastError());
     *launches += 1;
 }

@@ -34,16 +34,37 @@ uint64_t Chunk::get_bits(const std::vector<uint64_t> &words, uint64_t i, unsigne
     return width == 64 ? v : v & ((1ull << width) - 1);
 }
 
-// appends src entries [src_first, src_first + src_n) to dst, which holds dst_n entries
+// appends src entries [src_first, src_first + src_n) to dst, which holds dst_n entries (its padding
+// bits are zero). Word-wise: 64 source bits per step through a funnel shift (a plain copy when both
+// bit offsets are word aligned), not one entry per step -- chunks hold billions of rows.
 void Chunk::append_bits(std::vector<uint64_t> *dst, uint64_t dst_n, unsigned width,
                         const std::vector<uint64_t> &src, uint64_t src_first, uint64_t src_n) {
-    if (!width) return;
-    dst->resize(((dst_n + src_n) * width + 63) / 64, 0);
-    for (uint64_t i = 0; i < src_n; ++i) {
-        uint64_t v = get_bits(src, src_first + i, width);
-        uint64_t bit = (dst_n + i) * width, w = bit >> 6, off = bit & 63;
-        (*dst)[w] |= v << off;
-        if (off + width > 64) (*dst)[w + 1] |= v >> (64 - off);
+    if (!width || !src_n) return;
+    const uint64_t nbits = src_n * width, sb = src_first * width, db = dst_n * width;
+    dst->resize((db + nbits + 63) / 64, 0);
+    auto get64 = [&](uint64_t bit) -> uint64_t {   // 64 bits of src from `bit` on (zero padded)
+        const uint64_t w = bit >> 6, o = bit & 63;
+        uint64_t v = w < src.size() ? src[w] >> o : 0;
+        if (o && w + 1 < src.size()) v |= src[w + 1] << (64 - o);
+        return v;
+    };
+    auto low = [](uint64_t n) -> uint64_t { return n >= 64 ? ~0ull : (1ull << n) - 1; };
+    uint64_t done = 0;
+    if (db & 63) {   // fill up the partial last word of dst
+        const uint64_t o = db & 63, take = std::min<uint64_t>(64 - o, nbits);
+        (*dst)[db >> 6] |= (get64(sb) & low(take)) << o;
+        done = take;
+    }
+    uint64_t w = (db + done) >> 6;
+    if (((sb + done) & 63) == 0 && done < nbits) {   // aligned: straight copy of the full words
+        const uint64_t full = (nbits - done) / 64;
+        if (full) memcpy(dst->data() + w, src.data() + ((sb + done) >> 6), 8 * full);
+        w += full;
+        done += full * 64;
+    }
+    for (; done < nbits; done += 64) {
+        const uint64_t take = std::min<uint64_t>(64, nbits - done);
+        (*dst)[w++] = get64(sb + done) & low(take);
     }
 }
 
@@ -211,6 +232,12 @@ class BOSSChunkConstructor : public IBOSSChunkConstructor {
             counts.push_back(s.second);
         }
         push(bases, offsets, counts.data());
+    }
+
+    void add_packed(const char *bases, const uint64_t *offsets, size_t n_reads) override {
+        if (!n_reads) return;
+        if (int rc = mtg_push_reads(ctx_, bases, offsets, nullptr, n_reads))
+            throw std::runtime_error(std::string(mtg_last_error(ctx_)) + " (code " + std::to_string(rc) + ")");
     }
 
     Chunk build_chunk() override {

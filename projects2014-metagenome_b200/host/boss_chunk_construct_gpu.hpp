@@ -104,6 +104,9 @@ class IBOSSChunkConstructor {
     virtual void add_sequences(std::vector<std::pair<std::string, uint64_t>> &&sequences) = 0;
     virtual Chunk build_chunk() = 0;
     virtual uint64_t get_k() const = 0;
+    // the C ABI's native form (what host/read_feeder.hpp produces): read i = bases[offsets[i] .. offsets[i+1]).
+    // Thread-safe; the buffers are free again when the call returns.
+    virtual void add_packed(const char *bases, const uint64_t *offsets, size_t n_reads) = 0;
 };
 
 // BOSSConstructor (boss_construct.hpp:12-53). The reference's build_graph(BOSS*) hands the
@@ -129,6 +132,9 @@ class BOSSConstructor {
     }
     void add_sequences(std::vector<std::pair<std::string, uint64_t>> &&sequences) {
         constructor_->add_sequences(std::move(sequences));
+    }
+    void add_packed(const char *bases, const uint64_t *offsets, size_t n_reads) {
+        constructor_->add_packed(bases, offsets, n_reads);
     }
     Chunk build_graph() { return constructor_->build_chunk(); }
     uint64_t get_k() const { return constructor_->get_k(); }

@@ -4,8 +4,6 @@
 // (boss_chunk.cpp:372-386); `mtg_build concatenate` joins chunk files (build_boss_from_chunks,
 // boss_chunk.cpp:286-328). The wavelet-tree / rank-select construction that turns a chunk into
 // a .dbg (BOSS::initialize, boss.cpp:99-122) stays with the reference host code.
-#include <zlib.h>
-
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -14,52 +12,12 @@
 #include <vector>
 
 #include "boss_chunk_construct_gpu.hpp"
+#include "read_feeder.hpp"
+#include "../../include/mtg_gpu.h"
 
 using namespace mtg::gpu;
 
 namespace {
-
-// FASTA / FASTQ (optionally gzip) reader in the spirit of read_fasta_file_critical
-// (seq_io/sequence_io.cpp:364-405): calls `cb` with every sequence.
-template <class F>
-void read_sequences(const std::string &path, F cb) {
-    gzFile f = gzopen(path.c_str(), "rb");
-    if (!f) {
-        fprintf(stderr, "ERROR: cannot open %s\n", path.c_str());
-        exit(1);
-    }
-    gzbuffer(f, 1 << 20);
-    std::string line, seq;
-    std::vector<char> buf(1 << 20);
-    int state = 0;   // 0: header expected / FASTA body, 1: FASTQ sequence, 2: FASTQ '+', 3: FASTQ quality
-    bool fastq = false, first = true;
-    auto handle = [&](const std::string &l) {
-        if (first) { fastq = !l.empty() && l[0] == '@'; first = false; }
-        if (fastq) {
-            if (state == 0) state = 1;
-            else if (state == 1) { seq = l; state = 2; }
-            else if (state == 2) state = 3;
-            else { cb(seq); seq.clear(); state = 0; }
-        } else if (!l.empty() && l[0] == '>') {
-            if (!seq.empty()) cb(seq);
-            seq.clear();
-        } else {
-            seq += l;
-        }
-    };
-    while (gzgets(f, buf.data(), (int)buf.size())) {
-        size_t n = strlen(buf.data());
-        bool eol = n && buf[n - 1] == '\n';
-        line.append(buf.data(), n - (eol ? 1 : 0));
-        if (!eol) continue;
-        if (!line.empty() && line.back() == '\r') line.pop_back();
-        handle(line);
-        line.clear();
-    }
-    if (!line.empty()) handle(line);
-    if (!fastq && !seq.empty()) cb(seq);
-    gzclose(f);
-}
 
 int usage() {
     fprintf(stderr,
@@ -67,7 +25,8 @@ int usage() {
             "                       [-p <threads>] [--mem-cap-gb <G>] [--alphabet DNA|Protein] [--device <id>]\n"
             "                       [--suffix <S>]\n"
             "                       [-v] -o <outbase> FILE1 [FILE2 ...]\n"
-            "       mtg_build concatenate -o <outbase> CHUNK1 [CHUNK2 ...]\n");
+            "       mtg_build concatenate -o <outbase> CHUNK1 [CHUNK2 ...]\n"
+            "       mtg_build parse [-p <threads>] [--checksum] FILE1 [FILE2 ...]      (feeder only: reads, bases, checksum, GB/s)\n");
     return 1;
 }
 
@@ -77,7 +36,7 @@ int main(int argc, char **argv) {
     if (argc < 2) return usage();
     const std::string cmd = argv[1];
     size_t k = 3, threads = 1;
-    bool canonical = false, count_kmers = false, verbose = false;
+    bool canonical = false, count_kmers = false, verbose = false, checksum = false;
     int count_width = 8, device = 0;   // config.hpp:103 default --count-width 8
     double mem_cap_gb = 1;
     Alphabet alphabet = Alphabet::DNA;
@@ -103,8 +62,25 @@ int main(int argc, char **argv) {
         else if (a == "--suffix") suffix = next();   // config.cpp:279: build one chunk of the graph
         else if (a == "-o" || a == "--outfile-base") out = next();
         else if (a == "-v" || a == "--verbose") verbose = true;
+        else if (a == "--checksum") checksum = true;
         else if (a[0] == '-') { fprintf(stderr, "Error: unknown option %s\n", a.c_str()); return usage(); }
         else files.push_back(a);
+    }
+    if (cmd == "parse" && !files.empty()) {
+        // the host feeder alone (no device): what it parses and how fast
+        try {
+            ReadFeeder feeder([](const char *, const uint64_t *, size_t) {}, threads, size_t(32) << 20, nullptr,
+                              nullptr, checksum);
+            FeederStats st = feeder.run(files);
+            printf("files %llu reads %llu bases %llu batches %llu checksum %016llx seconds %.4f input_GBps %.3f\n",
+                   (unsigned long long)st.n_files, (unsigned long long)st.n_reads, (unsigned long long)st.n_bases,
+                   (unsigned long long)st.n_batches, (unsigned long long)st.checksum, st.seconds,
+                   st.input_bytes / 1e9 / st.seconds);
+        } catch (const std::exception &e) {
+            fprintf(stderr, "%s\n", e.what());
+            return 1;
+        }
+        return 0;
     }
     if (out.empty() || files.empty()) return usage();
     try {
@@ -126,22 +102,17 @@ int main(int argc, char **argv) {
         // cli/build.cpp:100,122-134: BOSS node length = k - 1
         BOSSConstructor constructor(k - 1, canonical, (uint8_t)count_width, suffix, threads, mem_cap_gb * 1e9,
                                     ContainerType::VECTOR, "/tmp/", 1e9, alphabet, device);
-        std::vector<std::string> batch;
-        size_t batch_bytes = 0, n_seq = 0;
-        for (const auto &f : files) {
-            if (verbose) fprintf(stderr, "Parsing %s\n", f.c_str());
-            read_sequences(f, [&](const std::string &s) {
-                batch_bytes += s.size();
-                batch.push_back(s);
-                ++n_seq;
-                if (batch_bytes > (32u << 20)) {
-                    constructor.add_sequences(std::move(batch));
-                    batch = {};
-                    batch_bytes = 0;
-                }
-            });
-        }
-        if (!batch.empty()) constructor.add_sequences(std::move(batch));
+        // -p threads parse (ranges of plain files / one gzip file each) into pinned batches and push them
+        // while the others parse: H2D of one batch overlaps the parsing of the next (host/read_feeder.hpp)
+        ReadFeeder feeder([&](const char *bases, const uint64_t *offsets, size_t n) {
+                              constructor.add_packed(bases, offsets, n);
+                          },
+                          threads, size_t(32) << 20, mtg_alloc_pinned, mtg_free_pinned);
+        FeederStats fst = feeder.run(files);
+        if (verbose)
+            fprintf(stderr, "Parsed %llu reads, %llu bases from %llu files with %zu threads in %.3f sec (%.2f GB/s)\n",
+                    (unsigned long long)fst.n_reads, (unsigned long long)fst.n_bases,
+                    (unsigned long long)fst.n_files, threads, fst.seconds, fst.input_bytes / 1e9 / fst.seconds);
         auto t1 = std::chrono::steady_clock::now();
         Chunk chunk = constructor.build_graph();
         auto t2 = std::chrono::steady_clock::now();

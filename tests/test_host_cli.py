@@ -94,3 +94,30 @@ def test_cli_build_writes_the_reference_chunk_files(name, tmp_path):
     assert "Graph chunk with %d k-mers was built" % (len(g["W"]) - 1) in out.stdout
     for ext in ("", ".W", ".last", ".weights"):
         assert sha(str(tmp_path / "out.dbg.chunk") + ext) == g["sha256"][ext], ext
+
+
+@pytest.mark.gpu
+def test_cli_build_parallel_feeder_plain_gzip_fastq(tmp_path):
+    """`mtg_build build -p 8` over three input files of different formats (the host feeder: pinned batches
+    pushed from 8 threads) == the chunk of the same reads pushed in one go."""
+    import gzip
+    case, g = CASES["cfg2_k31_canonical"], load_golden("cfg2_k31_canonical")
+    reads, _ = case_reads(case)
+    reads = [r for r in reads if r]
+    third = len(reads) // 3
+    with open(tmp_path / "a.fa", "w") as f:
+        for r in reads[:third]:
+            f.write(">r\n%s\n" % r)
+    with gzip.open(tmp_path / "b.fa.gz", "wt") as f:
+        for r in reads[third:2 * third]:
+            f.write(">r\n%s\n" % r)
+    with open(tmp_path / "c.fq", "w") as f:
+        for r in reads[2 * third:]:
+            f.write("@r\n%s\n+\n%s\n" % (r, "@" * len(r)))
+    out = subprocess.run([CLI, "build", "-v", "-p", "8", "-k", str(case["K"]), "--mode", "canonical", "-o",
+                          str(tmp_path / "out"), str(tmp_path / "a.fa"), str(tmp_path / "b.fa.gz"),
+                          str(tmp_path / "c.fq")], capture_output=True, text=True)
+    assert out.returncode == 0, out.stderr
+    assert "Parsed %d reads" % len(reads) in out.stderr
+    for ext in ("", ".W", ".last", ".weights"):
+        assert sha(str(tmp_path / "out.dbg.chunk") + ext) == g["sha256"][ext], ext
