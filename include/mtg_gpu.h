@@ -36,6 +36,10 @@ extern "C" {
 #define MTG_ALPHABET_DNA 0      /* -D_DNA_GRAPH: "ACGT" / "$ACGT" (kmer/alphabets.hpp:65-77,128-141) */
 #define MTG_ALPHABET_PROTEIN 1  /* -D_PROTEIN_GRAPH (kmer/alphabets.hpp:27-39,90-102) */
 
+/* mtg_params.reserved: keep every pushed read until the build instead of folding the input into sorted
+ * runs batch by batch (the range-partitioned phases mtg_mg_* consume the raw reads themselves) */
+#define MTG_FLAG_NO_BATCHING 1u
+
 #define MTG_MAX_SIGMA 32
 #define MTG_MAX_K 128
 
@@ -53,7 +57,7 @@ typedef struct mtg_params {
                                * chunk is built straight from them (KmerExtractorBOSS,
                                * kmer/kmer_extractor.cpp:317-381; boss_chunk_construct.cpp:961-1013) */
     int32_t device;           /* CUDA device ordinal */
-    uint32_t reserved;
+    uint32_t reserved;        /* flags: MTG_FLAG_NO_BATCHING */
     double memory_preallocated; /* bytes; hint for the initial read-staging capacity */
 } mtg_params;
 

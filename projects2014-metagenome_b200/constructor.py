@@ -149,7 +149,7 @@ class BOSSChunkConstructor:
     `k` is the BOSS node length (CLI -k minus 1)."""
 
     def __init__(self, k, both_strands=False, bits_per_count=0, filter_suffix="",
-                 num_threads=1, memory_preallocated=0, alphabet="DNA", device=0):
+                 num_threads=1, memory_preallocated=0, alphabet="DNA", device=0, no_batching=False):
         self._lib = _lib.load()
         self._ctx = ctypes.c_void_p()
         self._k = int(k)
@@ -157,7 +157,7 @@ class BOSSChunkConstructor:
         prm = MtgParams(k=int(k), alphabet=_lib.ALPHABETS[alphabet],
                         both_strands=int(bool(both_strands)), bits_per_count=int(bits_per_count),
                         filter_suffix=filter_suffix.encode() if filter_suffix else None,
-                        device=int(device), reserved=0,
+                        device=int(device), reserved=1 if no_batching else 0,   # MTG_FLAG_NO_BATCHING
                         memory_preallocated=float(memory_preallocated))
         rc = self._lib.mtg_create(ctypes.byref(prm), ctypes.byref(self._ctx))
         if rc != _lib.MTG_OK:

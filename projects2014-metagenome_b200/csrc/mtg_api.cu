@@ -218,6 +218,20 @@ struct mtg_ctx {
     // the reads are dropped; mtg_build_chunk merges the runs (saturating count sums).
     std::vector<RealSet> runs;
     uint64_t pending_windows = 0, batch_limit = 0, n_batches = 0;
+    // Pipelined host pushes: the reads of a segment go up on copy_stream into one of two staging
+    // buffers while the device folds the previous batch (extract + sort + fold of >= push_batch k-mer
+    // windows) on `stream`; the batch of a segment is cut when the NEXT segment's copy is in flight
+    // (or by mtg_build_chunk).
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t copy_done = nullptr;
+    struct Stage {
+        void *d_raw = nullptr, *d_off = nullptr;
+        size_t raw_cap = 0, off_cap = 0;
+        cudaEvent_t consumed = nullptr;   // the pack kernel that read this staging buffer is done
+    } stage[2];
+    int stage_idx = 0;
+    bool flush_pending = false;
+    uint64_t push_batch = 0;
     // range-partitioned (multi-GPU) build state, see mtg_mg_* below
     struct Mg {
         DevBuf keys, targets, tset, sinks, src, rkeys, rcounts;
@@ -426,6 +440,15 @@ int mtg_create(const mtg_params *p, mtg_ctx **out) {
         const uint64_t kb = ctx->al.K * ctx->al.L <= 64 ? 8 : 16;
         ctx->batch_limit = (uint64_t)(0.35 * (double)prop.totalGlobalMem / (2.0 * (double)(kb + (p->bits_per_count ? 4 : 0))));
         if (const char *e = getenv("MTG_BATCH_KMERS")) ctx->batch_limit = strtoull(e, nullptr, 10);
+        // host pushes are folded in batches of ~280 M k-mer windows (a quarter of BASELINE cfg #2) so that
+        // the sort of one batch runs under the H2D copy of the next
+        ctx->push_batch = 280000000ull;
+        if (const char *e = getenv("MTG_PUSH_BATCH_KMERS")) ctx->push_batch = strtoull(e, nullptr, 10);
+        if (ctx->batch_limit && ctx->push_batch > ctx->batch_limit) ctx->push_batch = ctx->batch_limit;
+        if (p->reserved & MTG_FLAG_NO_BATCHING) ctx->batch_limit = ctx->push_batch = 0;
+        MTG_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+        MTG_CUDA(cudaEventCreateWithFlags(&ctx->copy_done, cudaEventDisableTiming));
+        for (auto &st : ctx->stage) MTG_CUDA(cudaEventCreateWithFlags(&st.consumed, cudaEventDisableTiming));
     } catch (const CudaError &e) {
         int rc = fail_cuda(nullptr, e);
         delete ctx;
@@ -445,6 +468,14 @@ void mtg_destroy(mtg_ctx *ctx) {
         if (b.ev) cudaEventDestroy(b.ev);
     }
     if (ctx->stream) cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) { cudaStreamSynchronize(ctx->copy_stream); cudaStreamDestroy(ctx->copy_stream); }
+    if (ctx->copy_done) cudaEventDestroy(ctx->copy_done);
+    for (auto &st : ctx->stage) {
+        if (st.d_raw) cudaFree(st.d_raw);
+        if (st.d_off) cudaFree(st.d_off);
+        if (st.consumed) cudaEventDestroy(st.consumed);
+    }
+    ctx->runs.clear();
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
 }
@@ -461,7 +492,7 @@ void mtg_pack_reads(const char *bases, const uint64_t *offsets, size_t n_reads, 
 }
 
 }  // extern "C"
-namespace { void maybe_flush_batch(mtg_ctx *ctx, uint64_t new_windows); }
+namespace { void maybe_flush_batch(mtg_ctx *ctx, uint64_t new_windows, bool force = false); }
 extern "C" {
 
 int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, const uint64_t *counts,
@@ -479,7 +510,9 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
         cudaPointerAttributes attr;
         const bool pinned_src = cudaPointerGetAttributes(&attr, bases) == cudaSuccess && attr.type == cudaMemoryTypeHost;
         cudaGetLastError();
-        const size_t CHUNK = pinned_src ? (size_t)1 << 30 : (size_t)64 << 20;
+        // segment size: pinned caller memory goes up in pieces of about one fold batch (~400 MB), pageable
+        // memory through 64 MB pinned staging pieces
+        const size_t CHUNK = pinned_src ? (size_t)400 << 20 : (size_t)64 << 20;
         size_t r0 = 0;
         while (r0 < n_reads) {
             // segment end: first r1 with packed size (raw bytes + one separator per read) >= CHUNK
@@ -517,12 +550,43 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
                     h_counts[r - r0] = (uint32_t)std::min<uint64_t>(counts[r], ctx->cmax);
             {
                 std::lock_guard<std::mutex> lk(ctx->mu);
-                cudaStream_t s = ctx->stream;
-                DevBuf d_raw(std::max<size_t>(raw_bytes, 16), s), d_off(off_bytes, s);
+                cudaStream_t s = ctx->stream, cs = ctx->copy_stream;
+                mtg_ctx::Stage &st = ctx->stage[ctx->stage_idx];
+                ctx->stage_idx ^= 1;
+                if (st.raw_cap < raw_bytes || st.off_cap < off_bytes) {   // (re)size this staging buffer
+                    MTG_CUDA(cudaEventSynchronize(st.consumed));
+                    if (st.raw_cap < raw_bytes) {
+                        if (st.d_raw) cudaFree(st.d_raw);
+                        st.d_raw = nullptr;
+                        st.raw_cap = 0;
+                        const size_t cap = std::max<size_t>(raw_bytes + (raw_bytes >> 3), 1 << 20);
+                        MTG_CUDA(cudaMalloc(&st.d_raw, cap));
+                        st.raw_cap = cap;
+                    }
+                    if (st.off_cap < off_bytes) {
+                        if (st.d_off) cudaFree(st.d_off);
+                        st.d_off = nullptr;
+                        st.off_cap = 0;
+                        const size_t cap = std::max<size_t>(off_bytes + (off_bytes >> 3), 1 << 16);
+                        MTG_CUDA(cudaMalloc(&st.d_off, cap));
+                        st.off_cap = cap;
+                    }
+                }
+                // the copies go up on their own stream, behind the pack kernel that last read this buffer
+                MTG_CUDA(cudaStreamWaitEvent(cs, st.consumed, 0));
+                MTG_CUDA(cudaMemcpyAsync(st.d_raw, pinned_src ? bases + offsets[r0] : h_raw, raw_bytes,
+                                         cudaMemcpyHostToDevice, cs));
+                MTG_CUDA(cudaMemcpyAsync(st.d_off, h_off, off_bytes, cudaMemcpyHostToDevice, cs));
+                MTG_CUDA(cudaEventRecord(ctx->copy_done, cs));
+                MTG_CUDA(cudaEventRecord(pb->ev, cs));
+                pb->state = PinnedBuf::IN_FLIGHT;
+                // ... and while they are in flight the device folds the batch that is due
+                if (ctx->flush_pending) {
+                    ctx->flush_pending = false;
+                    maybe_flush_batch(ctx, 0, true);
+                }
+                MTG_CUDA(cudaStreamWaitEvent(s, ctx->copy_done, 0));
                 seg.own_packed.alloc(padded, s);
-                MTG_CUDA(cudaMemcpyAsync(d_raw.p, pinned_src ? bases + offsets[r0] : h_raw, raw_bytes,
-                                         cudaMemcpyHostToDevice, s));
-                MTG_CUDA(cudaMemcpyAsync(d_off.p, h_off, off_bytes, cudaMemcpyHostToDevice, s));
                 if (want_starts) {
                     seg.starts.alloc(nr * 8, s);
                     seg.has_starts = true;
@@ -532,26 +596,24 @@ int mtg_push_reads(mtg_ctx *ctx, const char *bases, const uint64_t *offsets, con
                     MTG_CUDA(cudaMemcpyAsync(seg.counts.p, h_counts, nr * 4, cudaMemcpyHostToDevice, s));
                     seg.has_counts = true;
                     ctx->any_explicit_counts = true;
+                    MTG_CUDA(cudaEventRecord(pb->ev, s));   // the staging buffer is also read on this stream
                 }
-                pack_reads_device(d_raw.as<uint8_t>(), d_off.as<uint64_t>(), nr, seg.own_packed.as<uint8_t>(), padded,
-                                  want_starts ? seg.starts.as<uint64_t>() : nullptr, s);
+                pack_reads_device((const uint8_t *)st.d_raw, (const uint64_t *)st.d_off, nr, seg.own_packed.as<uint8_t>(),
+                                  padded, want_starts ? seg.starts.as<uint64_t>() : nullptr, s);
                 ctx->launches += 1;
-                MTG_CUDA(cudaEventRecord(pb->ev, s));
-                pb->state = PinnedBuf::IN_FLIGHT;
+                MTG_CUDA(cudaEventRecord(st.consumed, s));
                 seg.d_packed = seg.own_packed.as<uint8_t>();
                 seg.nbytes = padded;
                 seg.n_windows_max = nwin;
                 seg.n_reads = nr;
                 ctx->segs.push_back(std::move(seg));
-                // d_raw / d_off go back to the arena here: all work of the context is ordered on s
-            }
-            {
-                std::lock_guard<std::mutex> lk(ctx->mu);
-                maybe_flush_batch(ctx, nwin);
+                ctx->pending_windows += nwin;
+                if (ctx->push_batch && ctx->pending_windows >= ctx->push_batch && ctx->suffix.empty())
+                    ctx->flush_pending = true;   // cut when the next segment's copy is in flight (or never)
+                if (pinned_src) MTG_CUDA(cudaEventSynchronize(ctx->copy_done));   // the caller's memory is free again
             }
             r0 = r1;
         }
-        if (pinned_src) MTG_CUDA(cudaStreamSynchronize(ctx->stream));   // the caller's memory is free again
     } catch (const CudaError &e) {
         return fail_cuda(ctx, e);
     }
@@ -1300,13 +1362,15 @@ void clear_ctx(mtg_ctx *ctx) {
     ctx->segs.clear();
     ctx->runs.clear();
     ctx->pending_windows = 0;
+    ctx->flush_pending = false;
     ctx->any_explicit_counts = false;
 }
 
 // caller holds ctx->mu: cut a batch when the pending reads hold batch_limit k-mer windows
-void maybe_flush_batch(mtg_ctx *ctx, uint64_t new_windows) {
+void maybe_flush_batch(mtg_ctx *ctx, uint64_t new_windows, bool force) {
     ctx->pending_windows += new_windows;
-    if (!ctx->batch_limit || ctx->pending_windows < ctx->batch_limit || !ctx->suffix.empty()) return;
+    if (!ctx->suffix.empty()) return;
+    if (!force && (!ctx->batch_limit || ctx->pending_windows < ctx->batch_limit)) return;
     if (ctx->al.K * ctx->al.L <= 64) flush_batch<uint64_t>(ctx);
     else flush_batch<u128>(ctx);
 }
@@ -2051,6 +2115,8 @@ uint32_t mtg_mg_part_bits(const mtg_ctx *ctx) { return ctx ? mg_part_bits(ctx) :
 
 int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_t *n) {
     MG_GUARD(ctx, {
+        if (!ctx->runs.empty())
+            return fail(ctx, MTG_ERR_STATE, "create the context with MTG_FLAG_NO_BATCHING for the mtg_mg_* phases");
         if (ctx->any_explicit_counts)
             return fail(ctx, MTG_ERR_UNSUPPORTED, "per-read counts are not supported by the range-partitioned build");
         if (!ctx->suffix.empty())
@@ -2062,6 +2128,8 @@ int mtg_mg_extract(mtg_ctx *ctx, uint64_t *bucket_counts, void **d_keys, uint64_
 
 int mtg_mg_count(mtg_ctx *ctx, uint64_t *bucket_counts, uint64_t *n) {
     MG_GUARD(ctx, {
+        if (!ctx->runs.empty())
+            return fail(ctx, MTG_ERR_STATE, "create the context with MTG_FLAG_NO_BATCHING for the mtg_mg_* phases");
         if (ctx->any_explicit_counts)
             return fail(ctx, MTG_ERR_UNSUPPORTED, "per-read counts are not supported by the range-partitioned build");
         if (!ctx->suffix.empty())

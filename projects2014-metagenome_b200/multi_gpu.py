@@ -153,7 +153,9 @@ class RangedRank:
         self.torch = torch
         self.device = torch.device("cuda", device)
         self.words = key_words(K, alphabet)
-        self.ctor = BOSSChunkConstructor.initialize(K - 1, canonical, bpc, alphabet=alphabet, device=device)
+        # the mtg_mg_* phases consume the raw reads: no folding into runs at push time
+        self.ctor = BOSSChunkConstructor.initialize(K - 1, canonical, bpc, alphabet=alphabet, device=device,
+                                                    no_batching=True)
         self.nb = 1 << self.ctor.mg_part_bits()
 
     def extract(self):

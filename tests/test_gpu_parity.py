@@ -454,3 +454,32 @@ def test_super_batched_build(K, alphabet, canonical, bpc, explicit, monkeypatch)
     assert np.array_equal(chunk.F, ref["F"])
     if bpc:
         assert np.array_equal(chunk.weights, ref["weights"])
+
+
+@pytest.mark.parametrize("pinned", [False, True])
+@pytest.mark.parametrize("K,canonical,bpc", [(31, True, 8), (20, False, 0)])
+def test_pipelined_host_pushes(K, canonical, bpc, pinned, monkeypatch):
+    """Host pushes are pipelined: a segment's reads go up on the copy stream while the device folds the
+    previous batch (MTG_PUSH_BATCH_KMERS forced small here). Several pushes from pageable and from
+    pinned (torch pin_memory) host memory; the chunk must equal the oracle's."""
+    import torch
+    monkeypatch.setenv("MTG_PUSH_BATCH_KMERS", "30000")
+    reads = dna_reads(900 + K, 5000, 110, 30_000, n_frac=0.001)
+    ctor = mtg_b200.BOSSChunkConstructor.initialize(K - 1, canonical, bpc)
+    for i in range(0, len(reads), 700):
+        bases, offsets = oracle_lib.concat_reads(reads[i:i + 700])
+        arr = np.frombuffer(bases, dtype=np.uint8)
+        if pinned:
+            t = torch.empty(len(arr), dtype=torch.uint8, pin_memory=True)
+            t.numpy()[:] = arr
+            ctor.add_packed(t.numpy(), offsets)
+        else:
+            ctor.add_packed(arr.copy(), offsets)
+    chunk = ctor.build_chunk()
+    ctor.close()
+    ref = oracle_lib.oracle_build(reads, K, canonical=canonical, bits_per_count=bpc)
+    assert chunk.n_rows == ref["n_rows"] and chunk.stats["n_real"] == ref["n_real"]
+    assert np.array_equal(chunk.W, ref["W"]) and np.array_equal(chunk.last, ref["last"])
+    assert np.array_equal(chunk.F, ref["F"])
+    if bpc:
+        assert np.array_equal(chunk.weights, ref["weights"])
