@@ -100,8 +100,9 @@ unique_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_
 // The 16-byte left halo holds keys[tile_base - 1], so a head is simply sk[i] != sk[i - 1].
 constexpr int UB_THREADS = 256;
 
-// Tiles are numbered by blockIdx.x (blocks of a 1-D grid are dispatched in index order, which is
-// what the look-back needs), so the bulk load is issued by the first instruction of the block.
+// Tiles are numbered by an atomic ticket (like the onesweep pass): the look-back spins on the
+// predecessor tiles, so a tile may only wait for tiles whose blocks have already started -- CUDA
+// does not promise that blocks are dispatched in blockIdx order.
 template <typename KeyT, int UB_TILE_BYTES>
 __global__ void __launch_bounds__(UB_THREADS)
 unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__ out_keys,
@@ -116,17 +117,22 @@ unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__
     __shared__ __align__(8) unsigned long long bar;
     __shared__ uint32_t warp_cnt[WARPS + 1];
     __shared__ uint64_t slot;
-    const uint32_t tile = blockIdx.x;
+    __shared__ uint32_t sh_tile;
+    if (threadIdx.x == 0) {
+        const uint32_t t = atomicAdd(tile_counter, 1u);
+        sh_tile = t;
+        const uint64_t tb = (uint64_t)t * TILE;
+        const uint32_t v = (uint32_t)(n - tb < (uint64_t)TILE ? n - tb : TILE);
+        mbar_init(&bar, 1);
+        const uint32_t halo = t ? 16u : 0u;
+        const uint32_t bytes = ((v * (uint32_t)sizeof(KeyT) + 15u) & ~15u) + halo;
+        bulk_load_g2s(reinterpret_cast<unsigned char *>(sk) - halo,
+                      reinterpret_cast<const unsigned char *>(keys + tb) - halo, bytes, &bar);
+    }
+    __syncthreads();   // the barrier is initialised (and the ticket drawn) before anyone waits on it
+    const uint32_t tile = sh_tile;
     const uint64_t tile_base = (uint64_t)tile * TILE;
     const uint32_t valid = (uint32_t)(n - tile_base < (uint64_t)TILE ? n - tile_base : TILE);
-    if (threadIdx.x == 0) {
-        mbar_init(&bar, 1);
-        const uint32_t halo = tile ? 16u : 0u;
-        const uint32_t bytes = ((valid * (uint32_t)sizeof(KeyT) + 15u) & ~15u) + halo;
-        bulk_load_g2s(reinterpret_cast<unsigned char *>(sk) - halo,
-                      reinterpret_cast<const unsigned char *>(keys + tile_base) - halo, bytes, &bar);
-    }
-    __syncthreads();   // the barrier is initialised before anyone waits on it
     mbar_wait(&bar, 0);
 
     const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -172,17 +178,42 @@ unique_bulk_kernel(const KeyT *__restrict__ keys, uint64_t n, KeyT *__restrict__
 
 __global__ void run_counts_kernel(const uint64_t *__restrict__ starts, const uint32_t *__restrict__ vals,
                                   uint64_t m, uint32_t cmax, uint32_t *__restrict__ counts) {
-    uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= m) return;
-    uint64_t a = starts[j], b = starts[j + 1];
-    uint64_t c;
-    if (vals) {
-        c = 0;
-        for (uint64_t i = a; i < b && c < cmax; ++i) c += vals[i];
-    } else {
-        c = b - a;
+    // saturating sum of the counts of run j (sorted_multiset.cpp:70-82). A thread sums a short run on its
+    // own; a long one (a low-complexity k-mer with 10^6 copies) is summed by the whole warp, strided and
+    // coalesced, and stops once it saturates.
+    constexpr uint64_t LONG_RUN = 64;
+    const uint64_t j = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = j < m;
+    const unsigned lane = threadIdx.x & 31;
+    uint64_t a = 0, b = 0, c = 0;
+    if (valid) { a = starts[j]; b = starts[j + 1]; }
+    const bool is_long = valid && vals && b - a > LONG_RUN;
+    if (valid && !is_long) {
+        if (vals) {
+            for (uint64_t i = a; i < b && c < cmax; ++i) c += vals[i];
+        } else {
+            c = b - a;
+        }
     }
-    counts[j] = c > cmax ? cmax : (uint32_t)c;
+    unsigned todo = __ballot_sync(0xffffffffu, is_long);
+    while (todo) {
+        const int l = __ffs(todo) - 1;
+        todo &= todo - 1;
+        const uint64_t la = __shfl_sync(0xffffffffu, a, l), lb = __shfl_sync(0xffffffffu, b, l);
+        uint64_t sum = 0;
+        for (uint64_t i = la; i < lb; i += 32 * 8) {
+#pragma unroll
+            for (int u = 0; u < 8; ++u) {
+                const uint64_t q = i + (uint64_t)u * 32 + lane;
+                if (q < lb) sum += vals[q];
+            }
+            if (__any_sync(0xffffffffu, sum >= cmax)) break;   // saturated
+        }
+#pragma unroll
+        for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if ((int)lane == l) c = sum;
+    }
+    if (valid) counts[j] = c > cmax ? cmax : (uint32_t)c;
 }
 
 constexpr int SC_THREADS = 256;

@@ -483,3 +483,14 @@ def test_pipelined_host_pushes(K, canonical, bpc, pinned, monkeypatch):
     assert np.array_equal(chunk.F, ref["F"])
     if bpc:
         assert np.array_equal(chunk.weights, ref["weights"])
+
+
+def test_long_runs_with_explicit_counts():
+    """A low-complexity k-mer with thousands of copies and per-read counts: the saturating run sums of
+    long runs are computed warp-cooperatively (run_counts_kernel); 32-bit counts never saturate here, so
+    the whole run is summed."""
+    reads = ["A" * 150] * 300 + dna_reads(3, 400, 90, 3000) + ["ACGT" * 30] * 50
+    counts = [1 + (i % 7) for i in range(len(reads))]
+    for bpc in (8, 32):
+        check(reads, 21, canonical=True, bits_per_count=bpc, counts=counts)
+        check(reads, 21, canonical=False, bits_per_count=bpc, counts=counts)
