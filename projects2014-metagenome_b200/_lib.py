@@ -43,7 +43,7 @@ EXPORTS = ["mtg_create", "mtg_destroy", "mtg_last_error", "mtg_push_reads",
            "mtg_push_packed_device", "mtg_packed_size", "mtg_pack_reads", "mtg_build_chunk",
            "mtg_build_chunk_device", "mtg_set_stream", "mtg_free_chunk", "mtg_debug_sorted_kmers", "mtg_debug_free", "mtg_debug_sort_u64",
            "mtg_debug_sort_u128", "mtg_debug_sort_bench", "mtg_debug_unique_bench", "mtg_mg_part_bits", "mtg_mg_extract", "mtg_mg_count", "mtg_mg_route", "mtg_mg_targets_count", "mtg_mg_targets_route",
-           "mtg_mg_collect", "mtg_mg_strands", "mtg_mg_merge", "mtg_mg_targets", "mtg_mg_dummies", "mtg_mg_build", "mtg_peer_push", "mtg_mg_debug_pending", "mtg_mg_accumulate", "mtg_alloc_pinned", "mtg_free_pinned"]
+           "mtg_mg_collect", "mtg_mg_strands", "mtg_mg_merge", "mtg_mg_targets", "mtg_mg_dummies", "mtg_mg_build", "mtg_peer_push", "mtg_mg_debug_pending", "mtg_mg_accumulate", "mtg_alloc_pinned", "mtg_free_pinned", "mtg_debug_sort_config"]
 
 _lib = None
 
@@ -116,6 +116,8 @@ def load():
     lib.mtg_peer_push.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(ctypes.c_void_p),
                                   ctypes.POINTER(ctypes.c_void_p), u64p]
     lib.mtg_peer_push.restype = ctypes.c_int
+    lib.mtg_debug_sort_config.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.mtg_debug_sort_config.restype = None
     lib.mtg_alloc_pinned.argtypes = [ctypes.c_size_t]
     lib.mtg_alloc_pinned.restype = ctypes.c_void_p
     lib.mtg_free_pinned.argtypes = [ctypes.c_void_p]

@@ -1550,6 +1550,10 @@ int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_val
     return MTG_OK;
 }
 
+// tuning hook: stable-pass kernel (3 = peer masks, 5 = atomic slot + repair) and whether the first pass
+// of an order-free sort may rank unstably; -1 keeps a setting
+void mtg_debug_sort_config(int variant, int unstable_first) { set_sort_config(variant, unstable_first); }
+
 // Device-resident timing of the unique / fold kernel alone: keys[i] = i / dup (u64), best of iters.
 int mtg_debug_unique_bench(int device, uint64_t n, uint32_t dup, int with_starts, int iters, float *ms_out) {
     try {

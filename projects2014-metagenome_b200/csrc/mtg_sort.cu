@@ -527,21 +527,20 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
 // reverse-complement sort, the passes after the fold): 85.4 vs 81.3 ms on the whole cfg #2 build, so it
 // is not the default. The UNSTABLE v5 ranking (first pass of a sort that allows it) is 17 % faster
 // than a stable pass on random digits and is used; MTG_SORT_UNSTABLE_FIRST=0 switches it off.
+static int g_sort_variant = -1, g_unstable_first = -1;
 static int sort_variant() {
-    static int v = -1;
-    if (v < 0) {
+    if (g_sort_variant < 0) {
         const char *e = getenv("MTG_SORT_VARIANT");
-        v = e ? atoi(e) : 3;
+        g_sort_variant = e ? atoi(e) : 3;
     }
-    return v;
+    return g_sort_variant;
 }
 static bool unstable_first_allowed() {
-    static int v = -1;
-    if (v < 0) {
+    if (g_unstable_first < 0) {
         const char *e = getenv("MTG_SORT_UNSTABLE_FIRST");
-        v = e ? atoi(e) : 1;
+        g_unstable_first = e ? atoi(e) : 1;
     }
-    return v != 0;
+    return g_unstable_first != 0;
 }
 
 template <typename KeyT>
@@ -707,6 +706,12 @@ void fill_random_words(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t
     if (!nwords) return;
     fill_random_kernel<<<(unsigned)div_up(nwords, (size_t)256), 256, 0, stream>>>(words, nwords, seed,
                                                                                  hi_mask, wide ? 1 : 0);
+}
+
+// tuning hook (mtg_debug_sort_config): -1 keeps a setting
+void set_sort_config(int variant, int unstable_first) {
+    if (variant >= 0) g_sort_variant = variant;
+    if (unstable_first >= 0) g_unstable_first = unstable_first;
 }
 
 size_t sort_tile_keys(bool wide) {
