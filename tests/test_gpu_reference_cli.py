@@ -143,12 +143,20 @@ def test_reference_gtest_suite_through_the_c_abi():
     constructor and is reported."""
     need(UNIT)
     os.makedirs(os.path.join(REF, "test_data"), exist_ok=True)
-    p = run(UNIT, ["--gtest_filter=BOSSConstruct*:WeightedBOSSConstruct*"], True, REF)
+    # the whole selection takes ~4 min on the GPU box (the tests' own dynamic-insertion oracle dominates;
+    # ~20 min with the reference's CPU constructors): MTG_TEST_FULL_GTEST=1 runs all 11 tests (log of such a
+    # run: profiles/r02_reference_gtest_through_c_abi.log), the default a representative five
+    full = os.environ.get("MTG_TEST_FULL_GTEST") == "1"
+    flt = "BOSSConstruct*:WeightedBOSSConstruct*" if full else (
+        "BOSSConstruct.ConstructionEQAppendingCanonical:BOSSConstruct.ConstructionLowerCase:"
+        "BOSSConstruct.ConstructionDummySentinel:BOSSConstruct.ConstructionFromChunks:"
+        "WeightedBOSSConstruct.ConstructionDummyKmersZeroWeightChunks")
+    p = run(UNIT, ["--gtest_filter=" + flt], True, REF)
     out = p.stdout + p.stderr
-    assert "[  PASSED  ] 11 tests" in out, out[-3000:]
+    assert "[  PASSED  ] %d tests" % (11 if full else 5) in out, out[-3000:]
     line = [ln for ln in p.stderr.splitlines() if "chunks built on the GPU" in ln][-1]
     n_gpu = int(line.split("chunks built on the GPU:")[1].split(",")[0])
-    assert n_gpu > 500, line          # 11 tests x k = 1..63 (and chunked variants)
+    assert n_gpu > (500 if full else 150), line          # tests x k = 1..63 (and chunked variants)
 
 
 def test_cfg2_full_size_chunk_files_equal_reference(tmp_path):
