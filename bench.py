@@ -41,7 +41,7 @@ WORKLOADS = {
                  read_len=300, G=0, seed=4, e=0.0, K=12, canonical=False, bpc=0, alphabet="Protein",
                  scaling="strong"),
 }
-SLICE_READS = 12_500_000     # reads are generated and pushed in slices of at most this many
+SLICE_READS = 6_250_000      # reads are generated and pushed in slices of at most this many
 
 
 def parse_args():
@@ -294,8 +294,9 @@ def run_ours(args, wl):
     alphabet = wl.get("alphabet", "DNA")
     slices = []
     genome = synth.genome_torch(wl["seed"], wl["G"], dev) if alphabet == "DNA" else None
-    for r0 in range(0, n_reads, SLICE_READS):
-        r1 = min(n_reads, r0 + SLICE_READS)
+    slice_reads = n_reads if n_reads <= 12_500_000 else SLICE_READS     # the headline workload is one slice
+    for r0 in range(0, n_reads, slice_reads):
+        r1 = min(n_reads, r0 + slice_reads)
         if alphabet == "DNA":
             slices.append(synth.dna_reads_packed_torch(wl["seed"], n_reads, L, wl["G"], wl["e"], device=dev,
                                                        r0=r0, r1=r1, genome=genome))

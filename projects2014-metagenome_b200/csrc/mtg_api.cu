@@ -57,12 +57,35 @@ struct Arena {
             void *p = nullptr;
             cudaError_t e = cudaMalloc(&p, want);
             if (e != cudaSuccess && want > n) { cudaGetLastError(); want = n; e = cudaMalloc(&p, want); }
+            if (e != cudaSuccess) {
+                // slabs are never split across requests of other sizes: give the completely free ones
+                // back to the driver (cudaFree synchronises the device) and ask again
+                cudaGetLastError();
+                if (trim()) e = cudaMalloc(&p, want);
+            }
             if (e != cudaSuccess) { cudaGetLastError(); throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__}; }
             slabs.push_back(Slab{(char *)p, want});
             total += want;
             free_blocks[(char *)p] = want;
         }
         throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
+    }
+    // caller holds mu: cudaFree every slab that is one free block; true if something was released
+    bool trim() {
+        bool any = false;
+        for (size_t i = 0; i < slabs.size();) {
+            auto it = free_blocks.find(slabs[i].base);
+            if (it != free_blocks.end() && it->second == slabs[i].size) {
+                free_blocks.erase(it);
+                cudaFree(slabs[i].base);
+                total -= slabs[i].size;
+                slabs.erase(slabs.begin() + i);
+                any = true;
+            } else {
+                ++i;
+            }
+        }
+        return any;
     }
     void free(void *ptr) {
         if (!ptr) return;
@@ -437,8 +460,11 @@ int mtg_create(const mtg_params *p, mtg_ctx **out) {
         // super-batch size: the sort ping-pongs two key arrays, which may take ~35 % of the device
         // memory; the rest is for the reads, the folded runs and the later stages. MTG_BATCH_KMERS
         // overrides (the tests force the batched path on small inputs with it)
+        // per k-mer of a batch: the two key arrays of the sort, the fold's output and -- in counting mode
+        // -- the run starts (8 B) and counts; a quarter of the device memory for all of that
         const uint64_t kb = ctx->al.K * ctx->al.L <= 64 ? 8 : 16;
-        ctx->batch_limit = (uint64_t)(0.35 * (double)prop.totalGlobalMem / (2.0 * (double)(kb + (p->bits_per_count ? 4 : 0))));
+        const double per_kmer = 3.0 * (double)kb + (p->bits_per_count ? 16.0 : 0.0);
+        ctx->batch_limit = (uint64_t)(0.25 * (double)prop.totalGlobalMem / per_kmer);
         if (const char *e = getenv("MTG_BATCH_KMERS")) ctx->batch_limit = strtoull(e, nullptr, 10);
         // host pushes are folded in batches of ~280 M k-mer windows (a quarter of BASELINE cfg #2) so that
         // the sort of one batch runs under the H2D copy of the next
@@ -640,6 +666,9 @@ int mtg_push_packed_device(mtg_ctx *ctx, const void *d_packed, size_t n_bytes, u
     try {
         MTG_CUDA(cudaSetDevice(ctx->device));
         t_arena = ctx->arena;
+        // a batch never exceeds the limit by a whole segment: what is pending is folded first
+        if (ctx->batch_limit && ctx->pending_windows && ctx->pending_windows + n_windows_max > ctx->batch_limit)
+            maybe_flush_batch(ctx, 0, true);
         ReadSegment seg;
         seg.d_packed = (const uint8_t *)d_packed;
         seg.nbytes = n_bytes;
