@@ -7,6 +7,7 @@ exchange is additionally verified slice by slice (row counts + checksums, DistBu
 multi-GPU bench line carries a parity verdict.
   DIST_CHECK_VARIANTS=1,0   values of MTG_ROUTE (1 = exchanges fused into the scatter kernels)
   DIST_CHECK_REPEATS=n      repeats of every case and variant
+  DIST_CHECK_VERIFY=0       without the per-exchange verification (plain build timing)
 TEST INFRASTRUCTURE (uses oracle/)."""
 import os
 import sys
@@ -24,7 +25,7 @@ from mtg_b200 import multi_gpu, synth  # noqa: E402
 CASES = [(31, True, 0), (31, True, 8), (31, False, 12), (63, True, 0), (12, False, 0), (40, True, 16)]
 
 
-def run_cases(rank, world, local, variants=("1",), repeats=1, log=None, cases=CASES, n_reads=30_000):
+def run_cases(rank, world, local, variants=("1",), repeats=1, log=None, cases=CASES, n_reads=30_000, verify=True):
     """-> dict(cases, builds, ok, world, mismatches=[...]) on every rank (rank 0 decides, broadcast)."""
     log = log or (lambda m: print(m, flush=True))
     builds, bad = 0, []
@@ -36,7 +37,7 @@ def run_cases(rank, world, local, variants=("1",), repeats=1, log=None, cases=CA
         for variant in variants:
             os.environ["MTG_ROUTE"] = variant
             for rep in range(repeats):
-                db = multi_gpu.DistBuild(K, canonical, bpc, device=local, verify=True)
+                db = multi_gpu.DistBuild(K, canonical, bpc, device=local, verify=verify)
                 db.rank.ctor.add_sequences(reads[rank::world])
                 err = None
                 try:
@@ -80,7 +81,7 @@ def run_cases(rank, world, local, variants=("1",), repeats=1, log=None, cases=CA
     dist.broadcast(flag, 0)
     return {"cases": len(cases), "builds": builds, "ok": int(flag.item()) == 0, "world": world,
             "variants": ["fused route" if v != "0" else "separate exchange" for v in variants],
-            "repeats": repeats, "mismatches": bad,
+            "repeats": repeats, "exchange_verification": bool(verify), "mismatches": bad,
             "checker": "oracle/mtg_oracle.cpp chunk (W, last, F, weights bit for bit) + per-slice exchange checksums"}
 
 
@@ -91,7 +92,10 @@ def main():
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     variants = os.environ.get("DIST_CHECK_VARIANTS", "1").split(",")      # values of MTG_ROUTE
     repeats = int(os.environ.get("DIST_CHECK_REPEATS", "1"))
-    res = run_cases(rank, world, local, variants, repeats)
+    # DIST_CHECK_VERIFY=0: no per-exchange verification (it adds collectives and host synchronisation
+    # after every exchange): the timing of a plain build, checked only through the final chunk
+    verify = os.environ.get("DIST_CHECK_VERIFY", "1") != "0"
+    res = run_cases(rank, world, local, variants, repeats, verify=verify)
     if rank == 0:
         print("dist_check summary: %s" % res, flush=True)
     multi_gpu.release_symmetric_buffers()
