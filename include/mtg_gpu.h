@@ -243,8 +243,9 @@ int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_val
                          float *ms_out);
 /* tuning hook: which kernel runs the stable radix passes (3 = peer masks through shared memory, the
  * default; 5 = atomic slot + collision repair) and whether the first pass of an order-free sort may rank
- * unstably (default 1); -1 keeps a setting. Process-wide. */
-void mtg_debug_sort_config(int variant, int unstable_first);
+ * unstably (default 1); shape: 0 = 256 threads x 16 keys per block, 1 = 512 x 8; prefetch: distance in
+ * tiles of the L2 prefetch a block issues for a later tile (0 = off); -1 keeps a setting. Process-wide. */
+void mtg_debug_sort_config(int variant, int unstable_first, int shape, int prefetch);
 /* test/bench hook: times the unique (fold) kernel alone on keys[i] = i / dup; ms_out[0] = best ms,
  * ms_out[1] = number of distinct keys found */
 int mtg_debug_unique_bench(int device, uint64_t n, uint32_t dup, int with_starts, int iters, float *ms_out);

@@ -116,7 +116,7 @@ def load():
     lib.mtg_peer_push.argtypes = [ctypes.c_void_p, ctypes.c_uint32, ctypes.POINTER(ctypes.c_void_p),
                                   ctypes.POINTER(ctypes.c_void_p), u64p]
     lib.mtg_peer_push.restype = ctypes.c_int
-    lib.mtg_debug_sort_config.argtypes = [ctypes.c_int, ctypes.c_int]
+    lib.mtg_debug_sort_config.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_int]
     lib.mtg_debug_sort_config.restype = None
     lib.mtg_alloc_pinned.argtypes = [ctypes.c_size_t]
     lib.mtg_alloc_pinned.restype = ctypes.c_void_p

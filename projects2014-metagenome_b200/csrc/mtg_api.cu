@@ -970,18 +970,31 @@ void merge_fold_runs(mtg_ctx *ctx, RealSet &a, RealSet &b, RealSet *out) {
     }
     const uint64_t n_input = a.n_input + b.n_input;
     a.keys.release(); a.counts.release(); b.keys.release(); b.counts.release();
-    DevBuf dst(sizeof(KeyT) * std::max<uint64_t>(n, 1) + 16, s), starts;
-    if (counting) starts.alloc(8 * (n + 1), s);
-    {
-        DevBuf status(sizeof(unsigned long long) * unique_status_words(n), s), tctr(sizeof(unsigned int), s);
-        unique_keys<KeyT>(mk.as<KeyT>(), n, dst.as<KeyT>(), counting ? starts.as<uint64_t>() : nullptr, d_ctr,
-                          status.as<unsigned long long>(), tctr.as<unsigned int>(), s, &ctx->launches);
-    }
-    const uint64_t m = read_counter(d_ctr, s);
-    DevBuf dc;
-    if (counting) {
-        dc.alloc(4 * std::max<uint64_t>(m, 1), s);
-        run_counts(starts.as<uint64_t>(), mc.as<uint32_t>(), m, ctx->cmax, dc.as<uint32_t>(), s, &ctx->launches);
+    // fold in chunks, so that the run-start scratch (8 B per key of a chunk) stays small next to arrays
+    // of billions of keys; a chunk never ends between two equal keys
+    DevBuf dst(sizeof(KeyT) * std::max<uint64_t>(n, 1) + 16, s), dc;
+    if (counting) dc.alloc(4 * std::max<uint64_t>(n, 1), s);
+    uint64_t chunk = 1ull << 29;
+    if (const char *e = getenv("MTG_FOLD_CHUNK")) chunk = std::max<uint64_t>(2, strtoull(e, nullptr, 10)) & ~1ull;
+    DevBuf starts, status(sizeof(unsigned long long) * unique_status_words(std::min(n, chunk + 1)), s), tctr(sizeof(unsigned int), s);
+    if (counting) starts.alloc(8 * (std::min(n, chunk + 1) + 1), s);
+    uint64_t m = 0;
+    for (uint64_t lo = 0; lo < n;) {
+        uint64_t hi = std::min(n, lo + chunk);
+        if (hi < n) {   // do not split a pair
+            KeyT edge[2];
+            MTG_CUDA(cudaMemcpyAsync(edge, mk.as<KeyT>() + hi - 1, 2 * sizeof(KeyT), cudaMemcpyDeviceToHost, s));
+            MTG_CUDA(cudaStreamSynchronize(s));
+            if (w_eq(edge[0], edge[1])) ++hi;
+        }
+        unique_keys<KeyT>(mk.as<KeyT>() + lo, hi - lo, dst.as<KeyT>() + m, counting ? starts.as<uint64_t>() : nullptr,
+                          d_ctr, status.as<unsigned long long>(), tctr.as<unsigned int>(), s, &ctx->launches);
+        const uint64_t mc_chunk = read_counter(d_ctr, s);
+        if (counting)
+            run_counts(starts.as<uint64_t>(), mc.as<uint32_t>() + lo, mc_chunk, ctx->cmax, dc.as<uint32_t>() + m, s,
+                       &ctx->launches);
+        m += mc_chunk;
+        lo = hi;
     }
     out->keys = std::move(dst);
     out->counts = std::move(dc);
@@ -1000,20 +1013,26 @@ void flush_batch(mtg_ctx *ctx) {
     ctx->any_explicit_counts = false;
     ctx->pending_windows = 0;
     ctx->n_batches += 1;
+    // keep the runs geometric (like the levels of a log-structured merge): the newest two are merged
+    // while the older is not more than twice the newer, so what is held is < 2x the distinct k-mers
+    while (ctx->runs.size() >= 2) {
+        RealSet &older = ctx->runs[ctx->runs.size() - 2], &newer = ctx->runs.back();
+        if (older.m > 2 * newer.m) break;
+        RealSet merged;
+        merge_fold_runs<KeyT>(ctx, older, newer, &merged);
+        ctx->runs.pop_back();
+        ctx->runs.back() = std::move(merged);
+    }
 }
 
 // pairwise merge rounds over the runs -> one run
 template <typename KeyT>
 void merge_all_runs(mtg_ctx *ctx, std::vector<RealSet> &runs, RealSet *out) {
-    while (runs.size() > 1) {
-        std::vector<RealSet> next;
-        for (size_t i = 0; i + 1 < runs.size(); i += 2) {
-            RealSet m;
-            merge_fold_runs<KeyT>(ctx, runs[i], runs[i + 1], &m);
-            next.push_back(std::move(m));
-        }
-        if (runs.size() & 1) next.push_back(std::move(runs.back()));
-        runs.swap(next);
+    while (runs.size() > 1) {   // the runs are geometric, oldest = largest first: fold from the small end
+        RealSet m;
+        merge_fold_runs<KeyT>(ctx, runs[runs.size() - 2], runs.back(), &m);
+        runs.pop_back();
+        runs.back() = std::move(m);
     }
     *out = std::move(runs[0]);
     runs.clear();
@@ -1581,7 +1600,9 @@ int mtg_debug_sort_bench(int device, uint64_t n, uint32_t key_bits, int with_val
 
 // tuning hook: stable-pass kernel (3 = peer masks, 5 = atomic slot + repair) and whether the first pass
 // of an order-free sort may rank unstably; -1 keeps a setting
-void mtg_debug_sort_config(int variant, int unstable_first) { set_sort_config(variant, unstable_first); }
+void mtg_debug_sort_config(int variant, int unstable_first, int shape, int prefetch) {
+    set_sort_config(variant, unstable_first, shape, prefetch);
+}
 
 // Device-resident timing of the unique / fold kernel alone: keys[i] = i / dup (u64), best of iters.
 int mtg_debug_unique_bench(int device, uint64_t n, uint32_t dup, int with_starts, int iters, float *ms_out) {

@@ -98,6 +98,12 @@ __global__ void sort_scan_hist_kernel(unsigned long long *hist) {
     h[threadIdx.x] = sh[threadIdx.x];
 }
 
+// L2 prefetch of a whole tile (TMA bulk prefetch, one instruction): the tile that will be loaded
+// `ahead` tickets later is pulled from DRAM into L2 while this block works
+__device__ __forceinline__ void prefetch_tile_l2(const void *p, uint32_t bytes) {
+    asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
+
 constexpr unsigned long long OS_VALUE_MASK = (1ull << 56) - 1;
 __device__ __forceinline__ unsigned long long os_pack(unsigned flag, unsigned epoch,
                                                       unsigned long long v) {
@@ -158,7 +164,8 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
                         const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
                         uint64_t n, DigitPass dp, const unsigned long long *__restrict__ digit_offsets,
                         unsigned long long *__restrict__ status, unsigned int *tile_counter,
-                        unsigned epoch, const unsigned char *__restrict__ route_owner = nullptr) {
+                        unsigned epoch, const unsigned char *__restrict__ route_owner = nullptr,
+                        unsigned prefetch_ahead = 0) {
     constexpr int WARPS = THREADS / 32;
     constexpr int TILE = THREADS * IPT;
     static_assert(THREADS >= RADIX, "one digit per thread in the scan phases");
@@ -180,7 +187,14 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
 
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (ROUTE && tid < RADIX) sh_owner[tid] = route_owner[tid];
-    if (tid == 0) sh_tile = atomicAdd(tile_counter, 1u);
+    if (tid == 0) {
+        const unsigned t = atomicAdd(tile_counter, 1u);
+        sh_tile = t;
+        if (prefetch_ahead && ((uint64_t)t + prefetch_ahead + 1) * TILE <= n) {
+            prefetch_tile_l2(in_keys + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(sizeof(KeyT) * TILE));
+            if (HAS_VAL) prefetch_tile_l2(in_vals + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(4 * TILE));
+        }
+    }
     for (int i = tid; i < 2 * WARPS * RADIX; i += THREADS) whist[i] = 0;   // whist and wmask
     __syncthreads();
     const unsigned tile = sh_tile;
@@ -333,7 +347,8 @@ onesweep_pass_v5_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
                         const uint32_t *__restrict__ in_vals, uint32_t *__restrict__ out_vals,
                         uint64_t n, DigitPass dp, const unsigned long long *__restrict__ digit_offsets,
                         unsigned long long *__restrict__ status, unsigned int *tile_counter,
-                        unsigned epoch, const unsigned char *__restrict__ route_owner = nullptr) {
+                        unsigned epoch, const unsigned char *__restrict__ route_owner = nullptr,
+                        unsigned prefetch_ahead = 0) {
     constexpr int WARPS = THREADS / 32;
     constexpr int TILE = THREADS * IPT;
     static_assert(THREADS >= RADIX, "one digit per thread in the scan phases");
@@ -352,7 +367,14 @@ onesweep_pass_v5_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
 
     const unsigned tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (ROUTE && tid < RADIX) sh_owner[tid] = route_owner[tid];
-    if (tid == 0) sh_tile = atomicAdd(tile_counter, 1u);
+    if (tid == 0) {
+        const unsigned t = atomicAdd(tile_counter, 1u);
+        sh_tile = t;
+        if (prefetch_ahead && ((uint64_t)t + prefetch_ahead + 1) * TILE <= n) {
+            prefetch_tile_l2(in_keys + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(sizeof(KeyT) * TILE));
+            if (HAS_VAL) prefetch_tile_l2(in_vals + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(4 * TILE));
+        }
+    }
     for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;
     __syncthreads();
     const unsigned tile = sh_tile;
@@ -488,7 +510,8 @@ onesweep_pass_v5_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
 template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, bool UNSTABLE, bool ROUTE = false>
 void launch_v5(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
                uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
-               unsigned int *ctr, unsigned epoch, cudaStream_t stream, const unsigned char *route_owner = nullptr) {
+               unsigned int *ctr, unsigned epoch, cudaStream_t stream, const unsigned char *route_owner = nullptr,
+               unsigned prefetch = 0) {
     constexpr int TILE = THREADS * IPT;
     size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
                   + sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
@@ -500,13 +523,15 @@ void launch_v5(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
         attr_set = true;
     }
     kern<<<(unsigned)div_up(n, (size_t)TILE), THREADS, smem, stream>>>(in_keys, out_keys, in_vals, out_vals, n,
-                                                                      dp, offs, status, ctr, epoch, route_owner);
+                                                                      dp, offs, status, ctr, epoch, route_owner,
+                                                                      prefetch);
 }
 
 template <typename KeyT, bool HAS_VAL, int THREADS, int IPT, int MINB, int LB, bool ROUTE = false>
 void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uint32_t *out_vals,
                uint64_t n, DigitPass dp, const unsigned long long *offs, unsigned long long *status,
-               unsigned int *ctr, unsigned epoch, cudaStream_t stream, const unsigned char *route_owner = nullptr) {
+               unsigned int *ctr, unsigned epoch, cudaStream_t stream, const unsigned char *route_owner = nullptr,
+               unsigned prefetch = 0) {
     constexpr int TILE = THREADS * IPT;
     size_t smem = sizeof(KeyT) * TILE + (HAS_VAL ? sizeof(uint32_t) * TILE : 0)
                   + 2 * sizeof(uint32_t) * (THREADS / 32) * RADIX + sizeof(long long) * RADIX
@@ -518,7 +543,8 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
         attr_set = true;
     }
     kern<<<(unsigned)div_up(n, (size_t)TILE), THREADS, smem, stream>>>(in_keys, out_keys, in_vals, out_vals, n,
-                                                                      dp, offs, status, ctr, epoch, route_owner);
+                                                                      dp, offs, status, ctr, epoch, route_owner,
+                                                                      prefetch);
 }
 
 // Stable passes: v3 (peer masks through shared memory). MTG_SORT_VARIANT=5 selects v5's stable ranking
@@ -528,6 +554,23 @@ void launch_v3(const KeyT *in_keys, KeyT *out_keys, const uint32_t *in_vals, uin
 // is not the default. The UNSTABLE v5 ranking (first pass of a sort that allows it) is 17 % faster
 // than a stable pass on random digits and is used; MTG_SORT_UNSTABLE_FIRST=0 switches it off.
 static int g_sort_variant = -1, g_unstable_first = -1;
+// launch shape of a pass: 0 = 256 threads x 16 keys, 1 = 512 x 8 (same 4096-key tile, twice the warps);
+// L2 prefetch distance in tiles (0 = off)
+static int g_launch_shape = -1, g_prefetch = -1;
+static int launch_shape() {
+    if (g_launch_shape < 0) {
+        const char *e = getenv("MTG_SORT_SHAPE");
+        g_launch_shape = e ? atoi(e) : 0;
+    }
+    return g_launch_shape;
+}
+static unsigned prefetch_tiles() {
+    if (g_prefetch < 0) {
+        const char *e = getenv("MTG_SORT_PREFETCH");
+        g_prefetch = e ? atoi(e) : 0;
+    }
+    return (unsigned)g_prefetch;
+}
 static int sort_variant() {
     if (g_sort_variant < 0) {
         const char *e = getenv("MTG_SORT_VARIANT");
@@ -601,12 +644,20 @@ int radix_sort_impl(KeyT *keys[2], uint32_t *vals[2], uint64_t n, const SortPlan
         // the first pass of a sort has no earlier order to preserve: unstable ranking (one shared atomic
         // per key) when the caller allows it (equal keys may then leave the sort in any order)
         const bool unstable = p == 0 && plan.unstable_first && unstable_first_allowed();
-        if (unstable)
-            launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, true>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
-        else if (variant == 5)
-            launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, false>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
-        else
-            launch_v3<KeyT, HAS_VAL, 256, 16 / S, 3, 0>(ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream);
+        const unsigned pf = prefetch_tiles();
+        const bool wide_block = launch_shape() == 1;
+#define PASS_ARGS ik, ok, iv, ov, n, plan.p[p], offs, ws.status, ctr, ep, stream, nullptr, pf
+        if (unstable) {
+            if (wide_block) launch_v5<KeyT, HAS_VAL, 512, 8 / S, 3, true>(PASS_ARGS);
+            else launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, true>(PASS_ARGS);
+        } else if (variant == 5) {
+            if (wide_block) launch_v5<KeyT, HAS_VAL, 512, 8 / S, 3, false>(PASS_ARGS);
+            else launch_v5<KeyT, HAS_VAL, 256, 16 / S, 4, false>(PASS_ARGS);
+        } else {
+            if (wide_block) launch_v3<KeyT, HAS_VAL, 512, 8 / S, 3, 0>(PASS_ARGS);
+            else launch_v3<KeyT, HAS_VAL, 256, 16 / S, 3, 0>(PASS_ARGS);
+        }
+#undef PASS_ARGS
         if (ws.events) cudaEventRecord(ws.events[2 * p + 1], stream);
         *launches += 1;
         cur ^= 1;
@@ -709,9 +760,11 @@ void fill_random_words(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t
 }
 
 // tuning hook (mtg_debug_sort_config): -1 keeps a setting
-void set_sort_config(int variant, int unstable_first) {
+void set_sort_config(int variant, int unstable_first, int shape, int prefetch) {
     if (variant >= 0) g_sort_variant = variant;
     if (unstable_first >= 0) g_unstable_first = unstable_first;
+    if (shape >= 0) g_launch_shape = shape;
+    if (prefetch >= 0) g_prefetch = prefetch;
 }
 
 size_t sort_tile_keys(bool wide) {

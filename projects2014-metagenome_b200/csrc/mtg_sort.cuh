@@ -47,7 +47,7 @@ struct SortWorkspace {
 };
 
 size_t sort_tile_keys(bool wide);
-void set_sort_config(int variant, int unstable_first);   // tuning hook, -1 keeps a setting
+void set_sort_config(int variant, int unstable_first, int shape, int prefetch);   // tuning hook, -1 keeps a setting
 // test/bench helper: pseudo-random words (top word of every key masked with hi_mask)
 void fill_random_words(uint64_t *words, uint64_t nwords, uint64_t seed, uint64_t hi_mask, bool wide,
                        cudaStream_t stream);   // keys per tile of the active kernel configuration

@@ -430,6 +430,7 @@ def test_super_batched_build(K, alphabet, canonical, bpc, explicit, monkeypatch)
     sorted_set.hpp:69-82; saturating count sums, sorted_multiset.cpp:70-82; palindrome doubling after the
     merge, boss_chunk_construct.cpp:205-211). The chunk must equal the oracle's single-pass chunk."""
     monkeypatch.setenv("MTG_BATCH_KMERS", "40000")
+    monkeypatch.setenv("MTG_FOLD_CHUNK", "5000")     # the merged runs are folded in chunks: many chunk edges
     if alphabet == "DNA":
         reads = dna_reads(500 + K, 6000, 100, 40_000, n_frac=0.001)
         reads[7] = "ACGT" * 25          # palindromic k-mers: counts are doubled once, after the merge
