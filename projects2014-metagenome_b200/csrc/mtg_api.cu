@@ -22,6 +22,7 @@ using namespace mtg;
 namespace {
 
 thread_local std::string g_create_error;
+thread_local std::string g_oom_detail;   // what the arena could not get (appended to the OOM message)
 
 // Device memory arena: a few large cudaMalloc slabs kept for the lifetime of the context,
 // carved first-fit with coalescing. All work of a context is ordered on one stream, so a
@@ -63,7 +64,18 @@ struct Arena {
                 cudaGetLastError();
                 if (trim()) e = cudaMalloc(&p, want);
             }
-            if (e != cudaSuccess) { cudaGetLastError(); throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__}; }
+            if (e != cudaSuccess) {
+                cudaGetLastError();
+                size_t free_b = 0, total_b = 0, largest = 0, free_sum = 0;
+                cudaMemGetInfo(&free_b, &total_b);
+                for (auto &fb : free_blocks) { largest = std::max(largest, fb.second); free_sum += fb.second; }
+                char msg[256];
+                snprintf(msg, sizeof(msg), " [request %.2f GB; arena %.2f GB in %zu slabs, %.2f GB of it free (largest block %.2f GB); "
+                         "device free %.2f of %.2f GB]", n / 1e9, total / 1e9, slabs.size(), free_sum / 1e9, largest / 1e9,
+                         free_b / 1e9, total_b / 1e9);
+                g_oom_detail = msg;
+                throw CudaError{cudaErrorMemoryAllocation, __FILE__, __LINE__};
+            }
             slabs.push_back(Slab{(char *)p, want});
             total += want;
             free_blocks[(char *)p] = want;
@@ -274,6 +286,7 @@ int fail(mtg_ctx *ctx, int code, const std::string &msg) {
 int fail_cuda(mtg_ctx *ctx, const CudaError &e) {
     std::string msg = std::string("CUDA error: ") + cudaGetErrorString(e.err) + " at " + e.file + ":"
                       + std::to_string(e.line);
+    if (e.err == cudaErrorMemoryAllocation) { msg += g_oom_detail; g_oom_detail.clear(); }
     cudaGetLastError();
     return fail(ctx, e.err == cudaErrorMemoryAllocation ? MTG_ERR_OOM : MTG_ERR_CUDA, msg);
 }

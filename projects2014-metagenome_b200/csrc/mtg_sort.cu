@@ -564,10 +564,14 @@ static int launch_shape() {
     }
     return g_launch_shape;
 }
+// Default 600 tiles ~ the blocks resident on 148 SMs (4 per SM): a block prefetches the tile that a block
+// of the NEXT wave will load. Measured (profiles/r02_pass_configs.log, 400 M keys): stable pass 2.43 ->
+// 2.26 ms with 600, no gain with 1200 (the first use of a loaded key carries ~30 % of the warp stall
+// samples, profiles/r02_ncu_full_sort_pass_kernels.txt).
 static unsigned prefetch_tiles() {
     if (g_prefetch < 0) {
         const char *e = getenv("MTG_SORT_PREFETCH");
-        g_prefetch = e ? atoi(e) : 0;
+        g_prefetch = e ? atoi(e) : 600;
     }
     return (unsigned)g_prefetch;
 }

@@ -9,8 +9,7 @@ lib = mtg_b200._lib.load()
 ms = (ctypes.c_float * 5)()
 n = int(os.environ.get("PROBE_KEYS", "400000000"))
 os.environ["MTG_BENCH_UNSTABLE_FIRST"] = "1"
-configs = [(3, 0, 0), (3, 0, 600), (3, 0, 1200), (3, 1, 0), (3, 1, 600),
-           (5, 0, 0), (5, 0, 600), (5, 1, 0), (5, 1, 600)]
+configs = [(3, 0, 0), (3, 0, 150), (3, 0, 300), (3, 0, 450), (3, 0, 600), (3, 0, 750), (3, 0, 900)]
 if os.environ.get("PROBE_CONFIGS"):
     configs = [tuple(int(x) for x in c.split(":")) for c in os.environ["PROBE_CONFIGS"].split(",")]
 for variant, shape, prefetch in configs:
