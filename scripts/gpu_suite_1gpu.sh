@@ -10,7 +10,7 @@ for w in cfg5 cfg4 cfg3; do
 done
 # launch list of the headline bench (cold-cache, serialised: shares, not absolutes)
 python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > $O/plain_bench.log 2>&1 &&
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/r02_launches_cfg2.csv \
+ncu --metrics gpu__time_duration.sum --clock-control none -k regex:mtg -c 400 --csv --log-file $O/r02_launches_cfg2.csv \
     python bench.py --steps 2 --warmup 1 --no-e2e --no-cpu-baseline > $O/ncu_launches.log 2>&1
 echo "launch list rc=$?"
 # the pass kernels: v3 stable / v5 stable / v5 unstable first pass (scripts/sort_pass_probe.py)
