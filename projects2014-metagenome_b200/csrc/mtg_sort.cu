@@ -190,9 +190,9 @@ onesweep_pass_v3_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     if (tid == 0) {
         const unsigned t = atomicAdd(tile_counter, 1u);
         sh_tile = t;
-        if (prefetch_ahead && ((uint64_t)t + prefetch_ahead + 1) * TILE <= n) {
+        if (prefetch_ahead && ((uint64_t)t + prefetch_ahead + 1) * TILE <= n && (reinterpret_cast<uintptr_t>(in_keys) & 15) == 0) {
             prefetch_tile_l2(in_keys + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(sizeof(KeyT) * TILE));
-            if (HAS_VAL) prefetch_tile_l2(in_vals + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(4 * TILE));
+            if (HAS_VAL && (reinterpret_cast<uintptr_t>(in_vals) & 15) == 0) prefetch_tile_l2(in_vals + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(4 * TILE));
         }
     }
     for (int i = tid; i < 2 * WARPS * RADIX; i += THREADS) whist[i] = 0;   // whist and wmask
@@ -370,9 +370,9 @@ onesweep_pass_v5_kernel(const KeyT *__restrict__ in_keys, KeyT *__restrict__ out
     if (tid == 0) {
         const unsigned t = atomicAdd(tile_counter, 1u);
         sh_tile = t;
-        if (prefetch_ahead && ((uint64_t)t + prefetch_ahead + 1) * TILE <= n) {
+        if (prefetch_ahead && ((uint64_t)t + prefetch_ahead + 1) * TILE <= n && (reinterpret_cast<uintptr_t>(in_keys) & 15) == 0) {
             prefetch_tile_l2(in_keys + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(sizeof(KeyT) * TILE));
-            if (HAS_VAL) prefetch_tile_l2(in_vals + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(4 * TILE));
+            if (HAS_VAL && (reinterpret_cast<uintptr_t>(in_vals) & 15) == 0) prefetch_tile_l2(in_vals + ((uint64_t)t + prefetch_ahead) * TILE, (uint32_t)(4 * TILE));
         }
     }
     for (int i = tid; i < WARPS * RADIX; i += THREADS) whist[i] = 0;

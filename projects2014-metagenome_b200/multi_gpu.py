@@ -513,6 +513,13 @@ class DistBuild:
                 _SYMM_RETIRED.append(cur)
             buf = symm.empty(cap, dtype=self.torch.uint8, device=self.rank.device)
             hdl = symm.rendezvous(buf, name)
+            # A fresh block (and its signal pad) is initialised asynchronously by its owner: no peer may
+            # signal or store into it before every rank has drained that work. Round 1 re-allocated the
+            # buffers per build and went straight on to the barrier kernel: exchanges lost rows and the
+            # barrier eventually hung (profiles/r02_dist_check_n8_plain_legacy_FAILS.log). Blocks are now
+            # allocated once per process, and this (rare) path is fenced on the host.
+            self.torch.cuda.synchronize(self.rank.device)
+            self.dist.barrier(group=self.group)
             cur = (buf, hdl)
             _SYMM_SLOTS[key] = cur
         self._slots[slot] = cur
