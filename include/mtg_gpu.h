@@ -131,7 +131,12 @@ int mtg_build_chunk_device(mtg_ctx *ctx, mtg_chunk *out);
 void mtg_free_chunk(mtg_chunk *chunk);
 
 /* Run all work of this context on the caller's CUDA stream (cudaStream_t) instead of the
- * library's own, so that the caller's events bracket it. Call before any push. */
+ * library's own, so that the caller's events bracket it. Call before any push. A NULL handle -- which
+ * is what the legacy default stream (and torch's default stream) looks like -- keeps the library's own
+ * non-blocking stream. Ordering contract either way: every entry point that returns device pointers has
+ * synchronised its stream before it returns; device memory the caller PASSES IN (mtg_push_packed_device,
+ * the d_* arguments of mtg_mg_*) must be complete on the caller's side -- same stream, or the producing
+ * stream synchronised -- before the call (multi_gpu.DistBuild._drain). */
 int mtg_set_stream(mtg_ctx *ctx, void *cuda_stream);
 
 /* Test hooks (parity of intermediate stages): run extraction + sort +

@@ -711,6 +711,16 @@ class DistBuild:
         self._mark("route targets (scatter + exchange)")
         return tin, runs[self.rank_id]
 
+    def _drain(self):
+        """Host-synchronise the torch stream before a library phase that READS tensors torch produced
+        (torch.cat, NCCL results, peer copies). The library's phases end with a stream synchronise, so
+        library -> torch needs nothing; torch -> library does whenever the two run on different streams,
+        and they do by default: torch's default stream has the handle 0, for which mtg_set_stream keeps
+        the library's own (non-blocking) stream. The missing drain before mtg_mg_build was round 1's
+        8-GPU parity miss: the expansion read the gathered source nodes before torch.cat had written them
+        (DESIGN.md 5)."""
+        self.torch.cuda.current_stream(self.rank.device).synchronize()
+
     def _mark(self, name):
         """phase timing (CUDA events on the current stream, which the library shares in bench.py)"""
         if getattr(self, "phase_events", None) is not None:
@@ -750,6 +760,7 @@ class DistBuild:
                     self.ranges = plan_ranges(hist.cpu().numpy(), self.world)
                 recv = self._exchange(keys, split_sizes(counts, self.ranges), what="k-mers")
                 self._mark("exchange kmers")
+            self._drain()
             self.rank.collect(recv)
             del recv
             self._mark("collect (sort+fold)")
@@ -772,6 +783,7 @@ class DistBuild:
             rX, rR, r_runs = got[0][0], got[1][0], got[1][1]
             rXc, rRc = (got[2][0], got[3][0]) if Xc is not None else (None, None)
             self._mark("exchange strands")
+            self._drain()
             self.rank.merge(rX, rXc, rR, rRc, r_runs)
             del rX, rR, rXc, rRc
             self._mark("merge strands")
@@ -786,6 +798,7 @@ class DistBuild:
             tin = self._exchange(tg, split_sizes(tcounts, self.ranges), what="targets")
             runs = self.last_recv_sizes                      # one sorted run per source rank
             self._mark("exchange targets")
+        self._drain()
         src = self.rank.dummies(tin, runs, per_set)
         self._mark("dummies")
         n_src = torch.tensor([src.shape[0]], dtype=torch.int64, device=dev)
@@ -811,6 +824,7 @@ class DistBuild:
             self.verified.append("source nodes (all-gather)")
         lo, hi = self.ranges[self.rank_id]
         self._mark("gather sources")
+        self._drain()      # all_src = torch.cat(NCCL broadcasts) must be written before the library copies it
         out = self.rank.build(all_src, lo, hi, self.rank_id == 0, device_output)
         self._mark("build (expand+merge+emit)")
         return out
