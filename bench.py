@@ -357,20 +357,22 @@ def run_ours(args, wl):
     P = (K * Lb + 7) // 8
     alg = algorithmic_bytes(st, n_bytes, w, c, P, wl["canonical"], 4 if alphabet == "DNA" else 6, wl["bpc"])
     device_ms = sum(s["ms_total"] for s in stats) / len(stats)
-    # DRAM traffic of that kernel from the committed ncu --set full capture of this same workload
+    # DRAM traffic of that kernel: bytes per key of the committed ncu --set full capture of the same
+    # kernel (profiles/ncu_traffic.json says which) x the keys of this launch -- not measured in this run
     traffic, traffic_src = None, None
     try:
         with open(os.path.join(ROOT, "profiles", "ncu_traffic.json")) as f:
             ent = json.load(f)["onesweep_pass_v3_kernel<u64>"]
-        if w == 8 and int(st["onesweep_keys"]) == int(ent["keys_per_launch"]):
-            traffic = float(ent["dram_bytes_read"] + ent["dram_bytes_write"])
-            traffic_src = ent["source"]
+        if w == 8 and st["onesweep_keys"]:
+            traffic = float(ent["dram_bytes_per_key"]) * int(st["onesweep_keys"])
+            traffic_src = "not measured in this run: " + ent["source"]
     except Exception:
         pass
     roofline = {
         "bound": "hbm",
-        "kernel": "onesweep_pass_v3_kernel<u64> (low passes of the main k-mer sort over all input k-mers, "
-                  "%d launches/step)" % (n_launch // max(len(stats), 1)),
+        "kernel": "onesweep pass of the main k-mer sort over all input k-mers (%d launches/step: the first one "
+                  "onesweep_pass_v5_kernel<UNSTABLE>, the others onesweep_pass_v3_kernel; mean of all)"
+                  % (n_launch // max(len(stats), 1)),
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
         "algorithmic_bytes_per_launch": bytes_launch, "ms_per_launch": ms_kernel,
