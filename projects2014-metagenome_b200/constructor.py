@@ -73,6 +73,42 @@ class Chunk:
         return self._unpack(self.weights_words, self.n_rows, self.weights_width)
 
     # ---- BOSS::Chunk::extend (boss_chunk.cpp:230-270) ---------------------
+    @staticmethod
+    def _append_bits(dst_words, dst_n, width, src_words, src_first, src_n):
+        """dst (dst_n entries of `width` bits, packed LSB-first in uint64 words) + entries
+        [src_first, src_first + src_n) of src -> new word array. Word-wise: every output word is a funnel
+        shift of two source words (vectorised), not one entry per step -- chunks hold billions of rows."""
+        nbits, sb, db = src_n * width, src_first * width, dst_n * width
+        total_words = (db + nbits + 63) // 64
+        out = np.zeros(total_words, dtype=np.uint64)
+        keep = (db + 63) // 64
+        out[:keep] = np.asarray(dst_words[:keep], dtype=np.uint64)
+        if db & 63:                                   # padding bits of dst's last word must be zero
+            out[keep - 1] &= np.uint64((1 << (db & 63)) - 1)
+        if nbits == 0:
+            return out
+        src = np.concatenate([np.asarray(src_words, dtype=np.uint64), np.zeros(2, dtype=np.uint64)])
+        # the appended bit stream, word aligned: stream[j] = bits [sb + 64 j, sb + 64 j + 64) of src
+        nsw = (nbits + 63) // 64
+        w0, o = sb >> 6, sb & 63
+        lo = src[w0:w0 + nsw]
+        if o:
+            stream = (lo >> np.uint64(o)) | (src[w0 + 1:w0 + 1 + nsw] << np.uint64(64 - o))
+        else:
+            stream = lo.copy()
+        if nbits & 63:
+            stream[-1] &= np.uint64((1 << (nbits & 63)) - 1)
+        # place it at bit offset db of out
+        d0, do = db >> 6, db & 63
+        if do == 0:
+            out[d0:d0 + nsw] = stream
+        else:
+            out[d0:d0 + nsw] |= stream << np.uint64(do)
+            hi = stream >> np.uint64(64 - do)
+            n_hi = min(nsw, total_words - (d0 + 1))
+            out[d0 + 1:d0 + 1 + n_hi] |= hi[:n_hi]
+        return out
+
     def extend(self, other):
         if (self.alph_size != other.alph_size or self.k != other.k
                 or self.W_width != other.W_width):
@@ -81,15 +117,14 @@ class Chunk:
             return
         if (self.weights_words is not None) != (other.weights_words is not None):
             raise ValueError("ERROR: trying to concatenate weighted and unweighted blocks")
-        W = np.concatenate([self.W, other.W[1:]])
-        last = np.concatenate([self.last, other.last[1:]])
-        self.W_words = self._pack(W, self.W_width)
-        self.last_words = self._pack(last, 1)
+        n, m = self.n_rows, other.n_rows - 1          # other's row 0 is its placeholder
+        self.W_words = self._append_bits(self.W_words, n, self.W_width, other.W_words, 1, m)
+        self.last_words = self._append_bits(self.last_words, n, 1, other.last_words, 1, m)
         if self.weights_words is not None:
-            wts = np.concatenate([self.weights, other.weights[1:]])
-            self.weights_words = self._pack(wts, self.weights_width)
+            self.weights_words = self._append_bits(self.weights_words, n, self.weights_width,
+                                                   other.weights_words, 1, m)
         self.F = self.F + other.F
-        self.n_rows = len(W)
+        self.n_rows = n + m
 
     # ---- BOSS::Chunk::serialize / load (boss_chunk.cpp:330-386) -----------
     @staticmethod

@@ -65,3 +65,26 @@ def test_load_rejects_a_corrupted_chunk(tmp_path):
         f.write(np.uint64(3).tobytes() + np.uint64(5).tobytes())
     with pytest.raises(ValueError):
         mtg_b200.Chunk.load(base)
+
+
+def test_word_wise_extend_equals_entry_wise():
+    """Chunk.extend appends whole words through funnel shifts; compare with packing the concatenated
+    entries from scratch for every width the path uses and ragged row counts."""
+    import numpy as np
+    from mtg_b200.constructor import Chunk
+    rng = np.random.default_rng(0)
+    for width in (1, 4, 6, 8, 12, 16, 31, 32):
+        for n, m in ((1, 1), (1, 5), (17, 130), (64, 64), (65, 1), (1000, 4097), (129, 2)):
+            a = rng.integers(0, 1 << width, n, dtype=np.uint64)
+            b = rng.integers(0, 1 << width, m + 3, dtype=np.uint64)
+            first = 1
+            got = Chunk._append_bits(Chunk._pack(a, width), n, width, Chunk._pack(b, width), first, m)
+            exp = Chunk._pack(np.concatenate([a, b[first:first + m]]), width)
+            assert np.array_equal(got[:len(exp)], exp) and not got[len(exp):].any(), (width, n, m)
+    # dirty padding bits in dst's last word are ignored
+    a = rng.integers(0, 16, 5, dtype=np.uint64)
+    words = Chunk._pack(a, 4).copy()
+    words[0] |= np.uint64(0xFF) << np.uint64(40)
+    b = rng.integers(0, 16, 9, dtype=np.uint64)
+    got = Chunk._append_bits(words, 5, 4, Chunk._pack(b, 4), 1, 8)
+    assert np.array_equal(got, Chunk._pack(np.concatenate([a, b[1:]]), 4))
