@@ -224,3 +224,57 @@ def _exchange_worker(rank, world, port, tmp):
 def test_gloo_exchange_many_bookkeeping(world, tmp_path):
     mp.spawn(_exchange_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
     assert os.path.exists(tmp_path / "ok_exchange")
+
+
+def _exchange4_worker(rank, world, port, tmp):
+    """The counting canonical build's strand exchange: FOUR items (X, R, X counts, R counts) at world 8 = 32
+    (item, destination) ranges -- the shape ADVICE round 1 flagged for mtg_peer_push's former 16-range limit.
+    Bookkeeping + per-slice verifier on gloo."""
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        class _Rank:
+            device = torch.device("cpu")
+        db = multi_gpu.DistBuild.__new__(multi_gpu.DistBuild)
+        db.torch, db.dist, db.group = torch, dist, None
+        db.world, db.rank_id, db.rank = world, rank, _Rank()
+        db.use_symm, db.push_kernel, db.a2a_bytes, db.a2a_ms = False, False, 0, 0.0
+        db.verify, db.verified = True, []
+
+        class _Ev:
+            def __init__(self, **kw): pass
+            def record(self): pass
+            def synchronize(self): pass
+            def elapsed_time(self, other): return 0.0
+        real_event, torch.cuda.Event = torch.cuda.Event, _Ev
+        try:
+            rng = np.random.default_rng(11)
+            sizes = rng.integers(0, 5, (2, world, world))            # [X / R][source][destination]
+            def payload(kind, src, dst, n):
+                return [10000 * kind + 100 * src + 10 * dst + j for j in range(n)]
+            def tensor(kind, dtype):
+                vals = [v for d in range(world) for v in payload(kind, rank, d, sizes[kind % 2, rank, d])]
+                return torch.tensor(vals, dtype=dtype)
+            items = [(tensor(0, torch.int64), [int(x) for x in sizes[0, rank]], 1),
+                     (tensor(1, torch.int64), [int(x) for x in sizes[1, rank]], 2),
+                     (tensor(2, torch.int32), [int(x) for x in sizes[0, rank]], 3),
+                     (tensor(3, torch.int32), [int(x) for x in sizes[1, rank]], 4)]
+            got = db._exchange_many(items, "strands")
+            for kind in range(4):
+                exp = [v for s in range(world) for v in payload(kind, s, rank, sizes[kind % 2, s, rank])]
+                assert got[kind][0].tolist() == exp, kind
+                assert got[kind][1] == [int(sizes[kind % 2, s, rank]) for s in range(world)]
+            assert len(db.verified) == 4
+        finally:
+            torch.cuda.Event = real_event
+        dist.barrier()
+        if rank == 0:
+            open(os.path.join(tmp, "ok_exchange4"), "w").write("ok")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_gloo_four_item_exchange_at_world_8(tmp_path):
+    mp.spawn(_exchange4_worker, args=(8, _free_port(), str(tmp_path)), nprocs=8, join=True)
+    assert os.path.exists(tmp_path / "ok_exchange4")
